@@ -1,0 +1,108 @@
+/* libsphb200 — C ABI of the B200-native SPH particle time-step.
+ *
+ * The reference (dmuley/sph-code) has no FFI layer: its boundary for this path is the Python module
+ * namespace `navier_stokes_cleaned` (imported as `nsc`, sph/code_running.py:12).  Each entry point
+ * below is what a binding for one function of that namespace calls; the Python module
+ * `sph-code_b200/navier_stokes_cleaned.py` is that binding (ctypes), see INTEGRATION.md.
+ *
+ * Conventions
+ *   - every array pointer is a DEVICE pointer (cudaMalloc / torch tensor .data_ptr()) unless its
+ *     name ends in `_host`; arrays are C-contiguous float64 unless stated;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); calls are
+ *     asynchronous on that stream except where a host result is returned;
+ *   - return value 0 = success, non-zero = failure with the message in sphb200_last_error();
+ *   - no exceptions cross the ABI; one context per GPU; a context is not thread-safe.
+ */
+#ifndef SPHB200_H
+#define SPHB200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sphb200_ctx sphb200_ctx;
+
+/* ---- context ------------------------------------------------------------------------------ */
+int sphb200_create(sphb200_ctx** out, int device);
+int sphb200_destroy(sphb200_ctx* ctx);
+const char* sphb200_last_error(void);
+int sphb200_version(void);
+/* physical constants the reference takes from scipy.constants (navier_stokes_cleaned.py:21-36):
+ * Boltzmann k, atomic mass constant amu, hydrogen mass m_h, reference mass m_0 */
+int sphb200_set_constants(sphb200_ctx* ctx, double k_boltzmann, double amu, double m_h, double m_0);
+/* tunables: "cell_occ" (mean particles per cell), "cell_edge" (fixed cell edge, 0 = automatic),
+ * "knn_group" (lanes per target: 8, 16 or 32) */
+int sphb200_set_option(sphb200_ctx* ctx, const char* name, double value);
+/* counters: "launches", "knn_overflow", "knn_rescan", "knn_widen", "bad_index"; reading a flag
+ * synchronises the stream and resets it */
+int sphb200_get_counter(sphb200_ctx* ctx, const char* name, int64_t* value_host, void* stream);
+
+/* ---- A1: neighbors(points, dist, N_NEIGH)            navier_stokes_cleaned.py:541-552 ---------
+ * points (N,3).  Outputs: idx (N,k) int64 ascending distance, self first, missing = N;
+ * dists (N,k) (missing = 0); nontriv (N) int64; new_sizes (N) = row max of dists.
+ * Exact k-NN (the reference's eps=0.1 approximate search is replaced by eps=0). */
+int sphb200_neighbors(sphb200_ctx* ctx, const double* points, int64_t n, int k, double dist, int64_t* idx,
+                      double* dists, int64_t* nontriv, double* new_sizes, void* stream);
+
+/* ---- A2-A6: hydro_update(...)                         navier_stokes_cleaned.py:556-671 ---------
+ * neighbor (N,k) int64; points, velocities (N,3); mass, sizes, particle_type, T, mu_array,
+ * gamma_array (N); f_un (N,S) or NULL.  Outputs: hydro_accel, visc_accel (N,3); visc_heat, density,
+ * num_density, dust_density (N); f_un_neighbor (S,N) or NULL.
+ * Fails (IndexError in the binding) if a neighbour index is outside [-N, N). */
+int sphb200_hydro_update(sphb200_ctx* ctx, int64_t n, int k, const int64_t* neighbor, const double* points,
+                         const double* mass, const double* sizes, const double* f_un, int n_species,
+                         const double* particle_type, const double* T, const double* mu_array,
+                         const double* gamma_array, const double* velocities, double* hydro_accel,
+                         double* visc_accel, double* visc_heat, double* density, double* num_density,
+                         double* f_un_neighbor, double* dust_density, void* stream);
+
+/* ---- A9: crossing_time(neighbor, velocities, sizes, particle_type)         nsc:776-786 ---------
+ * result (seconds) is written to *result_host after synchronising the stream. */
+int sphb200_crossing_time(sphb200_ctx* ctx, int64_t n, int k, const int64_t* neighbor, const double* velocities,
+                          const double* sizes, const double* particle_type, double dt_0, double* result_host,
+                          void* stream);
+
+/* ---- A7-A8: loop-generation sums                                          nsc:673-816 ---------
+ * `d` is the module-global length scale the reference reads (nsc.d).  neighbor entries < 0 are
+ * padding (ragged rows).  mode: 0 density (nsc:693), 1 dust_density (nsc:704), 2 num_dens (nsc:744). */
+int sphb200_loop_density(sphb200_ctx* ctx, int mode, int64_t n, int k, const int64_t* neighbor, const double* points,
+                         const double* mass, const double* particle_type, const double* sizes,
+                         const double* mu_array, double d, double* out, void* stream);
+int sphb200_del_pressure(sphb200_ctx* ctx, int64_t n, int k, const int64_t* neighbor, const double* points,
+                         const double* mass, const double* particle_type, const double* E_internal,
+                         const double* gamma_array, double d, double* grad_pressure, void* stream);
+int sphb200_artificial_viscosity(sphb200_ctx* ctx, int64_t n, int k, const int64_t* neighbor, const double* points,
+                                 const double* particle_type, const double* sizes, const double* mass,
+                                 const double* densities, const double* velocities, const double* T,
+                                 const double* gamma_array, const double* mu_array, double d, double* visc_accel,
+                                 double* visc_heat, void* stream);
+
+/* ---- A10-A13: device-resident particle state and the whole time step ---------------------------
+ * The reference keeps its particle state as module-level numpy arrays in the driver
+ * (sph/code_running.py:121-167) and advances it inline (:217-540).  A session holds the same
+ * struct-of-arrays in HBM and advances it without leaving the GPU.
+ * Field names are the driver's variable names: "points", "velocities", "total_accel" (N,3);
+ * "mass", "sizes", "T", "E_internal", "mu_array", "gamma_array", "particle_type", "densities_0" (N).
+ * Read-only results: "densities", "num_densities", "dust_densities", "visc_heat" (N); "hydro_accel",
+ * "visc_accel", "pressure_accel" (N,3); "neighbor" (N,k) int64; "num_nontrivial" (N) int64.
+ * upload/download take DEVICE pointers in the caller's particle order. */
+int sphb200_session_create(sphb200_ctx* ctx, int64_t n, int k, double dist);
+int sphb200_session_upload(sphb200_ctx* ctx, const char* field, const void* src, int64_t count);
+int sphb200_session_download(sphb200_ctx* ctx, const char* field, void* dst, int64_t count, void* stream);
+/* run parameters: "dt_0", "MAX_AGE", "N_INT_PER_PARTICLE", "raise_factor", "AU", "dist", "age", "d", "dt" */
+int sphb200_session_set_scalar(sphb200_ctx* ctx, const char* name, double value);
+/* device scalars of the last step: "ct", "dt", "d", "age", "max_dist", "n_slow" (synchronises) */
+int sphb200_session_scalar(sphb200_ctx* ctx, const char* name, double* value_host, void* stream);
+/* code_running.py:171-179: first neighbour query + hydro_update, densities_0 <- densities */
+int sphb200_session_startup(sphb200_ctx* ctx, void* stream);
+/* one pass of the while-body, code_running.py:217-540 (gas/dust only, gravity/drag/chemistry zero) */
+int sphb200_session_step(sphb200_ctx* ctx, void* stream);
+/* one phase of the step, for per-kernel timing: "crossing", "dt_clamp", "sort", "knn", "pack",
+ * "density", "pi", "force", "integrate" */
+int sphb200_session_phase(sphb200_ctx* ctx, const char* phase, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

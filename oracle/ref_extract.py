@@ -1,0 +1,84 @@
+"""TEST INFRASTRUCTURE — not product code.
+
+Runs the reference's OWN text for the SPH hot path.  Nothing is copied into this
+repo: the cited line ranges of /root/reference/sph/navier_stokes_cleaned.py are read
+at run time, Python-2 `print` statements are neutralised, and the text is exec'd
+into a private namespace.  /root/reference exists only in the build container, so
+this module is used only by tests/golden/make_golden.py (fixture generator) and by
+the `-m "not gpu"` tests that validate oracle/sph_oracle.py (they skip when the
+reference tree is absent).  Nothing under the product package imports it.
+
+Documented deviations from the reference as written:
+  1. `eps`: `load(eps=0.0)` rewrites the literal 0.1 in `kdt.query(points, N_NEIGH, 0.1, 2, dist)`
+     (navier_stokes_cleaned.py:544) to 0.0 so the k-NN is exact; `eps=None` keeps 0.1.
+  2. `axis=1` -> `axis=0` in the artificial-viscosity reduction at
+     navier_stokes_cleaned.py:649 (as written the block raises IndexError for N>k).
+Both are applied by textual substitution on the exact reference line and asserted.
+"""
+import os
+import re
+import time
+
+import numpy as np
+
+REF_ROOT = os.environ.get("SPH_REFERENCE_ROOT", "/root/reference")
+NSC_PATH = os.path.join(REF_ROOT, "sph", "navier_stokes_cleaned.py")
+
+# (first, last) 1-based inclusive line ranges of navier_stokes_cleaned.py that are exec'd
+_RANGES = (
+    (21, 52),    # physical constants, species tables
+    (541, 552),  # neighbors
+    (556, 671),  # hydro_update
+    (673, 690),  # Weigh2, Weigh2_dust, grad_weight
+    (693, 717),  # density, dust_density
+    (744, 816),  # num_dens, del_pressure, crossing_time, artificial_viscosity
+)
+
+_PRINT = re.compile(r"^(\s*)print\b.*$")
+
+
+def available():
+    return os.path.isfile(NSC_PATH)
+
+
+def load(eps=0.0, repair_viscosity=True):
+    """Return a namespace object holding the reference functions.
+
+    The namespace doubles as the reference's module scope: set `ns.d`, `ns.dt_0` … the way
+    code_running.py:68-75 assigns `nsc.d`, `nsc.dt_0`.
+    """
+    with open(NSC_PATH, "r") as fh:
+        lines = fh.read().split("\n")
+    out = []
+    for a, b in _RANGES:
+        for ln in range(a, b + 1):
+            text = lines[ln - 1]
+            m = _PRINT.match(text)
+            if m:
+                text = m.group(1) + "pass"
+            if ln == 544 and eps is not None:
+                assert "N_NEIGH, 0.1, 2, dist" in text, text
+                text = text.replace("N_NEIGH, 0.1, 2, dist", "N_NEIGH, %r, 2, dist" % float(eps))
+            if ln == 649 and repair_viscosity:
+                assert text.rstrip().endswith("w_ab/rho_avg_ab,axis=1)"), text
+                text = text.rstrip()[: -len("axis=1)")] + "axis=0)"
+            out.append(text)
+        out.append("")
+    src = "\n".join(out)
+    from scipy import constants, spatial
+    glb = {"np": np, "constants": constants, "spatial": spatial, "time": time, "__name__": "nsc_reference"}
+    exec(compile(src, NSC_PATH + "<extracted>", "exec"), glb)
+
+    class _NS(object):
+        """attribute view of the exec'd globals (so `ns.d = ...` behaves like `nsc.d = ...`)."""
+
+        def __getattr__(self, name):
+            try:
+                return glb[name]
+            except KeyError:
+                raise AttributeError(name)
+
+        def __setattr__(self, name, value):
+            glb[name] = value
+
+    return _NS()

@@ -1,0 +1,110 @@
+// Shared declarations for libsphb200 (B200 / sm_100a only).
+// Device data layout, context and error plumbing.  See DESIGN.md "Data layout in HBM".
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#define SPHB200_MAX_ERR 512
+extern thread_local char g_sphb200_err[SPHB200_MAX_ERR];
+
+#define SPH_FAIL(...)                                                   \
+  do {                                                                  \
+    snprintf(g_sphb200_err, SPHB200_MAX_ERR, __VA_ARGS__);              \
+    return 1;                                                           \
+  } while (0)
+
+#define CUDA_TRY(expr)                                                                        \
+  do {                                                                                        \
+    cudaError_t _e = (expr);                                                                  \
+    if (_e != cudaSuccess) {                                                                  \
+      snprintf(g_sphb200_err, SPHB200_MAX_ERR, "%s:%d: %s -> %s", __FILE__, __LINE__, #expr,  \
+               cudaGetErrorString(_e));                                                       \
+      return 1;                                                                               \
+    }                                                                                         \
+  } while (0)
+
+#define SPH_TRY(expr)            \
+  do {                           \
+    int _r = (expr);             \
+    if (_r) return _r;           \
+  } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// Packed per-particle records.  Every gather kernel reads whole 32-byte records (two LDG.128 /
+// one 256-bit sector pair) so a neighbour costs a fixed number of sectors.
+//   R0 = {x, y, z, h^2}                    geometry                       (all gather passes)
+//   R1 = {c6, m_gas, m_num, m_dust}        c6 = 315/(64 pi h^9);  m_gas = m [t==0];
+//                                          m_num = m [t==0]/(amu mu);  m_dust = m [t==2]   (density)
+//   R2 = {vx, vy, vz, cs}                  cs = sqrt(gamma k T [t==0]/(mu amu))            (Pi, force)
+//   R3 = {AK, PK}                          AK = 6 c6 * m k T [t==0]/(mu amu)
+//                                          PK = 6 c6 * m Pi [t==0]                         (force)
+// ---------------------------------------------------------------------------------------------
+struct __align__(16) rec2 { double a, b; };
+
+struct PhysConst { double kB, amu; };
+
+struct GridSpec {
+  double ox, oy, oz;   // origin (lower corner of cell (0,0,0))
+  double inv_c;        // 1 / cell edge
+  double c;            // cell edge
+  int nx, ny, nz;
+  int ncells;
+};
+
+// A growable device buffer owned by the context.
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+};
+
+struct sphb200_ctx {
+  int device = 0;
+  PhysConst phys = {1.380649e-23, 1.66053906892e-27};   // overwritten by sphb200_set_constants
+  double m_h = 1.0008 * 1.66053906892e-27;
+  double m_0 = 31.622776601683793 * 1.989e30;
+  // --- scratch / session state (sorted particle order unless noted) ---
+  DevBuf r0, r1, r2, r3;           // packed records, N+1 entries (entry N = the reference's dummy particle)
+  DevBuf rho, pi_, aux;            // per-particle doubles
+  DevBuf list;                     // (N,k) int32 neighbour list in the index space of the records
+  DevBuf keys, keys_alt, perm, perm_alt, cell_start, cub_tmp;
+  DevBuf scal;                     // device scalars (doubles), see enum Scal
+  DevBuf flags;                    // device ints: error / statistics counters
+  DevBuf tmp0, tmp1, tmp2, tmp3;   // generic scratch
+  DevBuf sbuf[48];                 // session arrays (session.cu)
+  double cell_occ = 12.0;          // target mean particles per cell (tunable)
+  double cell_edge = 0.0;          // fixed cell edge (0 = from cell_occ)
+  int knn_group = 32;              // lanes per target in the k-NN kernel
+  GridSpec grid;
+  int64_t launches = 0;            // kernels launched through this context (for bench "gpu_launches")
+};
+
+int devbuf_reserve(DevBuf& b, size_t bytes);
+void devbuf_free(DevBuf& b);
+
+template <typename T>
+static inline T* bufp(DevBuf& b) { return reinterpret_cast<T*>(b.p); }
+
+static inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+// enum of device scalars kept in ctx->scal (doubles)
+enum Scal {
+  SC_BBOX = 0,        // 6 doubles: min x,y,z, max x,y,z
+  SC_CT = 6,          // crossing time (min over gas particles)
+  SC_DT = 7,
+  SC_D = 8,           // global length scale d
+  SC_AGE = 9,
+  SC_MAXDIST = 10,    // 90th percentile of |x|^2 among slow particles
+  SC_NSLOW = 11,
+  SC_COUNT = 32
+};
+
+// flags (ints)
+enum Flag {
+  FL_KNN_OVERFLOW = 0,   // k-NN: targets that exhausted the retry budget
+  FL_KNN_RESCAN = 1,     // k-NN: number of extra scans (statistics)
+  FL_KNN_WIDEN = 2,      // k-NN: number of targets that needed a wider cell block
+  FL_BAD_INDEX = 3,      // neighbour index outside [0, N)
+  FL_COUNT = 16
+};

@@ -1,0 +1,50 @@
+// Internal launch interfaces between the translation units of libsphb200.
+#pragma once
+#include "common.cuh"
+
+// cells.cu
+int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint, cudaStream_t st);
+
+// knn.cu
+int knn_cap_for(int k);
+int launch_knn(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, int32_t* list, double* dists,
+               double* h_out, int32_t* nontriv, cudaStream_t st);
+int launch_knn_unsort(sphb200_ctx* ctx, const int32_t* list, const double* dists, const double* h, const int32_t* nontriv,
+                      int n, int k, int64_t* idx_out, double* dist_out, int64_t* nontriv_out, double* h_out,
+                      cudaStream_t st);
+
+// hydro.cu  (vectorised generation, nsc:556-671)
+struct PackIn {
+  const double* points;     // (N,3) or nullptr when r0.xyz is already filled (sorted session path)
+  const double* vel;        // (N,3)
+  const double* mass;       // (N)
+  const double* h;          // (N)
+  const double* ptype;      // (N) 0 gas, 1 star, 2 dust (float64, as the reference stores it)
+  const double* T;          // (N)
+  const double* mu;         // (N)
+  const double* gamma;      // (N)
+};
+int launch_pack(sphb200_ctx* ctx, int n, const PackIn& in, cudaStream_t st);
+int launch_convert_list(sphb200_ctx* ctx, const int64_t* nb, int n, int k, int32_t* list, cudaStream_t st);
+int launch_density(sphb200_ctx* ctx, int n, int k, const int32_t* list, double* rho, double* dust, double* num,
+                   cudaStream_t st);
+int launch_pi(sphb200_ctx* ctx, int n, int k, const int32_t* list, const double* rho, cudaStream_t st);
+int launch_force(sphb200_ctx* ctx, int n, int k, const int32_t* list, const double* rho, const double* mass,
+                 double* hydro_accel, double* visc_accel, double* visc_heat, cudaStream_t st);
+int launch_species(sphb200_ctx* ctx, int n, int k, int S, const int32_t* list, const double* f_un, double* out,
+                   cudaStream_t st);
+int launch_crossing_time(sphb200_ctx* ctx, int n, int k, const int32_t* list, const double* vel, const double* sizes,
+                         const double* ptype, double dt_0, double* out_dev, cudaStream_t st);
+
+// loopgen.cu  (loop generation, nsc:673-816)
+struct LoopIn {
+  const double* points; const double* vel; const double* mass; const double* sizes; const double* ptype;
+  const double* T; const double* mu; const double* gamma; const double* E; const double* dens;
+  double d;
+};
+int launch_loop_density(sphb200_ctx* ctx, int n, int k, const int32_t* list, const LoopIn& in, int mode, double* out,
+                        cudaStream_t st);
+int launch_loop_del_pressure(sphb200_ctx* ctx, int n, int k, const int32_t* list, const LoopIn& in, double* out,
+                             cudaStream_t st);
+int launch_loop_viscosity(sphb200_ctx* ctx, int n, int k, const int32_t* list, const LoopIn& in, double* accel,
+                          double* heat, cudaStream_t st);

@@ -1,0 +1,221 @@
+// Exact fixed-k nearest-neighbour search on the cell list.
+// Replaces `kdt.query(points, N_NEIGH, eps, 2, dist)` of
+// /root/reference/sph/navier_stokes_cleaned.py:544 (with eps = 0) and the row-max
+// smoothing length of :548.
+//
+// One group of G lanes per target particle.  Lanes stride over the contiguous runs of sorted
+// particles that make up the (2m+1)^3 cell block around the target (cells along x are contiguous in
+// the sort order, so a block is (2m+1)^2 runs), test d^2 < R_try^2 and compact the survivors into a
+// per-group shared-memory buffer with ballot/popc.  R_try starts at the radius expected to hold
+// ~1.35 k particles at the block's mean density and is corrected (shrunk on overflow, grown when
+// fewer than k survive) until it holds between k and CAP candidates; it never exceeds the radius
+// R_safe = m*c that the searched block is guaranteed to cover, so the result is exact.  The k
+// smallest are then ranked by counting (rank = number of smaller keys), which also yields the
+// ascending-distance row order the reference's API returns.
+//
+// d^2 is evaluated as ((dx*dx + dy*dy) + dz*dz) with separately rounded products (no FMA
+// contraction) — the same arithmetic as numpy and cKDTree — so that the ordering of near-equal
+// distances and the returned h = sqrt(d^2_k) are bit-identical to the CPU oracle.
+#include "common.cuh"
+#include "kernels.cuh"
+#include <cooperative_groups.h>
+#include <cooperative_groups/reduce.h>
+#include <float.h>
+namespace cg = cooperative_groups;
+
+#define KNN_THREADS 128
+#define KNN_MAX_ITER 96
+
+template <int G>
+__global__ void __launch_bounds__(KNN_THREADS)
+knn_kernel(const double4* __restrict__ r0, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ cell_start,
+           GridSpec g, int n, int k, double dist2, int cap, const double* __restrict__ h_guess,
+           int32_t* __restrict__ list, double* __restrict__ dists, double* __restrict__ h_out,
+           int32_t* __restrict__ nontriv, int* __restrict__ flags) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cg::thread_block blk = cg::this_thread_block();
+  cg::thread_block_tile<G> tile = cg::tiled_partition<G>(blk);
+  const int lane = tile.thread_rank();
+  const int grp = tile.meta_group_rank();
+  constexpr int GROUPS = KNN_THREADS / G;
+  unsigned long long* keybuf = reinterpret_cast<unsigned long long*>(smem_raw) + (size_t)grp * cap;
+  int32_t* idxbuf = reinterpret_cast<int32_t*>(smem_raw + (size_t)GROUPS * cap * sizeof(unsigned long long)) + (size_t)grp * cap;
+
+  const int i = blockIdx.x * GROUPS + grp;
+  if (i >= n) return;
+  const double4 p = r0[i];
+  const uint32_t key = keys[i];
+  const int cx = key % g.nx, cy = (key / g.nx) % g.ny, cz = key / (g.nx * g.ny);
+  const double c3 = g.c * g.c * g.c;
+
+  int m = 1;
+  double R2try = -1.0;
+  if (h_guess) { double hg = h_guess[i]; if (hg > 0.0) { R2try = hg * hg; m = (int)(hg * g.inv_c) + 1; } }
+  int count = 0;
+  bool done = false;
+  int iter = 0, rescans = -1, widened = 0;
+  for (; iter < KNN_MAX_ITER && !done; ++iter) {
+    const int x0 = max(cx - m, 0), x1 = min(cx + m, g.nx - 1);
+    const int y0 = max(cy - m, 0), y1 = min(cy + m, g.ny - 1);
+    const int z0 = max(cz - m, 0), z1 = min(cz + m, g.nz - 1);
+    const bool whole = (x0 == 0 && y0 == 0 && z0 == 0 && x1 == g.nx - 1 && y1 == g.ny - 1 && z1 == g.nz - 1);
+    const double rsafe = (double)m * g.c * (1.0 - 1e-8);
+    const double R2lim = whole ? dist2 : fmin(dist2, rsafe * rsafe);
+    const int ysp = y1 - y0 + 1;
+    const int nrows = ysp * (z1 - z0 + 1);
+    if (R2try < 0.0) {
+      int cnt = 0;
+      for (int r = lane; r < nrows; r += G) {
+        const int base = ((z0 + r / ysp) * g.ny + (y0 + r % ysp)) * g.nx;
+        cnt += (int)(cell_start[base + x1 + 1] - cell_start[base + x0]);
+      }
+      cnt = cg::reduce(tile, cnt, cg::plus<int>());
+      if (cnt < k && !whole) { ++m; widened = 1; continue; }
+      const double vol = (double)(x1 - x0 + 1) * (double)nrows * c3;
+      const double R3 = 1.35 * (double)k * vol / (4.1887902047863905 * (double)(cnt > 0 ? cnt : 1));
+      const double Rt = cbrt(R3);
+      R2try = fmin(R2lim, Rt * Rt);
+    } else if (R2try > R2lim) {
+      R2try = R2lim;
+    }
+    // ---- scan the block ----
+    ++rescans;
+    count = 0;
+    for (int r = 0; r < nrows; ++r) {
+      const int base = ((z0 + r / ysp) * g.ny + (y0 + r % ysp)) * g.nx;
+      const int s = (int)cell_start[base + x0], e = (int)cell_start[base + x1 + 1];
+      for (int jb = s; jb < e; jb += G) {
+        const int j = jb + lane;
+        bool ok = false;
+        double d2 = 0.0;
+        if (j < e) {
+          const double4 q = r0[j];
+          const double dx = q.x - p.x, dy = q.y - p.y, dz = q.z - p.z;
+          d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+          ok = d2 < R2try;
+        }
+        const unsigned b = tile.ballot(ok);
+        if (b) {
+          const int pos = count + __popc(b & ((1u << lane) - 1u));
+          if (ok && pos < cap) { keybuf[pos] = (unsigned long long)__double_as_longlong(d2); idxbuf[pos] = j; }
+          count += __popc(b);
+        }
+      }
+    }
+    tile.sync();
+    if (count > cap) {                     // too many survivors: shrink the trial radius
+      const double f = cbrt(0.6 * (double)cap / (double)count);
+      R2try *= f * f;
+      continue;
+    }
+    if (count >= k) { done = true; break; }
+    if (R2try < R2lim) {                    // too few: grow towards the covered radius
+      const double f = cbrt(1.6 * (double)k / (double)(count > 0 ? count : 1));
+      R2try = fmin(R2lim, R2try * fmax(f * f, 1.2));
+      continue;
+    }
+    if (whole || R2lim >= dist2) { done = true; break; }   // everything inside the cut was seen
+    ++m; widened = 1;                       // block too small: widen, re-estimate
+    R2try = -1.0;
+  }
+  if (lane == 0) {
+    if (!done) atomicAdd(&flags[FL_KNN_OVERFLOW], 1);
+    if (rescans > 0) atomicAdd(&flags[FL_KNN_RESCAN], rescans);
+    if (widened) atomicAdd(&flags[FL_KNN_WIDEN], 1);
+  }
+  if (count > cap) count = cap;
+  // ---- rank by counting; rank < k are the neighbours, in ascending (d^2, index) order ----
+  const int nsel = count < k ? count : k;
+  const int64_t row = (int64_t)i * k;
+  for (int e = lane; e < count; e += G) {
+    const unsigned long long ke = keybuf[e];
+    const int je = idxbuf[e];
+    int rank = 0;
+    for (int f = 0; f < count; ++f) {
+      const unsigned long long kf = keybuf[f];
+      rank += (kf < ke) || (kf == ke && idxbuf[f] < je);
+    }
+    if (rank < k) {
+      list[row + rank] = je;
+      const double dd = sqrt(__longlong_as_double((long long)ke));
+      if (dists) dists[row + rank] = dd;
+      if (rank == nsel - 1) h_out[i] = dd;
+    }
+  }
+  for (int s = count + lane; s < k; s += G) {
+    list[row + s] = n;
+    if (dists) dists[row + s] = 0.0;
+  }
+  if (lane == 0) {
+    nontriv[i] = nsel;
+    if (nsel == 0) h_out[i] = 0.0;
+  }
+}
+
+int knn_cap_for(int k) {
+  int cap = ((3 * k + 31) / 32) * 32;
+  if (cap < 64) cap = 64;
+  return cap;
+}
+
+int launch_knn(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, int32_t* list, double* dists,
+               double* h_out, int32_t* nontriv, cudaStream_t st) {
+  if (k < 1) SPH_FAIL("knn: k must be >= 1");
+  const int cap = knn_cap_for(k);
+  const int G = ctx->knn_group;
+  const int groups = KNN_THREADS / G;
+  const size_t smem = (size_t)groups * cap * 12;
+  if (smem > 200 * 1024) SPH_FAIL("knn: k=%d needs %zu B of shared memory per block", k, smem);
+  double dist2 = dist * dist;                 // cKDTree squares the upper bound for p=2
+  if (!(dist2 == dist2)) dist2 = INFINITY;
+  const double4* r0 = bufp<double4>(ctx->r0);
+  const uint32_t* keys = bufp<uint32_t>(ctx->keys);
+  const uint32_t* cs = bufp<uint32_t>(ctx->cell_start);
+  int* flags = bufp<int>(ctx->flags);
+  const int blocks = ceil_div(n, groups);
+#define KNN_LAUNCH(GG)                                                                                         \
+  do {                                                                                                         \
+    if (smem > 48 * 1024)                                                                                      \
+      CUDA_TRY(cudaFuncSetAttribute(knn_kernel<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));  \
+    knn_kernel<GG><<<blocks, KNN_THREADS, smem, st>>>(r0, keys, cs, ctx->grid, n, k, dist2, cap, h_guess, list, \
+                                                      dists, h_out, nontriv, flags);                           \
+  } while (0)
+  if (G == 32) KNN_LAUNCH(32);
+  else if (G == 16) KNN_LAUNCH(16);
+  else if (G == 8) KNN_LAUNCH(8);
+  else SPH_FAIL("knn: unsupported group size %d", G);
+#undef KNN_LAUNCH
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// Sorted-space rows -> the reference's return layout (original particle order, int64 indices,
+// missing neighbour = N / distance 0).                                   nsc:545-548,552
+__global__ void __launch_bounds__(256)
+knn_unsort_kernel(const int32_t* __restrict__ list, const double* __restrict__ dists, const double* __restrict__ h,
+                  const int32_t* __restrict__ nontriv, const uint32_t* __restrict__ perm, int n, int k,
+                  int64_t* __restrict__ idx_out, double* __restrict__ dist_out, int64_t* __restrict__ nontriv_out,
+                  double* __restrict__ h_out) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= (int64_t)n * k) return;
+  const int i = (int)(t / k), s = (int)(t % k);
+  const int64_t o = (int64_t)perm[i] * k + s;
+  const int j = list[t];
+  idx_out[o] = (j < n) ? (int64_t)perm[j] : (int64_t)n;
+  dist_out[o] = dists[t];
+  if (s == 0) {
+    nontriv_out[perm[i]] = nontriv[i];
+    h_out[perm[i]] = h[i];
+  }
+}
+
+int launch_knn_unsort(sphb200_ctx* ctx, const int32_t* list, const double* dists, const double* h, const int32_t* nontriv,
+                      int n, int k, int64_t* idx_out, double* dist_out, int64_t* nontriv_out, double* h_out,
+                      cudaStream_t st) {
+  knn_unsort_kernel<<<ceil_div((int64_t)n * k, 256), 256, 0, st>>>(list, dists, h, nontriv, bufp<uint32_t>(ctx->perm), n, k,
+                                                                   idx_out, dist_out, nontriv_out, h_out);
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}

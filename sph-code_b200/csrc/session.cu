@@ -1,0 +1,514 @@
+// Device-resident particle state and the full time step in the reference driver's order
+// (/root/reference/sph/code_running.py:217-540, gas/dust only; conventions in DESIGN.md §step).
+// The state lives in HBM in the CURRENT SORT ORDER (cell order of the last neighbour build) and is
+// re-gathered through the new permutation each step; `id` maps back to the caller's order.
+#include "common.cuh"
+#include "kernels.cuh"
+#include "../../include/sphb200.h"
+#include <cub/cub.cuh>
+#include <float.h>
+#include <math.h>
+
+enum Field { F_POS = 0, F_VEL, F_ACC, F_MASS, F_H, F_T, F_E, F_MU, F_GAMMA, F_TYPE, F_RHO0, F_NFIELDS };
+static const int kFieldWidth[F_NFIELDS] = {3, 3, 3, 1, 1, 1, 1, 1, 1, 1, 1};
+static const char* kFieldName[F_NFIELDS] = {"points", "velocities", "total_accel", "mass", "sizes", "T", "E_internal",
+                                            "mu_array", "gamma_array", "particle_type", "densities_0"};
+enum Out { O_RHO = 0, O_NUM, O_DUST, O_HACC, O_VACC, O_HEAT, O_PACC, O_NOUT };
+static const int kOutWidth[O_NOUT] = {1, 1, 1, 3, 3, 1, 3};
+static const char* kOutName[O_NOUT] = {"densities", "num_densities", "dust_densities", "hydro_accel", "visc_accel",
+                                       "visc_heat", "pressure_accel"};
+// sbuf layout: [2*f + which] state double buffers, then ids, outputs, scratch
+#define SB_ID 24
+#define SB_ID_ALT 25
+#define SB_OUT 26            // .. 26 + O_NOUT
+#define SB_NONTRIV 34
+#define SB_DISTSQ 35
+#define SB_DISTSQ_ALT 36
+#define SB_KNNH 37           // k-th neighbour distance of the last search (guess for the next one)
+#define SB_KNNH_ALT 38
+
+struct SessionScalars {      // host mirror of the run parameters
+  double dt_0, max_age, n_int, raise_factor, au;
+};
+
+struct Session {
+  int64_t n = 0;
+  int k = 0;
+  double dist = 0;
+  int cur[F_NFIELDS];        // which of the two buffers is current
+  int id_cur = 0;
+  int knnh_cur = 0;
+  int has_list = 0;
+  int use_guess = 1;
+  SessionScalars sc;
+};
+static Session g_sess[16];   // one per device
+
+static Session& sess(sphb200_ctx* ctx) { return g_sess[ctx->device & 15]; }
+static double* fld(sphb200_ctx* ctx, int f, int alt = 0) {
+  Session& s = sess(ctx);
+  return bufp<double>(ctx->sbuf[2 * f + (s.cur[f] ^ alt)]);
+}
+static double* outp(sphb200_ctx* ctx, int o) { return bufp<double>(ctx->sbuf[SB_OUT + o]); }
+
+__device__ __forceinline__ double nan_to_num_d(double v) {
+  if (v != v) return 0.0;
+  if (v > DBL_MAX) return DBL_MAX;
+  if (v < -DBL_MAX) return -DBL_MAX;
+  return v;
+}
+
+// ---- A10: time-step choice (device scalar)                          code_running.py:222-231 ----
+__global__ void choose_dt_kernel(double* scal, SessionScalars sc) {
+  const double ct = scal[SC_CT];
+  const double age = scal[SC_AGE];
+  double dt = (age == 0.0) ? sc.dt_0 / 10 : fmax(sc.dt_0 / 5., fmin(sc.dt_0 * 2., ct));
+  if (ct > sc.max_age) dt = sc.max_age / 100.;
+  scal[SC_DT] = dt;
+  scal[SC_AGE] = age + dt;                                                       // :447
+}
+
+// ---- A10: position clamp + nan_to_num                                code_running.py:233-238 ----
+__global__ void __launch_bounds__(256) clamp_kernel(int64_t n3, double lim, double* __restrict__ pos, double* __restrict__ vel) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= n3) return;
+  double x = pos[t];
+  if (x > lim) x = lim;
+  if (x < -lim) x = -lim;
+  // velocities[points > lim] = 0.1 is evaluated after the clamp, so it never fires (as written)
+  pos[t] = nan_to_num_d(x);
+  vel[t] = nan_to_num_d(vel[t]);
+}
+
+struct ReorderArgs {
+  const double* src[F_NFIELDS];
+  double* dst[F_NFIELDS];
+  const uint32_t* id_src; uint32_t* id_dst;
+  const double* knnh_src; double* knnh_dst;
+};
+
+__global__ void __launch_bounds__(256) reorder_kernel(int n, const uint32_t* __restrict__ perm, ReorderArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int64_t p = perm[i];
+#pragma unroll
+  for (int f = 0; f < 3; ++f) {
+    a.dst[f][3 * (int64_t)i + 0] = a.src[f][3 * p + 0];
+    a.dst[f][3 * (int64_t)i + 1] = a.src[f][3 * p + 1];
+    a.dst[f][3 * (int64_t)i + 2] = a.src[f][3 * p + 2];
+  }
+#pragma unroll
+  for (int f = 3; f < F_NFIELDS; ++f) a.dst[f][i] = a.src[f][p];
+  a.id_dst[i] = a.id_src[p];
+  a.knnh_dst[i] = a.knnh_src[p];
+}
+
+__global__ void __launch_bounds__(256) iota_kernel(int n, uint32_t* id) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) id[i] = (uint32_t)i;
+}
+
+// ---- A11: force assembly, kick-drift, heating                        code_running.py:460-491 ----
+// also emits |x|^2 (or +inf for fast particles) for the percentile of A12 and counts slow particles.
+__global__ void __launch_bounds__(256)
+integrate_kernel(int n, const double* __restrict__ scal, double kB, double m_h, double* __restrict__ pos,
+                 double* __restrict__ vel, double* __restrict__ acc, double* __restrict__ E, double* __restrict__ T,
+                 const double* __restrict__ mass, const double* __restrict__ mu, const double* __restrict__ gamma,
+                 const double* __restrict__ ptype, const double* __restrict__ hacc, double* __restrict__ vacc,
+                 const double* __restrict__ heat, double* __restrict__ pacc, double* __restrict__ distsq,
+                 unsigned long long* __restrict__ nslow) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int slow = 0;
+  if (i < n) {
+    const double dt = scal[SC_DT];
+    const double gas = (ptype[i] == 0.0) ? 1.0 : 0.0;
+    double v[3], a[3], x[3], av[3], ap[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      v[c] = vel[3 * (int64_t)i + c];
+      x[c] = pos[3 * (int64_t)i + c];
+      av[c] = vacc[3 * (int64_t)i + c];
+      ap[c] = nan_to_num_d(hacc[3 * (int64_t)i + c] * gas);                     // :460
+    }
+    const double vmag = sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+    const double amag = sqrt(av[0] * av[0] + av[1] * av[1] + av[2] * av[2]);
+    if (vmag - amag * dt < 0) {                                                  // :475
+#pragma unroll
+      for (int c = 0; c < 3; ++c) av[c] = -v[c] / dt;
+    }
+    double v2 = 0.0, x2 = 0.0;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      a[c] = ap[c] + av[c];                                                      // :477 (gravity = 0)
+      const double xn = x[c] + ((a[c] * (dt * dt)) / 2. + v[c] * dt);            // :481
+      const double vn = v[c] + (a[c] + acc[3 * (int64_t)i + c]) / 2. * dt;       // :482-486
+      pos[3 * (int64_t)i + c] = xn;
+      vel[3 * (int64_t)i + c] = vn;
+      acc[3 * (int64_t)i + c] = a[c];
+      vacc[3 * (int64_t)i + c] = av[c];
+      pacc[3 * (int64_t)i + c] = ap[c];
+      v2 += vn * vn;
+      x2 += xn * xn;
+    }
+    const double e = nan_to_num_d(E[i]) + nan_to_num_d(heat[i] * dt);            // :490
+    E[i] = e;
+    T[i] = nan_to_num_d(e * (mu[i] * m_h) / (gamma[i] * mass[i] * kB));          // :491
+    slow = (v2 < 80000.0 * 80000.0);                                             // :493
+    distsq[i] = slow ? x2 : INFINITY;
+  }
+  const int cnt = __syncthreads_count(slow);
+  if (threadIdx.x == 0 && cnt) atomicAdd(nslow, (unsigned long long)cnt);
+}
+
+// ---- A12: global length scale from the 90th percentile              code_running.py:515-524 ----
+// `sorted` holds |x|^2 of slow particles ascending (+inf for the rest); numpy's linear percentile.
+__global__ void length_scale_kernel(const double* __restrict__ sorted, const unsigned long long* nslow, double* scal,
+                                    double n_int) {
+  const unsigned long long ns = *nslow;
+  scal[SC_NSLOW] = (double)ns;
+  if (ns == 0) { scal[SC_MAXDIST] = nan(""); scal[SC_D] = nan(""); return; }
+  const double pos = 0.9 * (double)(ns - 1);
+  const unsigned long long lo = (unsigned long long)floor(pos);
+  const double t = pos - (double)lo;
+  const double a = sorted[lo];
+  const double b = sorted[lo + 1 < ns ? lo + 1 : lo];
+  const double diff = b - a;
+  double v = a + diff * t;                              // numpy _lerp
+  if (t >= 0.5) v = b - diff * (1.0 - t);
+  scal[SC_MAXDIST] = v;
+  const double V_new = v * sqrt(v);                     // max_dist ** 1.5
+  scal[SC_D] = cbrt(V_new / (double)ns / 0.9 * n_int);  // :521
+}
+
+// ---- A12: smoothing-length update                                    code_running.py:532-540 ----
+// lonely = (in-degree + nontriv - 1 < 2).  Every particle lists itself, and a particle with a
+// single entry inside the distance cut cannot be listed by anyone else (the cut is symmetric), so
+// lonely <=> nontriv <= 1 and the O(N k) in-degree histogram of :527-530 is not needed.
+__global__ void __launch_bounds__(256)
+smoothing_kernel(int n, const double* __restrict__ scal, double raise_cbrt, const double* __restrict__ rho,
+                 double* __restrict__ rho0, const int32_t* __restrict__ nontriv, const double* __restrict__ ptype,
+                 double* __restrict__ sizes) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double d = scal[SC_D];
+  const double r = rho[i];
+  const double t = ptype[i];
+  double h = sizes[i];
+  if (t == 0.0) {
+    const double ns = (exp(nan_to_num_d(-(r - rho0[i]) / (3 * r))) * 2) / 2. + ((nontriv[i] <= 1) ? 0.1 : 0.0);  // :533
+    h = ns * h;                                         // :536
+    if (h > d) h = d;                                   // :537
+  } else if (t == 2.0) {
+    h = d / raise_cbrt;                                 // :538
+  }
+  sizes[i] = h;
+  rho0[i] = r;                                          // :540
+}
+
+__global__ void __launch_bounds__(256) copy_kernel(int64_t n, const double* __restrict__ a, double* __restrict__ b) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t < n) b[t] = a[t];
+}
+
+// un-permute a (N,w) double array from sort order to the caller's order
+__global__ void __launch_bounds__(256)
+unsort_kernel(int n, int w, const uint32_t* __restrict__ id, const double* __restrict__ src, double* __restrict__ dst) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= (int64_t)n * w) return;
+  const int i = (int)(t / w), c = (int)(t % w);
+  dst[(int64_t)id[i] * w + c] = src[t];
+}
+__global__ void __launch_bounds__(256)
+unsort_list_kernel(int n, int k, const uint32_t* __restrict__ id, const int32_t* __restrict__ list, int64_t* __restrict__ dst) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= (int64_t)n * k) return;
+  const int i = (int)(t / k), s = (int)(t % k);
+  const int j = list[t];
+  dst[(int64_t)id[i] * k + s] = (j >= 0 && j < n) ? (int64_t)id[j] : (int64_t)n;
+}
+__global__ void __launch_bounds__(256)
+unsort_i32_kernel(int n, const uint32_t* __restrict__ id, const int32_t* __restrict__ src, int64_t* __restrict__ dst) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[id[i]] = src[i];
+}
+__global__ void __launch_bounds__(256)
+sort_in_kernel(int n, int w, const uint32_t* __restrict__ id, const double* __restrict__ src, double* __restrict__ dst) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= (int64_t)n * w) return;
+  const int i = (int)(t / w), c = (int)(t % w);
+  dst[t] = src[(int64_t)id[i] * w + c];
+}
+
+// ------------------------------------------------------------------------------------------------
+static int phase_crossing(sphb200_ctx* ctx, cudaStream_t st) {
+  Session& s = sess(ctx);
+  double* scal = bufp<double>(ctx->scal);
+  if (!s.has_list) SPH_FAIL("session: no neighbour list yet (call startup first)");
+  return launch_crossing_time(ctx, (int)s.n, s.k, bufp<int32_t>(ctx->list), fld(ctx, F_VEL), fld(ctx, F_H),
+                              fld(ctx, F_TYPE), s.sc.dt_0, scal + SC_CT, st);
+}
+
+static int phase_dt_clamp(sphb200_ctx* ctx, cudaStream_t st) {
+  Session& s = sess(ctx);
+  choose_dt_kernel<<<1, 1, 0, st>>>(bufp<double>(ctx->scal), s.sc);
+  clamp_kernel<<<ceil_div(3 * s.n, 256), 256, 0, st>>>(3 * s.n, 1e11 * s.sc.au, fld(ctx, F_POS), fld(ctx, F_VEL));
+  ctx->launches += 2;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// cell build + state reorder                                             (replaces nsc:542)
+static int phase_sort(sphb200_ctx* ctx, cudaStream_t st) {
+  Session& s = sess(ctx);
+  SPH_TRY(build_cells(ctx, fld(ctx, F_POS), s.n, ctx->cell_edge, st));
+  ReorderArgs a;
+  for (int f = 0; f < F_NFIELDS; ++f) { a.src[f] = fld(ctx, f, 0); a.dst[f] = fld(ctx, f, 1); }
+  a.id_src = bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]);
+  a.id_dst = bufp<uint32_t>(ctx->sbuf[SB_ID + (s.id_cur ^ 1)]);
+  a.knnh_src = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]);
+  a.knnh_dst = bufp<double>(ctx->sbuf[SB_KNNH + (s.knnh_cur ^ 1)]);
+  reorder_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, bufp<uint32_t>(ctx->perm), a);
+  ctx->launches += 1;
+  for (int f = 0; f < F_NFIELDS; ++f) s.cur[f] ^= 1;
+  s.id_cur ^= 1;
+  s.knnh_cur ^= 1;
+  s.has_list = 0;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+static int phase_knn(sphb200_ctx* ctx, cudaStream_t st) {
+  Session& s = sess(ctx);
+  SPH_TRY(devbuf_reserve(ctx->list, (size_t)s.n * s.k * sizeof(int32_t)));
+  double* knnh = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]);
+  const double* guess = nullptr;      // TODO(perf): previous k-th distance as the first trial radius
+  SPH_TRY(launch_knn(ctx, (int)s.n, s.k, s.dist, guess, bufp<int32_t>(ctx->list), nullptr, fld(ctx, F_H),
+                     bufp<int32_t>(ctx->sbuf[SB_NONTRIV]), st));
+  copy_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>(s.n, fld(ctx, F_H), knnh);
+  ctx->launches += 1;
+  s.has_list = 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+static int phase_pack(sphb200_ctx* ctx, cudaStream_t st) {
+  Session& s = sess(ctx);
+  PackIn in = {nullptr, fld(ctx, F_VEL), fld(ctx, F_MASS), fld(ctx, F_H), fld(ctx, F_TYPE), fld(ctx, F_T), fld(ctx, F_MU),
+               fld(ctx, F_GAMMA)};
+  return launch_pack(ctx, (int)s.n, in, st);
+}
+static int phase_density(sphb200_ctx* ctx, cudaStream_t st) {
+  Session& s = sess(ctx);
+  return launch_density(ctx, (int)s.n, s.k, bufp<int32_t>(ctx->list), outp(ctx, O_RHO), outp(ctx, O_DUST), outp(ctx, O_NUM), st);
+}
+static int phase_pi(sphb200_ctx* ctx, cudaStream_t st) {
+  Session& s = sess(ctx);
+  return launch_pi(ctx, (int)s.n, s.k, bufp<int32_t>(ctx->list), outp(ctx, O_RHO), st);
+}
+static int phase_force(sphb200_ctx* ctx, cudaStream_t st) {
+  Session& s = sess(ctx);
+  return launch_force(ctx, (int)s.n, s.k, bufp<int32_t>(ctx->list), outp(ctx, O_RHO), fld(ctx, F_MASS), outp(ctx, O_HACC),
+                      outp(ctx, O_VACC), outp(ctx, O_HEAT), st);
+}
+
+static int phase_integrate(sphb200_ctx* ctx, cudaStream_t st) {
+  Session& s = sess(ctx);
+  const int n = (int)s.n;
+  SPH_TRY(devbuf_reserve(ctx->tmp0, 64));
+  unsigned long long* nslow = bufp<unsigned long long>(ctx->tmp0) + 1;
+  CUDA_TRY(cudaMemsetAsync(nslow, 0, sizeof(unsigned long long), st));
+  double* dsq = bufp<double>(ctx->sbuf[SB_DISTSQ]);
+  double* dsq_sorted = bufp<double>(ctx->sbuf[SB_DISTSQ_ALT]);
+  integrate_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, bufp<double>(ctx->scal), ctx->phys.kB, ctx->m_h, fld(ctx, F_POS),
+                                                     fld(ctx, F_VEL), fld(ctx, F_ACC), fld(ctx, F_E), fld(ctx, F_T),
+                                                     fld(ctx, F_MASS), fld(ctx, F_MU), fld(ctx, F_GAMMA), fld(ctx, F_TYPE),
+                                                     outp(ctx, O_HACC), outp(ctx, O_VACC), outp(ctx, O_HEAT),
+                                                     outp(ctx, O_PACC), dsq, nslow);
+  size_t tmp = 0;
+  cub::DeviceRadixSort::SortKeys(nullptr, tmp, dsq, dsq_sorted, n, 0, 64, st);
+  SPH_TRY(devbuf_reserve(ctx->cub_tmp, tmp));
+  CUDA_TRY(cub::DeviceRadixSort::SortKeys(ctx->cub_tmp.p, tmp, dsq, dsq_sorted, n, 0, 64, st));
+  length_scale_kernel<<<1, 1, 0, st>>>(dsq_sorted, nslow, bufp<double>(ctx->scal), s.sc.n_int);
+  smoothing_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, bufp<double>(ctx->scal), cbrt(s.sc.raise_factor), outp(ctx, O_RHO),
+                                                     fld(ctx, F_RHO0), bufp<int32_t>(ctx->sbuf[SB_NONTRIV]), fld(ctx, F_TYPE),
+                                                     fld(ctx, F_H));
+  ctx->launches += 3 + 9;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" {
+
+int sphb200_session_create(sphb200_ctx* ctx, int64_t n, int k, double dist) {
+  if (!ctx) SPH_FAIL("null context");
+  if (n <= 0 || n >= (int64_t)0x7fffffff) SPH_FAIL("session: bad particle count %lld", (long long)n);
+  if (k <= 0) SPH_FAIL("session: bad k=%d", k);
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  Session& s = sess(ctx);
+  s = Session();
+  s.n = n; s.k = k; s.dist = dist;
+  s.sc.dt_0 = 60. * 60. * 24. * 365. * 250000.;
+  s.sc.max_age = 3e7 * 60. * 60. * 24. * 365.;
+  s.sc.n_int = 3000.;
+  s.sc.raise_factor = 715.;
+  s.sc.au = 149597870700.0;
+  for (int f = 0; f < F_NFIELDS; ++f) {
+    s.cur[f] = 0;
+    SPH_TRY(devbuf_reserve(ctx->sbuf[2 * f], (size_t)n * kFieldWidth[f] * sizeof(double)));
+    SPH_TRY(devbuf_reserve(ctx->sbuf[2 * f + 1], (size_t)n * kFieldWidth[f] * sizeof(double)));
+    CUDA_TRY(cudaMemset(ctx->sbuf[2 * f].p, 0, (size_t)n * kFieldWidth[f] * sizeof(double)));
+  }
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_ID], n * sizeof(uint32_t)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_ID_ALT], n * sizeof(uint32_t)));
+  for (int o = 0; o < O_NOUT; ++o) SPH_TRY(devbuf_reserve(ctx->sbuf[SB_OUT + o], (size_t)n * kOutWidth[o] * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_NONTRIV], n * sizeof(int32_t)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_DISTSQ], n * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_DISTSQ_ALT], n * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_KNNH], n * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_KNNH_ALT], n * sizeof(double)));
+  CUDA_TRY(cudaMemset(ctx->sbuf[SB_KNNH].p, 0, n * sizeof(double)));
+  iota_kernel<<<ceil_div(n, 256), 256>>>((int)n, bufp<uint32_t>(ctx->sbuf[SB_ID]));
+  CUDA_TRY(cudaMemset(ctx->scal.p, 0, SC_COUNT * sizeof(double)));
+  CUDA_TRY(cudaDeviceSynchronize());
+  return 0;
+}
+
+static int find_field(const char* name) {
+  for (int f = 0; f < F_NFIELDS; ++f) if (!strcmp(name, kFieldName[f])) return f;
+  return -1;
+}
+
+// src: device pointer, caller's particle order, `count` doubles
+int sphb200_session_upload(sphb200_ctx* ctx, const char* name, const void* src, int64_t count) {
+  if (!ctx || !name || !src) SPH_FAIL("session_upload: null argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  Session& s = sess(ctx);
+  const int f = find_field(name);
+  if (f < 0) SPH_FAIL("session_upload: unknown field '%s'", name);
+  if (count != s.n * kFieldWidth[f]) SPH_FAIL("session_upload: '%s' needs %lld values, got %lld", name,
+                                              (long long)(s.n * kFieldWidth[f]), (long long)count);
+  const uint32_t* id = bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]);
+  sort_in_kernel<<<ceil_div(count, 256), 256>>>((int)s.n, kFieldWidth[f], id, (const double*)src, fld(ctx, f));
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// dst: device pointer, caller's particle order
+int sphb200_session_download(sphb200_ctx* ctx, const char* name, void* dst, int64_t count, void* stream) {
+  if (!ctx || !name || !dst) SPH_FAIL("session_download: null argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  Session& s = sess(ctx);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const uint32_t* id = bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]);
+  const int n = (int)s.n;
+  if (!strcmp(name, "neighbor")) {
+    if (!s.has_list) SPH_FAIL("session_download: no neighbour list");
+    if (count != s.n * s.k) SPH_FAIL("session_download: neighbor needs %lld values", (long long)(s.n * s.k));
+    unsort_list_kernel<<<ceil_div(count, 256), 256, 0, st>>>(n, s.k, id, bufp<int32_t>(ctx->list), (int64_t*)dst);
+  } else if (!strcmp(name, "num_nontrivial")) {
+    if (count != s.n) SPH_FAIL("session_download: num_nontrivial needs %lld values", (long long)s.n);
+    unsort_i32_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, id, bufp<int32_t>(ctx->sbuf[SB_NONTRIV]), (int64_t*)dst);
+  } else {
+    const double* src = nullptr;
+    int w = 0;
+    const int f = find_field(name);
+    if (f >= 0) { src = fld(ctx, f); w = kFieldWidth[f]; }
+    for (int o = 0; o < O_NOUT && !src; ++o) if (!strcmp(name, kOutName[o])) { src = outp(ctx, o); w = kOutWidth[o]; }
+    if (!src) SPH_FAIL("session_download: unknown field '%s'", name);
+    if (count != s.n * w) SPH_FAIL("session_download: '%s' needs %lld values, got %lld", name, (long long)(s.n * w), (long long)count);
+    unsort_kernel<<<ceil_div(count, 256), 256, 0, st>>>(n, w, id, src, (double*)dst);
+  }
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int sphb200_session_set_scalar(sphb200_ctx* ctx, const char* name, double value) {
+  if (!ctx || !name) SPH_FAIL("null argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  Session& s = sess(ctx);
+  double* scal = bufp<double>(ctx->scal);
+  if (!strcmp(name, "dt_0")) s.sc.dt_0 = value;
+  else if (!strcmp(name, "MAX_AGE")) s.sc.max_age = value;
+  else if (!strcmp(name, "N_INT_PER_PARTICLE")) s.sc.n_int = value;
+  else if (!strcmp(name, "raise_factor")) s.sc.raise_factor = value;
+  else if (!strcmp(name, "AU")) s.sc.au = value;
+  else if (!strcmp(name, "dist")) s.dist = value;
+  else if (!strcmp(name, "use_guess")) s.use_guess = (int)value;
+  else if (!strcmp(name, "age")) CUDA_TRY(cudaMemcpy(scal + SC_AGE, &value, sizeof(double), cudaMemcpyHostToDevice));
+  else if (!strcmp(name, "d")) CUDA_TRY(cudaMemcpy(scal + SC_D, &value, sizeof(double), cudaMemcpyHostToDevice));
+  else if (!strcmp(name, "dt")) CUDA_TRY(cudaMemcpy(scal + SC_DT, &value, sizeof(double), cudaMemcpyHostToDevice));
+  else SPH_FAIL("session_set_scalar: unknown scalar '%s'", name);
+  return 0;
+}
+
+int sphb200_session_scalar(sphb200_ctx* ctx, const char* name, double* out, void* stream) {
+  if (!ctx || !name || !out) SPH_FAIL("null argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  int which = -1;
+  if (!strcmp(name, "ct")) which = SC_CT;
+  else if (!strcmp(name, "dt")) which = SC_DT;
+  else if (!strcmp(name, "d")) which = SC_D;
+  else if (!strcmp(name, "age")) which = SC_AGE;
+  else if (!strcmp(name, "max_dist")) which = SC_MAXDIST;
+  else if (!strcmp(name, "n_slow")) which = SC_NSLOW;
+  else SPH_FAIL("session_scalar: unknown scalar '%s'", name);
+  CUDA_TRY(cudaMemcpyAsync(out, bufp<double>(ctx->scal) + which, sizeof(double), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  return 0;
+}
+
+// code_running.py:171-179: first neighbour query + hydro_update; densities_0 <- densities (:183)
+int sphb200_session_startup(sphb200_ctx* ctx, void* stream) {
+  if (!ctx) SPH_FAIL("null context");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  Session& s = sess(ctx);
+  SPH_TRY(phase_sort(ctx, st));
+  SPH_TRY(phase_knn(ctx, st));
+  SPH_TRY(phase_pack(ctx, st));
+  SPH_TRY(phase_density(ctx, st));
+  SPH_TRY(phase_pi(ctx, st));
+  SPH_TRY(phase_force(ctx, st));
+  copy_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>(s.n, outp(ctx, O_RHO), fld(ctx, F_RHO0));
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int sphb200_session_step(sphb200_ctx* ctx, void* stream) {
+  if (!ctx) SPH_FAIL("null context");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  SPH_TRY(phase_crossing(ctx, st));
+  SPH_TRY(phase_dt_clamp(ctx, st));
+  SPH_TRY(phase_sort(ctx, st));
+  SPH_TRY(phase_knn(ctx, st));
+  SPH_TRY(phase_pack(ctx, st));
+  SPH_TRY(phase_density(ctx, st));
+  SPH_TRY(phase_pi(ctx, st));
+  SPH_TRY(phase_force(ctx, st));
+  SPH_TRY(phase_integrate(ctx, st));
+  return 0;
+}
+
+// run one phase of the step (per-kernel timing in bench.py / profiles)
+int sphb200_session_phase(sphb200_ctx* ctx, const char* phase, void* stream) {
+  if (!ctx || !phase) SPH_FAIL("null argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (!strcmp(phase, "crossing")) return phase_crossing(ctx, st);
+  if (!strcmp(phase, "dt_clamp")) return phase_dt_clamp(ctx, st);
+  if (!strcmp(phase, "sort")) return phase_sort(ctx, st);
+  if (!strcmp(phase, "knn")) return phase_knn(ctx, st);
+  if (!strcmp(phase, "pack")) return phase_pack(ctx, st);
+  if (!strcmp(phase, "density")) return phase_density(ctx, st);
+  if (!strcmp(phase, "pi")) return phase_pi(ctx, st);
+  if (!strcmp(phase, "force")) return phase_force(ctx, st);
+  if (!strcmp(phase, "integrate")) return phase_integrate(ctx, st);
+  SPH_FAIL("session_phase: unknown phase '%s'", phase);
+}
+
+}  // extern "C"

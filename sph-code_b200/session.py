@@ -1,0 +1,101 @@
+"""Device-resident particle state + the whole time step.
+
+The reference keeps its state as module-level numpy arrays in the driver
+(/root/reference/sph/code_running.py:121-167) and advances it inline (:217-540); there is no function
+for it.  `Session` holds the same struct-of-arrays in HBM and advances it with
+`sphb200_session_step` so nothing crosses PCIe between steps.  Field names are the driver's
+variable names.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+from . import constants as C
+
+STATE_FIELDS = {"points": 3, "velocities": 3, "total_accel": 3, "mass": 1, "sizes": 1, "T": 1, "E_internal": 1,
+                "mu_array": 1, "gamma_array": 1, "particle_type": 1, "densities_0": 1}
+RESULT_FIELDS = {"densities": 1, "num_densities": 1, "dust_densities": 1, "visc_heat": 1, "hydro_accel": 3,
+                 "visc_accel": 3, "pressure_accel": 3}
+PHASES = ("crossing", "dt_clamp", "sort", "knn", "pack", "density", "pi", "force", "integrate")
+
+
+class Session(object):
+    def __init__(self, n, k=C.N_NEIGH, dist=np.inf, device=None, dt_0=C.dt_0):
+        self.ctx = _lib.context(device)
+        self.lib = _lib.load()
+        self.n = int(n)
+        self.k = int(k)
+        self.device = torch.device("cuda", self.ctx.device)
+        _lib.check(self.lib.sphb200_session_create(self.ctx.handle, self.n, self.k, float(dist)))
+        for name, val in (("dt_0", dt_0), ("MAX_AGE", C.MAX_AGE), ("N_INT_PER_PARTICLE", C.N_INT_PER_PARTICLE),
+                          ("raise_factor", C.raise_factor), ("AU", C.AU)):
+            self.set_scalar(name, val)
+
+    # -- plumbing ---------------------------------------------------------------------------
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def set_scalar(self, name, value):
+        _lib.check(self.lib.sphb200_session_set_scalar(self.ctx.handle, name.encode(), float(value)))
+
+    def scalar(self, name):
+        out = ctypes.c_double(0.0)
+        _lib.check(self.lib.sphb200_session_scalar(self.ctx.handle, name.encode(), ctypes.byref(out), self._stream()))
+        return float(out.value)
+
+    def upload_tensor(self, name, t):
+        """t: contiguous float64 CUDA tensor in the caller's particle order."""
+        w = STATE_FIELDS[name]
+        if t.numel() != self.n * w or t.dtype != torch.float64 or not t.is_cuda:
+            raise ValueError("field %s needs a float64 CUDA tensor of %d values" % (name, self.n * w))
+        torch.cuda.current_stream(self.device).synchronize()
+        _lib.check(self.lib.sphb200_session_upload(self.ctx.handle, name.encode(), ctypes.c_void_p(t.data_ptr()),
+                                                   t.numel()))
+        torch.cuda.synchronize(self.device)
+
+    def upload(self, state):
+        """state: dict of host arrays keyed by the driver's variable names (missing keys keep zeros)."""
+        for name in STATE_FIELDS:
+            if name in state and state[name] is not None:
+                a = np.ascontiguousarray(np.asarray(state[name]), dtype=np.float64)
+                self.upload_tensor(name, torch.from_numpy(a).to(self.device))
+        if "d" in state:
+            self.set_scalar("d", state["d"])
+
+    def download_tensor(self, name):
+        if name == "neighbor":
+            out = torch.empty((self.n, self.k), dtype=torch.int64, device=self.device)
+        elif name == "num_nontrivial":
+            out = torch.empty((self.n,), dtype=torch.int64, device=self.device)
+        else:
+            w = STATE_FIELDS.get(name) or RESULT_FIELDS[name]
+            out = torch.empty((self.n, w) if w > 1 else (self.n,), dtype=torch.float64, device=self.device)
+        _lib.check(self.lib.sphb200_session_download(self.ctx.handle, name.encode(), ctypes.c_void_p(out.data_ptr()),
+                                                     out.numel(), self._stream()))
+        return out
+
+    def download(self, name):
+        return self.download_tensor(name).cpu().numpy()
+
+    # -- the path ---------------------------------------------------------------------------
+    def startup(self):
+        """code_running.py:171-179: first neighbour query + hydro_update; densities_0 <- densities."""
+        _lib.check(self.lib.sphb200_session_startup(self.ctx.handle, self._stream()))
+
+    def step(self):
+        """One pass of the while-body (code_running.py:217-540), asynchronous on the current stream."""
+        _lib.check(self.lib.sphb200_session_step(self.ctx.handle, self._stream()))
+
+    def phase(self, name):
+        _lib.check(self.lib.sphb200_session_phase(self.ctx.handle, name.encode(), self._stream()))
+
+    def check(self):
+        """Raise if the last k-NN searches did not converge."""
+        over = self.ctx.counter("knn_overflow", self._stream())
+        if over:
+            raise _lib.Sphb200Error("k-NN search did not converge for %d particles" % over)
+
+    def launches(self):
+        return self.ctx.counter("launches")
