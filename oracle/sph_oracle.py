@@ -286,8 +286,9 @@ def step(s, neighbors_fn=neighbors, hydro_fn=hydro_update):
     s = dict(s)
     points = s['points'].copy(); velocities = s['velocities'].copy()
     ptype = s['particle_type']; mass = s['mass']; mu = s['mu_array']; gam = s['gamma_array']
-    ct = crossing_time(s['neighbor'], velocities, s['sizes'], ptype)                      # :222
-    dt = dt_0 / 10 if s['age'] == 0 else max(dt_0 / 5., min(dt_0 * 2., ct))               # :223-226
+    dt0 = s.get('dt_0', dt_0)       # nsc.dt_0, a module global the caller sets (code_running.py:75)
+    ct = crossing_time(s['neighbor'], velocities, s['sizes'], ptype, dt0)                 # :222
+    dt = dt0 / 10 if s['age'] == 0 else max(dt0 / 5., min(dt0 * 2., ct))                  # :223-226
     if ct > MAX_AGE:
         dt = MAX_AGE / 100.                                                               # :228-229
     points[points > 1e11 * AU] = 1e11 * AU                                                # :233-236

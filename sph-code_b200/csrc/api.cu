@@ -87,9 +87,14 @@ int sphb200_get_counter(sphb200_ctx* ctx, const char* name, int64_t* value_host,
   CUDA_TRY(cudaSetDevice(ctx->device));
   cudaStream_t st = as_stream(stream);
   if (!strcmp(name, "launches")) { *value_host = ctx->launches; return 0; }
+  if (!strcmp(name, "grid_ncells")) { *value_host = ctx->grid.ncells; return 0; }
+  if (!strcmp(name, "grid_nx")) { *value_host = ctx->grid.nx; return 0; }
+  if (!strcmp(name, "grid_ny")) { *value_host = ctx->grid.ny; return 0; }
+  if (!strcmp(name, "grid_nz")) { *value_host = ctx->grid.nz; return 0; }
   if (!strcmp(name, "knn_overflow")) return read_flag(ctx, FL_KNN_OVERFLOW, value_host, st);
   if (!strcmp(name, "knn_rescan")) return read_flag(ctx, FL_KNN_RESCAN, value_host, st);
   if (!strcmp(name, "knn_widen")) return read_flag(ctx, FL_KNN_WIDEN, value_host, st);
+  if (!strcmp(name, "knn_nonfinite")) return read_flag(ctx, FL_KNN_NONFINITE, value_host, st);
   if (!strcmp(name, "bad_index")) return read_flag(ctx, FL_BAD_INDEX, value_host, st);
   SPH_FAIL("unknown counter '%s'", name);
 }

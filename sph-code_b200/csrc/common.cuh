@@ -106,5 +106,6 @@ enum Flag {
   FL_KNN_RESCAN = 1,     // k-NN: number of extra scans (statistics)
   FL_KNN_WIDEN = 2,      // k-NN: number of targets that needed a wider cell block
   FL_BAD_INDEX = 3,      // neighbour index outside [0, N)
+  FL_KNN_NONFINITE = 4,  // k-NN: targets with NaN/inf coordinates
   FL_COUNT = 16
 };

@@ -48,6 +48,11 @@ knn_kernel(const double4* __restrict__ r0, const uint32_t* __restrict__ keys, co
   const int cx = key % g.nx, cy = (key / g.nx) % g.ny, cz = key / (g.nx * g.ny);
   const double c3 = g.c * g.c * g.c;
 
+  if (!(isfinite(p.x) && isfinite(p.y) && isfinite(p.z))) {   // NaN/inf target: no neighbours (cKDTree raises)
+    for (int s = lane; s < k; s += G) { list[(int64_t)i * k + s] = n; if (dists) dists[(int64_t)i * k + s] = 0.0; }
+    if (lane == 0) { nontriv[i] = 0; h_out[i] = 0.0; atomicAdd(&flags[FL_KNN_NONFINITE], 1); }
+    return;
+  }
   int m = 1;
   double R2try = -1.0;
   if (h_guess) { double hg = h_guess[i]; if (hg > 0.0) { R2try = hg * hg; m = (int)(hg * g.inv_c) + 1; } }

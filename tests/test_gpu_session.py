@@ -17,16 +17,14 @@ def rel(a, b):
 
 def _run(st, nsteps):
     from sphb200.session import Session
-    s = Session(len(st["points"]), st["N_NEIGH"], st["dist"])
+    s = Session(len(st["points"]), st["N_NEIGH"], st["dist"], dt_0=st.get("dt_0", O.dt_0))
     s.upload(st)
     s.startup()
     ref = O.startup(st)
-    out = []
     for _ in range(nsteps):
         s.step()
         s.check()
         ref = O.step(ref)
-        out.append((s, ref))
         yield s, ref
 
 
@@ -51,6 +49,11 @@ def test_ten_steps_default_config(built_lib):
     """BASELINE config 1: default config at reduced N = 10^4 gas particles, 10 steps."""
     from sphb200 import ics
     st = ics.uniform_box(10000, 0)
+    # nsc.dt_0 is a caller-set global (code_running.py:75).  With the default 250 000 yr the repaired
+    # viscosity block drives 20 % of the temperatures negative in the first step and the reference's
+    # own loop dies in the second (test_default_dt0_blows_up_like_the_reference); 0.25 yr keeps the
+    # ten steps finite while still moving every quantity.
+    st["dt_0"] = O.dt_0 * 1e-6
     nstep = 0
     for s, ref in _run(st, 10):
         nstep += 1
@@ -69,8 +72,33 @@ def test_steps_with_dust(built_lib):
     """dust particles present (types 0 and 2 mixed in the neighbour rows)."""
     from sphb200 import ics
     st = ics.uniform_box(6000, 3, n_dust=30)
+    st["dt_0"] = O.dt_0 * 1e-6
     for s, ref in _run(st, 3):
         assert np.array_equal(s.download("neighbor"), ref["neighbor"])
         assert np.array_equal(s.download("num_nontrivial"), ref["num_nontrivial"])
         for name in ("points", "velocities", "sizes", "T", "densities", "dust_densities"):
             assert rel(s.download(name), ref[name]) < RTOL, name
+
+
+def test_default_dt0_blows_up_like_the_reference(built_lib):
+    """With the reference's default dt_0 the first step matches, and the second step ends with no
+    finite slow particle: the reference raises in np.percentile (code_running.py:515-518), the device
+    path reports n_slow = 0 and d = NaN instead of crashing."""
+    from sphb200 import ics
+    from sphb200.session import Session
+    st = ics.uniform_box(5000, 0)
+    s = Session(5000, st["N_NEIGH"], st["dist"])
+    s.upload(st)
+    s.startup()
+    ref = O.startup(st)
+    s.step(); s.check()
+    ref = O.step(ref)
+    assert np.array_equal(s.download("neighbor"), ref["neighbor"])
+    for name in ("points", "velocities", "E_internal", "T", "sizes"):
+        assert rel(s.download(name), ref[name]) < RTOL, name
+    assert (ref["T"] < 0).any()                       # negative temperatures after one step
+    with pytest.raises(IndexError):
+        O.step(ref)
+    s.step()
+    assert s.scalar("n_slow") == 0.0
+    assert np.isnan(s.scalar("d"))

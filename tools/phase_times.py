@@ -20,7 +20,10 @@ def main():
     t0 = time.time()
     st = ics.uniform_box(n, 1) if kind == "uniform" else ics.clustered_cloud(n, 2)
     print("ics %.1fs" % (time.time() - t0), flush=True)
-    s = Session(n, st["N_NEIGH"], st["dist"])
+    from sphb200 import constants as C
+    # dt_0 (the caller-set nsc.dt_0) scaled down so that the repaired viscosity block does not drive
+    # temperatures negative within a few steps (DESIGN.md "stability of the reference step")
+    s = Session(n, st["N_NEIGH"], st["dist"], dt_0=C.dt_0 * float(opts.pop("dt_scale", 1e-6)))
     for kopt, v in opts.items():
         s.ctx.set_option(kopt, float(v))
     s.upload(st)
