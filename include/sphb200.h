@@ -88,7 +88,7 @@ int sphb200_artificial_viscosity(sphb200_ctx* ctx, int64_t n, int k, const int64
  * "visc_accel", "pressure_accel" (N,3); "neighbor" (N,k) int64; "num_nontrivial" (N) int64.
  * upload/download take DEVICE pointers in the caller's particle order. */
 int sphb200_session_create(sphb200_ctx* ctx, int64_t n, int k, double dist);
-int sphb200_session_upload(sphb200_ctx* ctx, const char* field, const void* src, int64_t count);
+int sphb200_session_upload(sphb200_ctx* ctx, const char* field, const void* src, int64_t count, void* stream);
 int sphb200_session_download(sphb200_ctx* ctx, const char* field, void* dst, int64_t count, void* stream);
 /* run parameters: "dt_0", "MAX_AGE", "N_INT_PER_PARTICLE", "raise_factor", "AU", "dist", "age", "d", "dt" */
 int sphb200_session_set_scalar(sphb200_ctx* ctx, const char* name, double value);

@@ -123,7 +123,7 @@ def _hydro_block(rows, neighbor, pts_2, mas_2, vels_2, sizes_2, temp_2, f_un_2, 
 
 
 def hydro_update(neighbor, points, mass, sizes, f_un, particle_type, T, mu_array, gamma_array, velocities,
-                 chunk=20000, species=True):
+                 chunk=20000, species=True, threads=1):
     """Same signature and return tuple as navier_stokes_cleaned.py:556-671, evaluated on row blocks so
     the (3,N,k)/(15,N,k) temporaries stay small.  Every output row depends only on its own neighbour
     row plus gathered per-particle arrays, so chunking does not change results."""
@@ -154,25 +154,41 @@ def hydro_update(neighbor, points, mass, sizes, f_un, particle_type, T, mu_array
     pgrad = np.zeros((3, n)); fun = np.zeros((S, n))
     args = (neighbor, pts_2, mas_2, vels_2, sizes_2, temp_2)
     rest = (sizes, mass, T, mu_array, gamma_array, particle_type)
-    for a in range(0, n, chunk):
-        rows = slice(a, min(n, a + chunk))
+    blocks = [slice(a, min(n, a + chunk)) for a in range(0, n, chunk)]
+
+    def run(fn):
+        """evaluate fn(rows) over the row blocks; `threads` > 1 only changes who runs a block
+        (numpy releases the GIL in its large array ops), never a result."""
+        if threads > 1 and len(blocks) > 1:
+            from concurrent.futures import ThreadPoolExecutor
+            with ThreadPoolExecutor(max_workers=threads) as ex:
+                list(ex.map(fn, blocks))
+        else:
+            for rows in blocks:
+                fn(rows)
+
+    def p_dens(rows):
         o = _hydro_block(rows, *args, f_un_2, *rest, None, None, 'dens')
         density[rows] = o['density']; dust[rows] = o['dust']; num[rows] = o['num']; pgrad[:, rows] = o['pgrad']
         if S:
             fun[:, rows] = o['fun']
+    run(p_dens)
     with np.errstate(divide='ignore', invalid='ignore'):
         hydro_accel = (pgrad / density).T                                                # :619,631
     dens_2 = np.append(density, 0)                                                       # :639
     Pi = np.zeros(n)
-    with np.errstate(divide='ignore', invalid='ignore'):
-        for a in range(0, n, chunk):
-            rows = slice(a, min(n, a + chunk))
+    visc_accel = np.zeros((n, 3)); visc_heat = np.zeros(n)
+
+    def p_pi(rows):
+        with np.errstate(divide='ignore', invalid='ignore'):
             Pi[rows] = _hydro_block(rows, *args, None, *rest, dens_2, None, 'pi')['Pi']
-        visc_accel = np.zeros((n, 3)); visc_heat = np.zeros(n)
-        for a in range(0, n, chunk):
-            rows = slice(a, min(n, a + chunk))
+
+    def p_visc(rows):
+        with np.errstate(divide='ignore', invalid='ignore'):
             o = _hydro_block(rows, *args, None, *rest, dens_2, Pi, 'visc')
-            visc_accel[rows] = o['visc_accel'].T; visc_heat[rows] = o['visc_heat']
+        visc_accel[rows] = o['visc_accel'].T; visc_heat[rows] = o['visc_heat']
+    run(p_pi)
+    run(p_visc)
     return hydro_accel, visc_accel, visc_heat, density, num, fun, dust
 
 
@@ -281,13 +297,18 @@ def startup(state, neighbors_fn=neighbors, hydro_fn=hydro_update):
     return s
 
 
-def step(s, neighbors_fn=neighbors, hydro_fn=hydro_update):
-    """One pass of the `while` body; returns a new state dict (inputs are not mutated)."""
+def step(s, neighbors_fn=neighbors, hydro_fn=hydro_update, crossing_fn=None):
+    """One pass of the `while` body; returns a new state dict (inputs are not mutated).
+    The three hooks let tests/golden/make_golden.py drive the same harness with the reference's own
+    (extracted) functions."""
     s = dict(s)
     points = s['points'].copy(); velocities = s['velocities'].copy()
     ptype = s['particle_type']; mass = s['mass']; mu = s['mu_array']; gam = s['gamma_array']
     dt0 = s.get('dt_0', dt_0)       # nsc.dt_0, a module global the caller sets (code_running.py:75)
-    ct = crossing_time(s['neighbor'], velocities, s['sizes'], ptype, dt0)                 # :222
+    if crossing_fn is None:
+        ct = crossing_time(s['neighbor'], velocities, s['sizes'], ptype, dt0)             # :222
+    else:
+        ct = crossing_fn(s['neighbor'], velocities, s['sizes'], ptype)
     dt = dt0 / 10 if s['age'] == 0 else max(dt0 / 5., min(dt0 * 2., ct))                  # :223-226
     if ct > MAX_AGE:
         dt = MAX_AGE / 100.                                                               # :228-229

@@ -379,16 +379,17 @@ static int find_field(const char* name) {
 }
 
 // src: device pointer, caller's particle order, `count` doubles
-int sphb200_session_upload(sphb200_ctx* ctx, const char* name, const void* src, int64_t count) {
+int sphb200_session_upload(sphb200_ctx* ctx, const char* name, const void* src, int64_t count, void* stream) {
   if (!ctx || !name || !src) SPH_FAIL("session_upload: null argument");
   CUDA_TRY(cudaSetDevice(ctx->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   Session& s = sess(ctx);
   const int f = find_field(name);
   if (f < 0) SPH_FAIL("session_upload: unknown field '%s'", name);
   if (count != s.n * kFieldWidth[f]) SPH_FAIL("session_upload: '%s' needs %lld values, got %lld", name,
                                               (long long)(s.n * kFieldWidth[f]), (long long)count);
   const uint32_t* id = bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]);
-  sort_in_kernel<<<ceil_div(count, 256), 256>>>((int)s.n, kFieldWidth[f], id, (const double*)src, fld(ctx, f));
+  sort_in_kernel<<<ceil_div(count, 256), 256, 0, st>>>((int)s.n, kFieldWidth[f], id, (const double*)src, fld(ctx, f));
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;

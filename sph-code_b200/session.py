@@ -50,10 +50,8 @@ class Session(object):
         w = STATE_FIELDS[name]
         if t.numel() != self.n * w or t.dtype != torch.float64 or not t.is_cuda:
             raise ValueError("field %s needs a float64 CUDA tensor of %d values" % (name, self.n * w))
-        torch.cuda.current_stream(self.device).synchronize()
         _lib.check(self.lib.sphb200_session_upload(self.ctx.handle, name.encode(), ctypes.c_void_p(t.data_ptr()),
-                                                   t.numel()))
-        torch.cuda.synchronize(self.device)
+                                                   t.numel(), self._stream()))
 
     def upload(self, state):
         """state: dict of host arrays keyed by the driver's variable names (missing keys keep zeros)."""
@@ -99,3 +97,35 @@ class Session(object):
 
     def launches(self):
         return self.ctx.counter("launches")
+
+    def phases(self):
+        return PHASES
+
+    def n_owned(self):
+        return self.n
+
+    # -- host-resident state (the call a user of the reference makes: numpy arrays in, arrays out) --
+    def make_host_state(self, upload_fields, download_fields):
+        """Pinned host buffers holding the current state (inputs) and room for the results."""
+        hs = {"in": {}, "out": {}, "upload": tuple(upload_fields), "download": tuple(download_fields)}
+        for f in upload_fields:
+            hs["in"][f] = self.download_tensor(f).cpu().pin_memory()
+        for f in download_fields:
+            w = STATE_FIELDS.get(f) or RESULT_FIELDS[f]
+            hs["out"][f] = torch.empty((self.n, w) if w > 1 else (self.n,), dtype=torch.float64).pin_memory()
+        hs["h2d_bytes"] = sum(t.numel() * 8 for t in hs["in"].values())
+        hs["d2h_bytes"] = sum(t.numel() * 8 for t in hs["out"].values())
+        return hs
+
+    def step_host(self, hs):
+        """One time step of a host-resident state: upload every input field from pinned memory, step,
+        download the advanced fields into pinned memory, and make them the next step's inputs."""
+        for f in hs["upload"]:
+            self.upload_tensor(f, hs["in"][f].to(self.device, non_blocking=True))
+        self.step()
+        for f in hs["download"]:
+            hs["out"][f].copy_(self.download_tensor(f), non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()      # the caller reads the result
+        for f in hs["download"]:
+            if f in hs["in"]:
+                hs["in"][f], hs["out"][f] = hs["out"][f], hs["in"][f]

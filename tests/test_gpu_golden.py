@@ -1,0 +1,102 @@
+"""GPU: the CUDA path (through the drop-in module / the C ABI) against the committed outputs of the
+reference itself (tests/golden/*.npz; generated from the reference's own text by make_golden.py)."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+RTOL = 1e-10     # north_star tolerance for fp64 sums
+
+
+def rel(a, b):
+    a = np.asarray(a, dtype=float); b = np.asarray(b, dtype=float)
+    assert a.shape == b.shape, (a.shape, b.shape)
+    return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
+
+
+def test_functions_against_reference_outputs(built_lib):
+    from sphb200 import ics
+    from sphb200 import navier_stokes_cleaned as nsc
+    g = np.load(os.path.join(GOLD, "functions_n1000.npz"))
+    st = ics.uniform_box(1000, 0, n_dust=8)
+    idx, tree, dd, nontriv, sizes = nsc.neighbors(st["points"], st["dist"], 40)
+    assert np.array_equal(idx, g["idx"]) and np.array_equal(dd, g["dists"])          # bit-exact
+    assert np.array_equal(nontriv, g["nontriv"]) and np.array_equal(sizes, g["new_sizes"])
+    out = nsc.hydro_update(idx, st["points"], st["mass"], sizes, st["f_un"], st["particle_type"], st["T"],
+                           st["mu_array"], st["gamma_array"], st["velocities"])
+    for name, a in zip(("hydro_accel", "visc_accel", "visc_heat", "density", "num_density", "f_un_neighbor",
+                        "dust_density"), out):
+        assert rel(a, g["hu_" + name]) < RTOL, name
+    nsc.d = float(g["loop_d"])
+    p, m, pt = st["points"], st["mass"], st["particle_type"]
+    assert rel(nsc.density(p, m, pt, idx), g["lg_density"]) < RTOL
+    assert rel(nsc.dust_density(p, m, idx, pt, sizes), g["lg_dust_density"]) < RTOL
+    assert rel(nsc.num_dens(m, p, st["mu_array"], idx), g["lg_num_dens"]) < RTOL
+    assert rel(nsc.del_pressure(p, m, pt, idx, st["E_internal"], st["gamma_array"]), g["lg_del_pressure"]) < RTOL
+    va, vh = nsc.artificial_viscosity(idx, p, pt, sizes, m, g["lg_density"], st["velocities"], st["T"],
+                                      st["gamma_array"], st["mu_array"])
+    assert rel(va, g["lg_visc_accel"]) < RTOL and rel(vh, g["lg_visc_heat"]) < RTOL
+    from sphb200 import constants as C
+    nsc.dt_0 = C.dt_0
+    assert nsc.crossing_time(idx, st["velocities"], sizes, pt) == pytest.approx(float(g["crossing_time"]), rel=1e-13)
+
+
+def test_ten_steps_against_reference_outputs(built_lib):
+    """BASELINE config 1: N = 10^4, 10 steps, device-resident session vs the reference-driven harness."""
+    from sphb200 import ics, constants as C
+    from sphb200.session import Session
+    g = np.load(os.path.join(GOLD, "steps_n10000.npz"))
+    st = ics.uniform_box(10000, 0)
+    s = Session(10000, 40, st["dist"], dt_0=C.dt_0 * 1e-6)
+    s.upload(st)
+    s.startup()
+    assert np.array_equal(s.download("neighbor")[::50], g["startup_neighbor"])
+    assert rel(s.download("densities")[::50], g["startup_densities"]) < RTOL
+    w = np.arange(40)[None, :] + 1
+    for it in range(10):
+        s.step()
+        s.check()
+        nb = s.download("neighbor")
+        assert int(np.sum(nb * w)) == int(g["neighbor_checksum"][it]), it
+        for k in ("dt", "ct", "d", "age"):
+            assert s.scalar(k) == pytest.approx(float(g["scal_" + k][it]), rel=1e-12), (it, k)
+        if it in (0, 9):
+            assert np.array_equal(nb[::50], g["step%d_neighbor" % (it + 1)])
+            for f in ("points", "velocities", "total_accel", "E_internal", "T", "sizes", "densities", "num_densities",
+                      "pressure_accel", "visc_accel", "visc_heat"):
+                assert rel(s.download(f)[::50], g["step%d_%s" % (it + 1, f)]) < RTOL, (it, f)
+
+
+def test_full_size_properties(built_lib):
+    """BASELINE config 2 size (N = 10^6): size-independent properties of the neighbour search and sums.
+    rows sorted by distance, self first, h = last distance, k-th distance consistent with a brute-force
+    check on a random sample of targets; density positive and equal to a host sum over the returned rows."""
+    import torch
+    from sphb200 import ics
+    from sphb200 import navier_stokes_cleaned as nsc
+    n = 1000000
+    st = ics.uniform_box(n, 1)
+    idx, _, dd, nontriv, sizes = nsc.neighbors(st["points"], st["dist"], 40)
+    assert np.array_equal(idx[:, 0], np.arange(n))
+    assert np.all(np.diff(dd, axis=1) >= 0)
+    assert np.array_equal(sizes, dd[:, -1]) and np.all(nontriv == 40)
+    rs = np.random.RandomState(0)
+    p = st["points"]
+    for i in rs.randint(0, n, 40):
+        dx = p - p[i]
+        d2 = dx[:, 0] * dx[:, 0] + dx[:, 1] * dx[:, 1] + dx[:, 2] * dx[:, 2]
+        part = np.argpartition(d2, 40)[:40]
+        order = part[np.argsort(d2[part], kind="stable")]
+        assert np.array_equal(order, idx[i]), i
+        assert np.array_equal(np.sqrt(d2[order]), dd[i])
+    out = nsc.hydro_update(idx, p, st["mass"], sizes, None, st["particle_type"], st["T"], st["mu_array"],
+                           st["gamma_array"], st["velocities"])
+    rho = out[3]
+    sub = rs.randint(0, n, 2000)
+    hj = sizes[idx[sub]]
+    W = 315. / (64 * np.pi * hj ** 9) * (hj ** 2 - dd[sub] ** 2) ** 3
+    W[W < 0] = 0
+    assert rel(rho[sub], np.sum(st["mass"][idx[sub]] * W, axis=1)) < RTOL
+    assert np.all(rho > 0) and np.all(np.isfinite(out[0]))
