@@ -31,7 +31,7 @@ if ROOT not in sys.path:
 METRIC = "SPH particle-steps/sec"
 UNIT = "particle-steps/s"
 K_NEIGH = 40
-DT_SCALE = 1e-6      # nsc.dt_0 is caller-set; see DESIGN.md "stability of the reference step"
+DT_SCALE = 1e-8      # nsc.dt_0 is caller-set; see DESIGN.md "stability of the reference step"
 
 # algorithmic bytes per particle per launch (DESIGN.md "Kernels")
 ALGO_BYTES = {"sort": 216.0, "knn": 32.0, "density": 76.0, "pi": 116.0, "force": 156.0, "integrate": 248.0,

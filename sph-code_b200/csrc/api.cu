@@ -46,7 +46,7 @@ int sphb200_destroy(sphb200_ctx* ctx) {
   if (!ctx) return 0;
   cudaSetDevice(ctx->device);
   DevBuf* all[] = {&ctx->r0, &ctx->r1, &ctx->r2, &ctx->r3, &ctx->rho, &ctx->pi_, &ctx->aux, &ctx->list, &ctx->keys,
-                   &ctx->keys_alt, &ctx->perm, &ctx->perm_alt, &ctx->cell_start, &ctx->cub_tmp, &ctx->scal, &ctx->flags,
+                   &ctx->keys_alt, &ctx->perm, &ctx->perm_alt, &ctx->cell_start, &ctx->cub_tmp, &ctx->scal, &ctx->flags, &ctx->worklist, &ctx->soa,
                    &ctx->tmp0, &ctx->tmp1, &ctx->tmp2, &ctx->tmp3};
   for (DevBuf* b : all) devbuf_free(*b);
   for (DevBuf& b : ctx->sbuf) devbuf_free(b);
@@ -68,7 +68,9 @@ int sphb200_set_option(sphb200_ctx* ctx, const char* name, double value) {
     int g = (int)value;
     if (g != 8 && g != 16 && g != 32) SPH_FAIL("knn_group must be 8, 16 or 32");
     ctx->knn_group = g;
-  } else SPH_FAIL("unknown option '%s'", name);
+  } else if (!strcmp(name, "knn_fast")) ctx->knn_fast = value != 0.0;
+  else if (!strcmp(name, "knn_margin")) { if (!(value >= 0)) SPH_FAIL("knn_margin must be >= 0"); ctx->knn_margin = value; }
+  else SPH_FAIL("unknown option '%s'", name);
   return 0;
 }
 
@@ -91,6 +93,13 @@ int sphb200_get_counter(sphb200_ctx* ctx, const char* name, int64_t* value_host,
   if (!strcmp(name, "grid_nx")) { *value_host = ctx->grid.nx; return 0; }
   if (!strcmp(name, "grid_ny")) { *value_host = ctx->grid.ny; return 0; }
   if (!strcmp(name, "grid_nz")) { *value_host = ctx->grid.nz; return 0; }
+  if (!strcmp(name, "knn_worklist")) {          // length of the last search's work list (not reset)
+    int v = 0;
+    CUDA_TRY(cudaMemcpyAsync(&v, bufp<int>(ctx->flags) + FL_KNN_NWORK, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    *value_host = v;
+    return 0;
+  }
   if (!strcmp(name, "knn_overflow")) return read_flag(ctx, FL_KNN_OVERFLOW, value_host, st);
   if (!strcmp(name, "knn_rescan")) return read_flag(ctx, FL_KNN_RESCAN, value_host, st);
   if (!strcmp(name, "knn_widen")) return read_flag(ctx, FL_KNN_WIDEN, value_host, st);
@@ -111,8 +120,12 @@ int sphb200_neighbors(sphb200_ctx* ctx, const double* points, int64_t n, int k, 
   SPH_TRY(devbuf_reserve(ctx->tmp1, (size_t)n * k * sizeof(double)));
   SPH_TRY(devbuf_reserve(ctx->tmp2, (size_t)n * sizeof(double)));
   SPH_TRY(devbuf_reserve(ctx->tmp3, (size_t)n * sizeof(int32_t)));
-  SPH_TRY(launch_knn(ctx, (int)n, k, dist, nullptr, bufp<int32_t>(ctx->list), bufp<double>(ctx->tmp1),
-                     bufp<double>(ctx->tmp2), bufp<int32_t>(ctx->tmp3), st));
+  if (ctx->knn_fast && k <= knn_cell_max_k())
+    SPH_TRY(launch_knn_cell(ctx, (int)n, k, dist, nullptr, 0.0, bufp<int32_t>(ctx->list), bufp<double>(ctx->tmp1),
+                            bufp<double>(ctx->tmp2), bufp<int32_t>(ctx->tmp3), st));
+  else
+    SPH_TRY(launch_knn(ctx, (int)n, k, dist, nullptr, bufp<int32_t>(ctx->list), bufp<double>(ctx->tmp1),
+                       bufp<double>(ctx->tmp2), bufp<int32_t>(ctx->tmp3), st));
   SPH_TRY(launch_knn_unsort(ctx, bufp<int32_t>(ctx->list), bufp<double>(ctx->tmp1), bufp<double>(ctx->tmp2),
                             bufp<int32_t>(ctx->tmp3), (int)n, k, idx, dists, nontriv, new_sizes, st));
   return 0;

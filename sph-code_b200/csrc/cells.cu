@@ -72,13 +72,17 @@ __global__ void __launch_bounds__(256) cell_key_kernel(const double* __restrict_
   atomicAdd(&counts[key], 1u);
 }
 
-// sorted position records {x,y,z,0}; entry n is left to the caller
+// sorted position records {x,y,z,0} (entry n is left to the caller) and the same coordinates as
+// three arrays (the k-NN tiles are staged from these)
 __global__ void __launch_bounds__(256) gather_pos_kernel(const double* __restrict__ pts, const uint32_t* __restrict__ perm,
-                                                         int64_t n, double4* __restrict__ r0) {
+                                                         int64_t n, double4* __restrict__ r0, double* __restrict__ xs,
+                                                         double* __restrict__ ys, double* __restrict__ zs) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   int64_t p = perm[i];
-  r0[i] = make_double4(pts[3 * p], pts[3 * p + 1], pts[3 * p + 2], 0.0);
+  const double x = pts[3 * p], y = pts[3 * p + 1], z = pts[3 * p + 2];
+  r0[i] = make_double4(x, y, z, 0.0);
+  xs[i] = x; ys[i] = y; zs[i] = z;
 }
 
 int devbuf_reserve(DevBuf& b, size_t bytes) {
@@ -170,7 +174,11 @@ int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint
                                            bufp<uint32_t>(ctx->perm_alt), bufp<uint32_t>(ctx->perm), (int)n, 0, bits, st));
   CUDA_TRY(cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tmp_scan, cs, cs, g.ncells + 1, st));
   ctx->launches += 6;   // radix sort (histogram + onesweep passes) + scan, approximate
-  gather_pos_kernel<<<ceil_div(n, 256), 256, 0, st>>>(pts, bufp<uint32_t>(ctx->perm), n, bufp<double4>(ctx->r0));
+  const size_t ns = soa_stride(n);
+  SPH_TRY(devbuf_reserve(ctx->soa, 3 * ns * sizeof(double)));
+  double* xs = bufp<double>(ctx->soa);
+  gather_pos_kernel<<<ceil_div(n, 256), 256, 0, st>>>(pts, bufp<uint32_t>(ctx->perm), n, bufp<double4>(ctx->r0), xs, xs + ns,
+                                                      xs + 2 * ns);
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;

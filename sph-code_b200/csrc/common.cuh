@@ -69,13 +69,17 @@ struct sphb200_ctx {
   DevBuf rho, pi_, aux;            // per-particle doubles
   DevBuf list;                     // (N,k) int32 neighbour list in the index space of the records
   DevBuf keys, keys_alt, perm, perm_alt, cell_start, cub_tmp;
+  DevBuf worklist;                 // k-NN targets left to the general kernel
+  DevBuf soa;                      // sorted coordinates as three arrays xs|ys|zs of soa_stride(n) doubles
   DevBuf scal;                     // device scalars (doubles), see enum Scal
   DevBuf flags;                    // device ints: error / statistics counters
   DevBuf tmp0, tmp1, tmp2, tmp3;   // generic scratch
   DevBuf sbuf[48];                 // session arrays (session.cu)
   double cell_occ = 12.0;          // target mean particles per cell (tunable)
   double cell_edge = 0.0;          // fixed cell edge (0 = from cell_occ)
-  int knn_group = 32;              // lanes per target in the k-NN kernel
+  int knn_group = 32;              // lanes per target in the general k-NN kernel
+  int knn_fast = 1;                // 1: cell-tiled fast path (knn_cell.cu), 0: general kernel only
+  double knn_margin = 0.02;        // trial radius = previous k-th distance * (1 + margin)
   GridSpec grid;
   int64_t launches = 0;            // kernels launched through this context (for bench "gpu_launches")
 };
@@ -85,6 +89,9 @@ void devbuf_free(DevBuf& b);
 
 template <typename T>
 static inline T* bufp(DevBuf& b) { return reinterpret_cast<T*>(b.p); }
+
+// n + 2 slots (bulk copies read up to one element past a run), rounded so each array stays 16 B aligned
+static inline size_t soa_stride(int64_t n) { return ((size_t)n + 2 + 1) & ~(size_t)1; }
 
 static inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
@@ -107,5 +114,6 @@ enum Flag {
   FL_KNN_WIDEN = 2,      // k-NN: number of targets that needed a wider cell block
   FL_BAD_INDEX = 3,      // neighbour index outside [0, N)
   FL_KNN_NONFINITE = 4,  // k-NN: targets with NaN/inf coordinates
+  FL_KNN_NWORK = 5,      // k-NN: length of the work list of the last search
   FL_COUNT = 16
 };

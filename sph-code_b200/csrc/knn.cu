@@ -31,7 +31,8 @@ __global__ void __launch_bounds__(KNN_THREADS)
 knn_kernel(const double4* __restrict__ r0, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ cell_start,
            GridSpec g, int n, int k, double dist2, int cap, const double* __restrict__ h_guess,
            int32_t* __restrict__ list, double* __restrict__ dists, double* __restrict__ h_out,
-           int32_t* __restrict__ nontriv, int* __restrict__ flags) {
+           int32_t* __restrict__ nontriv, int* __restrict__ flags, const int* __restrict__ worklist,
+           const int* __restrict__ nwork) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cg::thread_block blk = cg::this_thread_block();
   cg::thread_block_tile<G> tile = cg::tiled_partition<G>(blk);
@@ -41,8 +42,10 @@ knn_kernel(const double4* __restrict__ r0, const uint32_t* __restrict__ keys, co
   unsigned long long* keybuf = reinterpret_cast<unsigned long long*>(smem_raw) + (size_t)grp * cap;
   int32_t* idxbuf = reinterpret_cast<int32_t*>(smem_raw + (size_t)GROUPS * cap * sizeof(unsigned long long)) + (size_t)grp * cap;
 
-  const int i = blockIdx.x * GROUPS + grp;
-  if (i >= n) return;
+  // targets: all particles, or the entries of a device-side work list (grid-stride)
+  const int ntarget = worklist ? *nwork : n;
+  for (int tgt = blockIdx.x * GROUPS + grp; tgt < ntarget; tgt += gridDim.x * GROUPS) {
+  const int i = worklist ? worklist[tgt] : tgt;
   const double4 p = r0[i];
   const uint32_t key = keys[i];
   const int cx = key % g.nx, cy = (key / g.nx) % g.ny, cz = key / (g.nx * g.ny);
@@ -51,7 +54,7 @@ knn_kernel(const double4* __restrict__ r0, const uint32_t* __restrict__ keys, co
   if (!(isfinite(p.x) && isfinite(p.y) && isfinite(p.z))) {   // NaN/inf target: no neighbours (cKDTree raises)
     for (int s = lane; s < k; s += G) { list[(int64_t)i * k + s] = n; if (dists) dists[(int64_t)i * k + s] = 0.0; }
     if (lane == 0) { nontriv[i] = 0; h_out[i] = 0.0; atomicAdd(&flags[FL_KNN_NONFINITE], 1); }
-    return;
+    continue;
   }
   int m = 1;
   double R2try = -1.0;
@@ -155,6 +158,8 @@ knn_kernel(const double4* __restrict__ r0, const uint32_t* __restrict__ keys, co
     nontriv[i] = nsel;
     if (nsel == 0) h_out[i] = 0.0;
   }
+  tile.sync();
+  }  // target loop
 }
 
 int knn_cap_for(int k) {
@@ -163,8 +168,8 @@ int knn_cap_for(int k) {
   return cap;
 }
 
-int launch_knn(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, int32_t* list, double* dists,
-               double* h_out, int32_t* nontriv, cudaStream_t st) {
+static int launch_knn_impl(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, int32_t* list, double* dists,
+                           double* h_out, int32_t* nontriv, const int* worklist, const int* nwork, cudaStream_t st) {
   if (k < 1) SPH_FAIL("knn: k must be >= 1");
   const int cap = knn_cap_for(k);
   const int G = ctx->knn_group;
@@ -177,13 +182,13 @@ int launch_knn(sphb200_ctx* ctx, int n, int k, double dist, const double* h_gues
   const uint32_t* keys = bufp<uint32_t>(ctx->keys);
   const uint32_t* cs = bufp<uint32_t>(ctx->cell_start);
   int* flags = bufp<int>(ctx->flags);
-  const int blocks = ceil_div(n, groups);
+  const int blocks = worklist ? 148 * 8 : ceil_div(n, groups);
 #define KNN_LAUNCH(GG)                                                                                         \
   do {                                                                                                         \
     if (smem > 48 * 1024)                                                                                      \
       CUDA_TRY(cudaFuncSetAttribute(knn_kernel<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));  \
     knn_kernel<GG><<<blocks, KNN_THREADS, smem, st>>>(r0, keys, cs, ctx->grid, n, k, dist2, cap, h_guess, list, \
-                                                      dists, h_out, nontriv, flags);                           \
+                                                      dists, h_out, nontriv, flags, worklist, nwork);          \
   } while (0)
   if (G == 32) KNN_LAUNCH(32);
   else if (G == 16) KNN_LAUNCH(16);
@@ -193,6 +198,16 @@ int launch_knn(sphb200_ctx* ctx, int n, int k, double dist, const double* h_gues
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;
+}
+
+int launch_knn(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, int32_t* list, double* dists,
+               double* h_out, int32_t* nontriv, cudaStream_t st) {
+  return launch_knn_impl(ctx, n, k, dist, h_guess, list, dists, h_out, nontriv, nullptr, nullptr, st);
+}
+
+int launch_knn_worklist(sphb200_ctx* ctx, int n, int k, double dist, const int* worklist, const int* nwork, int32_t* list,
+                        double* dists, double* h_out, int32_t* nontriv, cudaStream_t st) {
+  return launch_knn_impl(ctx, n, k, dist, nullptr, list, dists, h_out, nontriv, worklist, nwork, st);
 }
 
 // Sorted-space rows -> the reference's return layout (original particle order, int64 indices,

@@ -218,13 +218,34 @@ unsort_kernel(int n, int w, const uint32_t* __restrict__ id, const double* __res
   const int i = (int)(t / w), c = (int)(t % w);
   dst[(int64_t)id[i] * w + c] = src[t];
 }
-__global__ void __launch_bounds__(256)
-unsort_list_kernel(int n, int k, const uint32_t* __restrict__ id, const int32_t* __restrict__ list, int64_t* __restrict__ dst) {
-  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (t >= (int64_t)n * k) return;
-  const int i = (int)(t / k), s = (int)(t % k);
-  const int j = list[t];
-  dst[(int64_t)id[i] * k + s] = (j >= 0 && j < n) ? (int64_t)id[j] : (int64_t)n;
+// un-permute the (N,k) neighbour rows, every row put into the reference's order (ascending (d^2, index), nsc:544): the fast
+// k-NN path keeps rows unordered because the sums do not need the order.  `r0` holds the positions
+// the search ran on.  Thread per row, keys recomputed on the fly (download path, not hot).
+__device__ __forceinline__ double row_key(const double4* __restrict__ r0, const double4 p, int j, int n) {
+  if (j < 0 || j >= n) return INFINITY;
+  const double4 q = r0[j];
+  const double dx = q.x - p.x, dy = q.y - p.y, dz = q.z - p.z;
+  return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+}
+__global__ void __launch_bounds__(128)
+unsort_list_sorted_kernel(int n, int k, const uint32_t* __restrict__ id, const int32_t* __restrict__ list,
+                          const double4* __restrict__ r0, int64_t* __restrict__ dst) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int32_t* row = list + (int64_t)i * k;
+  const double4 p = r0[i];
+  int64_t* out = dst + (int64_t)id[i] * k;
+  for (int s = 0; s < k; ++s) {
+    const int js = row[s];
+    const double ks = row_key(r0, p, js, n);
+    int rank = 0;
+    for (int f = 0; f < k; ++f) {
+      const int jf = row[f];
+      const double kf = row_key(r0, p, jf, n);
+      rank += (kf < ks) || (kf == ks && (jf < js || (jf == js && f < s)));
+    }
+    out[rank] = (js >= 0 && js < n) ? (int64_t)id[js] : (int64_t)n;
+  }
 }
 __global__ void __launch_bounds__(256)
 unsort_i32_kernel(int n, const uint32_t* __restrict__ id, const int32_t* __restrict__ src, int64_t* __restrict__ dst) {
@@ -281,9 +302,14 @@ static int phase_knn(sphb200_ctx* ctx, cudaStream_t st) {
   Session& s = sess(ctx);
   SPH_TRY(devbuf_reserve(ctx->list, (size_t)s.n * s.k * sizeof(int32_t)));
   double* knnh = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]);
-  const double* guess = nullptr;      // TODO(perf): previous k-th distance as the first trial radius
-  SPH_TRY(launch_knn(ctx, (int)s.n, s.k, s.dist, guess, bufp<int32_t>(ctx->list), nullptr, fld(ctx, F_H),
-                     bufp<int32_t>(ctx->sbuf[SB_NONTRIV]), st));
+  // previous k-th distance (reordered with the state) as the first trial radius; zeros before start-up
+  const double* guess = s.use_guess ? knnh : nullptr;
+  if (ctx->knn_fast && s.k <= knn_cell_max_k())
+    SPH_TRY(launch_knn_cell(ctx, (int)s.n, s.k, s.dist, guess, ctx->knn_margin, bufp<int32_t>(ctx->list), nullptr,
+                            fld(ctx, F_H), bufp<int32_t>(ctx->sbuf[SB_NONTRIV]), st));
+  else
+    SPH_TRY(launch_knn(ctx, (int)s.n, s.k, s.dist, nullptr, bufp<int32_t>(ctx->list), nullptr, fld(ctx, F_H),
+                       bufp<int32_t>(ctx->sbuf[SB_NONTRIV]), st));
   copy_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>(s.n, fld(ctx, F_H), knnh);
   ctx->launches += 1;
   s.has_list = 1;
@@ -406,7 +432,8 @@ int sphb200_session_download(sphb200_ctx* ctx, const char* name, void* dst, int6
   if (!strcmp(name, "neighbor")) {
     if (!s.has_list) SPH_FAIL("session_download: no neighbour list");
     if (count != s.n * s.k) SPH_FAIL("session_download: neighbor needs %lld values", (long long)(s.n * s.k));
-    unsort_list_kernel<<<ceil_div(count, 256), 256, 0, st>>>(n, s.k, id, bufp<int32_t>(ctx->list), (int64_t*)dst);
+    unsort_list_sorted_kernel<<<ceil_div(n, 128), 128, 0, st>>>(n, s.k, id, bufp<int32_t>(ctx->list), bufp<double4>(ctx->r0),
+                                                              (int64_t*)dst);
   } else if (!strcmp(name, "num_nontrivial")) {
     if (count != s.n) SPH_FAIL("session_download: num_nontrivial needs %lld values", (long long)s.n);
     unsort_i32_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, id, bufp<int32_t>(ctx->sbuf[SB_NONTRIV]), (int64_t*)dst);
