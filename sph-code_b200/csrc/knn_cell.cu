@@ -76,11 +76,13 @@ struct KnnCellArgs {
   int* nwork;
 };
 
-// Shared-memory tile of one chunk of the cell block's candidates.
-struct KnnTile {
-  double* X; double* Y; double* Z;   // KC_CHP each
-  int32_t* G;                        // sorted index of the entry, or -1 for alignment padding
-};
+// Shared-memory tile of one chunk of the cell block's candidates: one base address, fixed offsets
+// (X at 0, Y at KC_CHP, Z at 2 KC_CHP doubles; sorted index / -1 for alignment padding after them).
+struct KnnTile { double* T; };
+#define TILE_X(t) ((t).T)
+#define TILE_Y(t) ((t).T + KC_CHP)
+#define TILE_Z(t) ((t).T + 2 * KC_CHP)
+#define TILE_G(t) (reinterpret_cast<int32_t*>((t).T + 3 * KC_CHP))
 
 // The nine runs of the 3x3x3 block, one per lane (lanes >= nrows hold empty runs).
 struct KnnRuns {
@@ -124,9 +126,9 @@ __device__ __forceinline__ void knn_stage(const KnnCellArgs& a, const KnnRuns& r
   if (hi > lo) {
     const int src = r.ps + (lo - r.poff);
     const uint32_t bytes = (uint32_t)(hi - lo) * 8u;
-    bulk_g2s(t.X + (lo - c_begin), a.xs + src, bytes, bar);
-    bulk_g2s(t.Y + (lo - c_begin), a.ys + src, bytes, bar);
-    bulk_g2s(t.Z + (lo - c_begin), a.zs + src, bytes, bar);
+    bulk_g2s(TILE_X(t) + (lo - c_begin), a.xs + src, bytes, bar);
+    bulk_g2s(TILE_Y(t) + (lo - c_begin), a.ys + src, bytes, bar);
+    bulk_g2s(TILE_Z(t) + (lo - c_begin), a.zs + src, bytes, bar);
   }
   for (int run = 0; run < 9; ++run) {                     // index table, filled by the whole warp
     const int q_ps = __shfl_sync(0xffffffffu, r.ps, run), q_off = __shfl_sync(0xffffffffu, r.poff, run);
@@ -135,45 +137,42 @@ __device__ __forceinline__ void knn_stage(const KnnCellArgs& a, const KnnRuns& r
     const int qlo = max(q_off, c_begin), qhi = min(q_off + q_len, c_begin + c_n);
     for (int c = qlo + lane; c < qhi; c += 32) {
       const int gi = q_ps + (c - q_off);
-      t.G[c - c_begin] = (gi >= q_rs && gi < q_re) ? gi : -1;   // alignment padding is masked
+      TILE_G(t)[c - c_begin] = (gi >= q_rs && gi < q_re) ? gi : -1;   // alignment padding is masked
     }
   }
+  for (int c = c_n + lane; c < ((c_n + 31) & ~31); c += 32) TILE_X(t)[c] = nan("");   // tail of the last 32-wide group
   mbar_wait(bar, phase);
   phase ^= 1u;
   if (hi > lo) {                                          // padding never passes `d2 < R2` (NaN)
-    if (r.ps < r.rs && r.poff >= lo) t.X[r.poff - c_begin] = nan("");
+    if (r.ps < r.rs && r.poff >= lo) TILE_X(t)[r.poff - c_begin] = nan("");
     const int last = r.poff + r.plen - 1;
-    if (r.ps + r.plen > r.re && last < hi) t.X[last - c_begin] = nan("");
+    if (r.ps + r.plen > r.re && last < hi) TILE_X(t)[last - c_begin] = nan("");
   }
 }
 
 // One warp scans the staged chunk for one target: survivors (d^2 < R2try) are appended to the warp's
-// buffer in tile order.  Returns the updated survivor count (may exceed KC_CAP: overflow is counted,
-// not stored).
+// buffer in tile order.  The tile is NaN-padded to a multiple of 32, so no bounds checks.  Returns the
+// updated survivor count (may exceed KC_CAP: overflow is counted, not stored).
 __device__ __forceinline__ int knn_scan_chunk(const KnnTile& t, int c_n, double px, double py, double pz, double R2try,
                                               int count, double* keybuf, int32_t* idxbuf, int lane) {
   const unsigned lt = (1u << lane) - 1u;
+  const double* T = t.T + lane;
 #pragma unroll 2
   for (int c0 = 0; c0 < c_n; c0 += 32) {
-    const int c = c0 + lane;
-    bool ok = false;
-    double d2 = 0.0;
-    if (c < c_n) {
-      const double dx = t.X[c] - px, dy = t.Y[c] - py, dz = t.Z[c] - pz;
-      d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
-      ok = d2 < R2try;
-    }
+    const double dx = T[c0] - px, dy = T[c0 + KC_CHP] - py, dz = T[c0 + 2 * KC_CHP] - pz;
+    const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+    const bool ok = d2 < R2try;
     const unsigned b = __ballot_sync(0xffffffffu, ok);
     if (b) {
       const int pos = count + __popc(b & lt);
-      if (ok && pos < KC_CAP) { keybuf[pos] = d2; idxbuf[pos] = t.G[c]; }
+      if (ok && pos < KC_CAP) { keybuf[pos] = d2; idxbuf[pos] = reinterpret_cast<const int32_t*>(T + 3 * KC_CHP - lane)[c0 + lane]; }
       count += __popc(b);
     }
   }
   return count;
 }
 
-// Warp-wide maximum of (key, idx) pairs in lexicographic order.
+// Warp-wide maximum of (key, idx) pairs in lexicographic order (exact; used when float keys tie).
 __device__ __forceinline__ void warp_max_pair(double& k, int& i) {
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) {
@@ -183,13 +182,36 @@ __device__ __forceinline__ void warp_max_pair(double& k, int& i) {
   }
 }
 
-// The warp's buffer holds `count` (<= KC_CAP) survivors of target i; emit its row.
+// Largest (key, idx) among the two entries each lane holds (removed / absent entries have key -1).
+// Fast path: a warp REDUX on the keys rounded UP to float (monotone, so a unique float maximum is the
+// exact maximum); exact pair reduction only when floats tie.  Returns the owner's (key, idx) to all.
+__device__ __forceinline__ void knn_max_entry(double k0, int i0, double k1, int i1, double& km, int& im) {
+  const unsigned f0 = (k0 >= 0.0) ? __float_as_uint(__double2float_ru(k0)) + 1u : 0u;
+  const unsigned f1 = (k1 >= 0.0) ? __float_as_uint(__double2float_ru(k1)) + 1u : 0u;
+  const unsigned m = __reduce_max_sync(0xffffffffu, max(f0, f1));
+  const unsigned b0 = __ballot_sync(0xffffffffu, f0 == m), b1 = __ballot_sync(0xffffffffu, f1 == m);
+  if (m != 0u && __popc(b0) + __popc(b1) == 1) {
+    const int src = b0 ? (__ffs(b0) - 1) : (__ffs(b1) - 1);
+    const double kk = b0 ? k0 : k1; const int ii = b0 ? i0 : i1;
+    km = __shfl_sync(0xffffffffu, kk, src); im = __shfl_sync(0xffffffffu, ii, src);
+    return;
+  }
+  double ka = (f0 == m) ? k0 : -1.0, kb = (f1 == m) ? k1 : -1.0;
+  int ia = (f0 == m) ? i0 : -1, ib = (f1 == m) ? i1 : -1;
+  if (kb > ka || (kb == ka && ib > ia)) { ka = kb; ia = ib; }
+  warp_max_pair(ka, ia);
+  km = ka; im = ia;
+}
+
+// The warp's buffer holds `count` (<= KC_CAP) survivors of target i; write its row and return the
+// squared k-th distance (0 when the row is empty).
 template <bool SORTED>
-__device__ __forceinline__ void knn_emit(const KnnCellArgs& a, int i, int count, const double* keybuf, const int32_t* idxbuf,
-                                         int lane) {
+__device__ __forceinline__ double knn_emit(const KnnCellArgs& a, int i, int count, const double* keybuf,
+                                           const int32_t* idxbuf, int lane) {
   const int k = a.k;
   const int nsel = min(count, k);
   const int64_t row = (int64_t)i * k;
+  double km = -1.0; int im = -1;
   __syncwarp();
   if (SORTED) {
     // API layout: rank by counting; rank < k are the neighbours in ascending (d^2, index) order
@@ -202,75 +224,67 @@ __device__ __forceinline__ void knn_emit(const KnnCellArgs& a, int i, int count,
       }
       if (rank < k) {
         a.list[row + rank] = je;
-        const double dd = sqrt(ke);
-        a.dists[row + rank] = dd;
-        if (rank == nsel - 1) a.h_out[i] = dd;
+        a.dists[row + rank] = sqrt(ke);
+        if (ke > km) km = ke;
       }
     }
     for (int s = nsel + lane; s < k; s += 32) { a.list[row + s] = a.n; a.dists[row + s] = 0.0; }
+    warp_max_pair(km, im);
   } else {
     // session layout: drop the (count - k) largest, keep the rest unordered with self in column 0
     double k0 = (lane < count) ? keybuf[lane] : -1.0, k1 = (lane + 32 < count) ? keybuf[lane + 32] : -1.0;
     int i0 = (lane < count) ? idxbuf[lane] : -1, i1 = (lane + 32 < count) ? idxbuf[lane + 32] : -1;
     for (int r = count; r > nsel; --r) {
-      double km; int im;
-      if (k1 > k0 || (k1 == k0 && i1 > i0)) { km = k1; im = i1; } else { km = k0; im = i0; }
-      warp_max_pair(km, im);
-      if (k0 == km && i0 == im) { k0 = -1.0; i0 = -1; }
-      else if (k1 == km && i1 == im) { k1 = -1.0; i1 = -1; }
+      knn_max_entry(k0, i0, k1, i1, km, im);
+      if (i0 == im && k0 == km) { k0 = -1.0; i0 = -1; }
+      else if (i1 == im && k1 == km) { k1 = -1.0; i1 = -1; }
     }
-    double km = fmax(k0, k1); int im = 0;
-    warp_max_pair(km, im);
+    knn_max_entry(k0, i0, k1, i1, km, im);
     const unsigned lt = (1u << lane) - 1u;
     const unsigned b0 = __ballot_sync(0xffffffffu, i0 >= 0), b1 = __ballot_sync(0xffffffffu, i1 >= 0);
     const unsigned s0 = __ballot_sync(0xffffffffu, i0 == i), s1 = __ballot_sync(0xffffffffu, i1 == i);
     int ps = -1;                                             // position of self among the kept entries
     if (s0) ps = __popc(b0 & ((1u << (__ffs(s0) - 1)) - 1u));
     else if (s1) ps = __popc(b0) + __popc(b1 & ((1u << (__ffs(s1) - 1)) - 1u));
-    if (i0 >= 0) { const int pos = __popc(b0 & lt); a.list[row + ((pos == ps) ? 0 : (pos < ps ? pos + 1 : pos))] = i0; }
-    if (i1 >= 0) { const int pos = __popc(b0) + __popc(b1 & lt); a.list[row + ((pos == ps) ? 0 : (pos < ps ? pos + 1 : pos))] = i1; }
-    for (int s = nsel + lane; s < k; s += 32) a.list[row + s] = a.n;
-    if (lane == 0) a.h_out[i] = (nsel > 0) ? sqrt(km) : 0.0;
+    int32_t* out = a.list + row;
+    if (i0 >= 0) { const int pos = __popc(b0 & lt); out[(pos == ps) ? 0 : (pos < ps ? pos + 1 : pos)] = i0; }
+    if (i1 >= 0) { const int pos = __popc(b0) + __popc(b1 & lt); out[(pos == ps) ? 0 : (pos < ps ? pos + 1 : pos)] = i1; }
+    for (int s = nsel + lane; s < k; s += 32) out[s] = a.n;
   }
-  if (lane == 0) { a.nontriv[i] = nsel; if (SORTED && nsel == 0) a.h_out[i] = 0.0; }
   __syncwarp();
+  return (nsel > 0 && km > 0.0) ? km : 0.0;
 }
 
 struct KnnBlock {          // geometry of the 3x3x3 block of one cell (warp-uniform)
-  int x0, x1, y0, y1, z0, z1;
   bool whole;              // the block is the whole grid
   double vol;              // its volume
+  double lox, hix, loy, hiy, loz, hiz;   // block faces that are not faces of the whole grid (else -/+inf)
 };
 
-struct KnnTarget {
+struct KnnTarget {         // per-lane: lane j of a warp prepares the warp's j-th target
   double px, py, pz, R2lim, R2try;
-  bool active, unresolved, finite;
-  int count, rescans;
+  bool active;             // finite coordinates: a search is needed
 };
 
+// `own` = this lane is the only one preparing target i (it may write the row of a non-finite target).
 __device__ __forceinline__ KnnTarget knn_target_init(const KnnCellArgs& a, const KnnBlock& b, int total, int i, bool valid,
-                                                     int lane) {
+                                                     bool own) {
   KnnTarget t;
   t.px = t.py = t.pz = 0.0; t.R2lim = a.dist2; t.R2try = 0.0;
-  t.active = valid; t.unresolved = false; t.count = 0; t.rescans = -1;
+  t.active = valid;
   if (valid) { t.px = a.xs[i]; t.py = a.ys[i]; t.pz = a.zs[i]; }
   if (valid && !(isfinite(t.px) && isfinite(t.py) && isfinite(t.pz))) {      // cKDTree raises on these
     t.active = false;
-    for (int s = lane; s < a.k; s += 32) { a.list[(int64_t)i * a.k + s] = a.n; if (a.dists) a.dists[(int64_t)i * a.k + s] = 0.0; }
-    if (lane == 0) { a.nontriv[i] = 0; a.h_out[i] = 0.0; atomicAdd(&a.flags[FL_KNN_NONFINITE], 1); }
+    if (own) {
+      for (int s = 0; s < a.k; ++s) { a.list[(int64_t)i * a.k + s] = a.n; if (a.dists) a.dists[(int64_t)i * a.k + s] = 0.0; }
+      a.nontriv[i] = 0; a.h_out[i] = 0.0;
+      atomicAdd(&a.flags[FL_KNN_NONFINITE], 1);
+    }
   }
-  t.finite = t.active;
   if (t.active) {
-    const GridSpec& g = a.g;
     if (!b.whole) {
       // distance to the nearest face of the cell block that is not a face of the whole grid
-      double rs = DBL_MAX;
-      if (b.x0 > 0) rs = fmin(rs, t.px - (g.ox + (double)b.x0 * g.c));
-      if (b.x1 < g.nx - 1) rs = fmin(rs, (g.ox + (double)(b.x1 + 1) * g.c) - t.px);
-      if (b.y0 > 0) rs = fmin(rs, t.py - (g.oy + (double)b.y0 * g.c));
-      if (b.y1 < g.ny - 1) rs = fmin(rs, (g.oy + (double)(b.y1 + 1) * g.c) - t.py);
-      if (b.z0 > 0) rs = fmin(rs, t.pz - (g.oz + (double)b.z0 * g.c));
-      if (b.z1 < g.nz - 1) rs = fmin(rs, (g.oz + (double)(b.z1 + 1) * g.c) - t.pz);
+      double rs = fmin(fmin(t.px - b.lox, b.hix - t.px), fmin(fmin(t.py - b.loy, b.hiy - t.py), fmin(t.pz - b.loz, b.hiz - t.pz)));
       rs = fmax(rs, 0.0) * (1.0 - 1e-6);
       t.R2lim = fmin(a.dist2, rs * rs);
     }
@@ -286,106 +300,150 @@ __device__ __forceinline__ KnnTarget knn_target_init(const KnnCellArgs& a, const
   return t;
 }
 
-// after one complete scan of the block: accept, or correct the trial radius
-__device__ __forceinline__ void knn_target_update(const KnnCellArgs& a, const KnnBlock& b, KnnTarget& t) {
-  if (!t.active) return;
-  if (t.count > KC_CAP) {                       // too many survivors: shrink the trial radius
-    const double f = cbrt(0.75 * (double)KC_CAP / (double)t.count);
-    t.R2try *= f * f;
-  } else if (t.count >= a.k) {
-    t.active = false;
-  } else if (t.R2try < t.R2lim) {               // too few: grow towards the covered radius
-    const double f = cbrt(1.4 * (double)a.k / (double)(t.count > 0 ? t.count : 1));
-    t.R2try = fmin(t.R2lim, t.R2try * fmax(f * f, 1.1));
-  } else {
-    if (!(b.whole || t.R2lim >= a.dist2)) t.unresolved = true;    // k-th neighbour may lie outside the block
-    t.active = false;
+// After one complete scan of the block with `count` survivors: 0 = accept, 1 = rescan with the
+// corrected trial radius, 2 = the k-th neighbour may lie outside the block (general kernel).
+__device__ __forceinline__ int knn_radius_update(const KnnCellArgs& a, bool whole, int count, double R2lim,
+                                                 double& R2try) {
+  if (count > KC_CAP) {                         // too many survivors: shrink the trial radius
+    const double f = cbrt(0.75 * (double)KC_CAP / (double)count);
+    R2try *= f * f;
+    return 1;
   }
+  if (count >= a.k) return 0;
+  if (R2try < R2lim) {                          // too few: grow towards the covered radius
+    const double f = cbrt(1.4 * (double)a.k / (double)(count > 0 ? count : 1));
+    R2try = fmin(R2lim, R2try * fmax(f * f, 1.1));
+    return 1;
+  }
+  return (whole || R2lim >= a.dist2) ? 0 : 2;
 }
 
-template <bool SORTED>
-__device__ __forceinline__ void knn_target_finish(const KnnCellArgs& a, KnnTarget& t, int i, const double* keybuf,
-                                                  const int32_t* idxbuf, int lane) {
-  if (!t.finite) return;
-  if (t.active) t.unresolved = true;            // retry budget exhausted: leave it to the general kernel
-  if (lane == 0) {
-    if (t.rescans > 0) atomicAdd(&a.flags[FL_KNN_RESCAN], t.rescans);
-    if (t.unresolved) {
-      a.worklist[atomicAdd(a.nwork, 1)] = i;
-      atomicAdd(&a.flags[FL_KNN_WIDEN], 1);
-    }
-  }
-  if (!t.unresolved) knn_emit<SORTED>(a, i, min(t.count, KC_CAP), keybuf, idxbuf, lane);
-}
+// shared-memory layout of knn_cell_kernel (bytes)
+#define KC_OFF_KEY (28 * KC_CHP)                                  // after X, Y, Z (8 B) and G (4 B)
+#define KC_OFF_IDX (KC_OFF_KEY + KC_WARPS * KC_CAP * 8)
+#define KC_OFF_TGT (KC_OFF_IDX + KC_WARPS * KC_CAP * 4)           // per warp: 5 x 32 doubles + 32 ints
+#define KC_TGT_BYTES (5 * 32 * 8 + 32 * 4)
+#define KC_OFF_BLK (KC_OFF_TGT + KC_WARPS * KC_TGT_BYTES)         // KnnBlock
+#define KC_OFF_BAR (KC_OFF_BLK + 64)
+#define KC_SMEM (KC_OFF_BAR + 16)
 
 template <bool SORTED>
-__global__ void __launch_bounds__(KC_WARPS * 32, 8) knn_cell_kernel(KnnCellArgs a) {
-  __shared__ __align__(128) double sX[KC_CHP];
-  __shared__ __align__(128) double sY[KC_CHP];
-  __shared__ __align__(128) double sZ[KC_CHP];
-  __shared__ int32_t sG[KC_CHP];
-  __shared__ double sKey[KC_WARPS][KC_CAP];
-  __shared__ int32_t sIdx[KC_WARPS][KC_CAP];
-  __shared__ __align__(8) uint64_t bar;
+__global__ void __launch_bounds__(KC_WARPS * 32, 6) knn_cell_kernel(KnnCellArgs a) {
+  __shared__ __align__(128) unsigned char smem[KC_SMEM];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const GridSpec& g = a.g;
   const int cell = blockIdx.x;
   const int t_begin = (int)a.cell_start[cell], t_end = (int)a.cell_start[cell + 1];
   if (t_begin == t_end) return;
-  const int cx = cell % g.nx, cy = (cell / g.nx) % g.ny, cz = cell / (g.nx * g.ny);
-  KnnBlock b;
-  b.x0 = max(cx - 1, 0); b.x1 = min(cx + 1, g.nx - 1);
-  b.y0 = max(cy - 1, 0); b.y1 = min(cy + 1, g.ny - 1);
-  b.z0 = max(cz - 1, 0); b.z1 = min(cz + 1, g.nz - 1);
-  const int ysp = b.y1 - b.y0 + 1;
-  const int nrows = ysp * (b.z1 - b.z0 + 1);                       // <= 9
-  b.whole = (b.x0 == 0 && b.y0 == 0 && b.z0 == 0 && b.x1 == g.nx - 1 && b.y1 == g.ny - 1 && b.z1 == g.nz - 1);
-  b.vol = (double)(b.x1 - b.x0 + 1) * (double)nrows * g.c * g.c * g.c;
-  const KnnRuns runs = knn_runs(a, lane, b.x0, b.x1, b.y0, b.z0, ysp, nrows);
-  const KnnTile tile = {sX, sY, sZ, sG};
-  double* keybuf = sKey[warp];
-  int32_t* idxbuf = sIdx[warp];
-  const int nchunks = (runs.ptotal + KC_CHP - 1) / KC_CHP;
+  const KnnTile tile = {reinterpret_cast<double*>(smem)};
+  double* keybuf = reinterpret_cast<double*>(smem + KC_OFF_KEY) + warp * KC_CAP;
+  int32_t* idxbuf = reinterpret_cast<int32_t*>(smem + KC_OFF_IDX) + warp * KC_CAP;
+  double* tgt = reinterpret_cast<double*>(smem + KC_OFF_TGT + warp * KC_TGT_BYTES);   // [5][32]: px py pz R2lim R2try
+  int32_t* tres = reinterpret_cast<int32_t*>(tgt + 5 * 32);                          // [32]: result word per target
+  KnnBlock* sb = reinterpret_cast<KnnBlock*>(smem + KC_OFF_BLK);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + KC_OFF_BAR);
+  const GridSpec& g = a.g;
+  const int cxy = cell / g.nx;
+  const int cx = cell - cxy * g.nx, cz = cxy / g.ny, cy = cxy - cz * g.ny;
+  const int x0 = max(cx - 1, 0), x1 = min(cx + 1, g.nx - 1);
+  const int y0 = max(cy - 1, 0), y1 = min(cy + 1, g.ny - 1);
+  const int z0 = max(cz - 1, 0), z1 = min(cz + 1, g.nz - 1);
+  const int ysp = y1 - y0 + 1;
+  const int nrows = ysp * (z1 - z0 + 1);                       // <= 9
   if (threadIdx.x == 0) {
-    mbar_init(&bar, 1);
+    KnnBlock b;
+    b.whole = (x0 == 0 && y0 == 0 && z0 == 0 && x1 == g.nx - 1 && y1 == g.ny - 1 && z1 == g.nz - 1);
+    b.vol = (double)(x1 - x0 + 1) * (double)nrows * g.c * g.c * g.c;
+    b.lox = (x0 > 0) ? g.ox + (double)x0 * g.c : -INFINITY;  b.hix = (x1 < g.nx - 1) ? g.ox + (double)(x1 + 1) * g.c : INFINITY;
+    b.loy = (y0 > 0) ? g.oy + (double)y0 * g.c : -INFINITY;  b.hiy = (y1 < g.ny - 1) ? g.oy + (double)(y1 + 1) * g.c : INFINITY;
+    b.loz = (z0 > 0) ? g.oz + (double)z0 * g.c : -INFINITY;  b.hiz = (z1 < g.nz - 1) ? g.oz + (double)(z1 + 1) * g.c : INFINITY;
+    *sb = b;
+    mbar_init(bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  const KnnRuns runs = knn_runs(a, lane, x0, x1, y0, z0, ysp, nrows);
+  const int ptotal = runs.ptotal, total = runs.total;
+  const int nchunks = (ptotal + KC_CHP - 1) / KC_CHP;
   __syncthreads();
   uint32_t phase = 0;
 
   if (nchunks == 1) {
-    // ---- common case: the whole block fits the tile; stage once, warps take targets independently ----
-    if (warp == 0) knn_stage(a, runs, tile, &bar, phase, lane, 0, runs.ptotal);
-    __syncthreads();
-    for (int i = t_begin + warp; i < t_end; i += KC_WARPS) {
-      KnnTarget t = knn_target_init(a, b, runs.total, i, true, lane);
-      for (int attempt = 0; attempt < KC_MAX_ATTEMPT && t.active; ++attempt) {
-        t.count = 0; ++t.rescans;
-        __syncwarp();
-        t.count = knn_scan_chunk(tile, runs.ptotal, t.px, t.py, t.pz, t.R2try, 0, keybuf, idxbuf, lane);
-        knn_target_update(a, b, t);
+    // ---- common case: the whole block fits the tile.  Stage once; each warp walks its targets
+    // (t_begin + warp, + KC_WARPS, ...).  Lane j prepares the warp's j-th target (position, covered
+    // radius, trial radius) into the warp's table while the tile arrives, and afterwards finishes it
+    // (sqrt, scalar outputs), so the per-target scalar work is done 32 targets at a time. ----
+    if (warp == 0) knn_stage(a, runs, tile, bar, phase, lane, 0, ptotal);
+    const int first = t_begin + warp;
+    for (int batch = first; batch < t_end || batch == first; batch += KC_WARPS * 32) {
+      const int my_i = batch + lane * KC_WARPS;
+      {
+        const KnnTarget mine = knn_target_init(a, *sb, total, my_i, my_i < t_end, true);
+        tgt[lane] = mine.px; tgt[32 + lane] = mine.py; tgt[64 + lane] = mine.pz; tgt[96 + lane] = mine.R2lim;
+        tgt[128 + lane] = mine.active ? mine.R2try : -1.0;
+        tres[lane] = -1;                                       // -1: nothing to write (invalid / non-finite)
       }
-      knn_target_finish<SORTED>(a, t, i, keybuf, idxbuf, lane);
+      if (batch == first) __syncthreads(); else __syncwarp();  // tile staged; every warp passes here with batch == first
+      const int nb = min(32, (t_end - batch + KC_WARPS - 1) / KC_WARPS);
+      for (int j = 0; j < nb; ++j) {
+        double R2try = tgt[128 + j];
+        if (R2try < 0.0) continue;
+        const double px = tgt[j], py = tgt[32 + j], pz = tgt[64 + j], R2lim = tgt[96 + j];
+        int count = 0, verdict = 1, scans = 0;
+        for (int attempt = 0; attempt < KC_MAX_ATTEMPT && verdict == 1; ++attempt) {
+          __syncwarp();
+          count = knn_scan_chunk(tile, ptotal, px, py, pz, R2try, 0, keybuf, idxbuf, lane);
+          verdict = knn_radius_update(a, sb->whole, count, R2lim, R2try);
+          ++scans;
+        }
+        double h2 = 0.0;
+        if (verdict == 0) h2 = knn_emit<SORTED>(a, batch + j * KC_WARPS, min(count, KC_CAP), keybuf, idxbuf, lane);
+        if (lane == 0) {                                       // result word: nsel | unresolved << 8 | rescans << 16
+          tgt[j] = h2;
+          tres[j] = min(count, a.k) | ((verdict != 0) << 8) | ((scans - 1) << 16);
+        }
+      }
+      __syncwarp();
+      const int res = tres[lane];
+      if (res >= 0) {                                          // per-target scalars, one lane per target
+        if (res & 0x100) {
+          a.worklist[atomicAdd(a.nwork, 1)] = my_i;
+          atomicAdd(&a.flags[FL_KNN_WIDEN], 1);
+        } else {
+          a.h_out[my_i] = sqrt(tgt[lane]);
+          a.nontriv[my_i] = res & 0xff;
+        }
+        if (res >> 16) atomicAdd(&a.flags[FL_KNN_RESCAN], res >> 16);
+      }
+      __syncwarp();
     }
   } else {
     // ---- crowded block: rounds of KC_WARPS targets, every round walks all chunks (CTA-synchronous) ----
     for (int base = t_begin; base < t_end; base += KC_WARPS) {
       const int i = base + warp;
-      KnnTarget t = knn_target_init(a, b, runs.total, i, i < t_end, lane);
+      const KnnTarget t = knn_target_init(a, *sb, total, i, i < t_end, lane == 0);
+      double R2try = t.R2try;
+      int count = 0, verdict = t.active ? 1 : 0, scans = 0;
       for (int attempt = 0; attempt < KC_MAX_ATTEMPT; ++attempt) {
-        if (!__syncthreads_or(t.active ? 1 : 0)) break;
-        if (t.active) { t.count = 0; ++t.rescans; }
+        if (!__syncthreads_or(verdict == 1)) break;
+        if (verdict == 1) { count = 0; ++scans; }
         for (int ch = 0; ch < nchunks; ++ch) {
           const int c_begin = ch * KC_CHP;
-          const int c_n = min(KC_CHP, runs.ptotal - c_begin);
+          const int c_n = min(KC_CHP, ptotal - c_begin);
           __syncthreads();                                   // everyone is done with the previous chunk
-          if (warp == 0) knn_stage(a, runs, tile, &bar, phase, lane, c_begin, c_n);
+          if (warp == 0) knn_stage(a, runs, tile, bar, phase, lane, c_begin, c_n);
           __syncthreads();
-          if (t.active) t.count = knn_scan_chunk(tile, c_n, t.px, t.py, t.pz, t.R2try, t.count, keybuf, idxbuf, lane);
+          if (verdict == 1) count = knn_scan_chunk(tile, c_n, t.px, t.py, t.pz, R2try, count, keybuf, idxbuf, lane);
         }
-        knn_target_update(a, b, t);
+        if (verdict == 1) verdict = knn_radius_update(a, sb->whole, count, t.R2lim, R2try);
       }
-      if (i < t_end) knn_target_finish<SORTED>(a, t, i, keybuf, idxbuf, lane);
+      if (t.active) {
+        if (verdict != 0) {
+          if (lane == 0) { a.worklist[atomicAdd(a.nwork, 1)] = i; atomicAdd(&a.flags[FL_KNN_WIDEN], 1); }
+        } else {
+          const double h2 = knn_emit<SORTED>(a, i, min(count, KC_CAP), keybuf, idxbuf, lane);
+          if (lane == 0) { a.h_out[i] = sqrt(h2); a.nontriv[i] = min(count, a.k); }
+        }
+        if (lane == 0 && scans > 1) atomicAdd(&a.flags[FL_KNN_RESCAN], scans - 1);
+      }
     }
   }
 }
