@@ -75,7 +75,7 @@ struct sphb200_ctx {
   DevBuf flags;                    // device ints: error / statistics counters
   DevBuf tmp0, tmp1, tmp2, tmp3;   // generic scratch
   DevBuf sbuf[48];                 // session arrays (session.cu)
-  double cell_occ = 12.0;          // target mean particles per cell (tunable)
+  double cell_occ = 16.0;          // target mean particles per cell (tunable)
   double cell_edge = 0.0;          // fixed cell edge (0 = from cell_occ)
   int knn_group = 32;              // lanes per target in the general k-NN kernel
   int knn_fast = 1;                // 1: cell-tiled fast path (knn_cell.cu), 0: general kernel only

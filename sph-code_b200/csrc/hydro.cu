@@ -286,28 +286,39 @@ int launch_species(sphb200_ctx* ctx, int n, int k, int S, const int32_t* list, c
 // Here "self" is the row index (nsc:780 uses velocities[j]).
 __global__ void crossing_init_kernel(unsigned long long* slot) { *slot = 0xffffffffffffffffull; }
 
+// velocities (N,3) -> 32-byte records so that a neighbour costs one sector pair instead of three
+// strided 8-byte loads
+__global__ void __launch_bounds__(256) vel_pack_kernel(int n, const double* __restrict__ vel, double4* __restrict__ rec) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) rec[i] = make_double4(vel[3 * (int64_t)i], vel[3 * (int64_t)i + 1], vel[3 * (int64_t)i + 2], 0.0);
+}
+
 template <int G>
 __global__ void __launch_bounds__(HY_THREADS)
-crossing_kernel(int n, int k, const int32_t* __restrict__ list, const double* __restrict__ vel,
+crossing_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __restrict__ vrec,
                 const double* __restrict__ sizes, const double* __restrict__ ptype, unsigned long long* slot) {
+  __shared__ unsigned long long smin;
   cg::thread_block_tile<G> tile = cg::tiled_partition<G>(cg::this_thread_block());
-  const int i = blockIdx.x * (HY_THREADS / G) + tile.meta_group_rank();
-  if (i >= n) return;
+  const int i = min(blockIdx.x * (HY_THREADS / G) + (int)tile.meta_group_rank(), n - 1);   // tail groups repeat n-1
+  if (threadIdx.x == 0) smin = 0xffffffffffffffffull;
+  __syncthreads();
   const int lane = tile.thread_rank();
   const int32_t* row = list + (int64_t)i * k;
-  const double vx = vel[3 * (int64_t)i], vy = vel[3 * (int64_t)i + 1], vz = vel[3 * (int64_t)i + 2];
+  const double4 vi = vrec[i];
   double mx = 0.0;
   bool nan = false;
   for (int s = lane; s < k; s += G) {
     const int j = row[s];
     if (j < 0 || j >= n) continue;
-    const double ax = vel[3 * (int64_t)j] - vx, ay = vel[3 * (int64_t)j + 1] - vy, az = vel[3 * (int64_t)j + 2] - vz;
+    const double4 vj = vrec[j];
+    const double ax = vj.x - vi.x, ay = vj.y - vi.y, az = vj.z - vi.z;
     const double v2 = ax * ax + ay * ay + az * az;
     if (v2 != v2) nan = true;                           // np.max propagates NaN
     mx = fmax(mx, v2);
   }
   mx = cg::reduce(tile, mx, cg::greater<double>());
   nan = tile.any(nan);
+  unsigned long long u = 0xffffffffffffffffull;
   if (lane == 0 && ptype[i] == 0.0) {
     double ct = nan ? 0.0 : sizes[i] / sqrt(mx);        // nan_to_num: NaN -> 0
     if (ct != ct) ct = 0.0;                             // 0/0
@@ -316,10 +327,13 @@ crossing_kernel(int n, int k, const int32_t* __restrict__ list, const double* __
     if (ct != 0.0) {
       // ordered encoding for signed doubles
       long long b = __double_as_longlong(ct);
-      unsigned long long u = (b >= 0) ? ((unsigned long long)b | 0x8000000000000000ull) : ~(unsigned long long)b;
-      atomicMin(slot, u);
+      u = (b >= 0) ? ((unsigned long long)b | 0x8000000000000000ull) : ~(unsigned long long)b;
     }
   }
+  // one global atomic per CTA, not per particle (a single hot address serialises in L2)
+  if (u != 0xffffffffffffffffull) atomicMin(&smin, u);
+  __syncthreads();
+  if (threadIdx.x == 0 && smin != 0xffffffffffffffffull) atomicMin(slot, smin);
 }
 
 __global__ void crossing_final_kernel(const unsigned long long* slot, double dt_0, double* out) {
@@ -333,10 +347,13 @@ int launch_crossing_time(sphb200_ctx* ctx, int n, int k, const int32_t* list, co
                          const double* ptype, double dt_0, double* out_dev, cudaStream_t st) {
   SPH_TRY(devbuf_reserve(ctx->tmp0, 64));
   unsigned long long* slot = bufp<unsigned long long>(ctx->tmp0);
+  SPH_TRY(devbuf_reserve(ctx->r2, (size_t)(n + 1) * sizeof(double4)));   // scratch here; pack() rewrites it later
+  double4* vrec = bufp<double4>(ctx->r2);
   crossing_init_kernel<<<1, 1, 0, st>>>(slot);
-  crossing_kernel<HY_G><<<ceil_div(n, HY_THREADS / HY_G), HY_THREADS, 0, st>>>(n, k, list, vel, sizes, ptype, slot);
+  vel_pack_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, vel, vrec);
+  crossing_kernel<HY_G><<<ceil_div(n, HY_THREADS / HY_G), HY_THREADS, 0, st>>>(n, k, list, vrec, sizes, ptype, slot);
   crossing_final_kernel<<<1, 1, 0, st>>>(slot, dt_0, out_dev);
-  ctx->launches += 3;
+  ctx->launches += 4;
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
