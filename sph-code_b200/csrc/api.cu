@@ -171,7 +171,7 @@ int sphb200_crossing_time(sphb200_ctx* ctx, int64_t n, int k, const int64_t* nei
   cudaStream_t st = as_stream(stream);
   SPH_TRY(prep_list(ctx, neighbor, n, k, st));
   double* out = bufp<double>(ctx->scal) + SC_CT;
-  SPH_TRY(launch_crossing_time(ctx, (int)n, k, bufp<int32_t>(ctx->list), velocities, sizes, particle_type, dt_0, out, st));
+  SPH_TRY(launch_crossing_time(ctx, (int)n, k, bufp<int32_t>(ctx->list), velocities, sizes, particle_type, dt_0, out, nullptr, (int)n, st));
   CUDA_TRY(cudaMemcpyAsync(result_host, out, sizeof(double), cudaMemcpyDeviceToHost, st));
   CUDA_TRY(cudaStreamSynchronize(st));
   return 0;

@@ -165,6 +165,22 @@ pi_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __restr
   }
 }
 
+// r3[i].b = 6 c6_i m_i Pi_i [gas_i] from the current Pi array (after ghosts' Pi were overwritten)
+__global__ void __launch_bounds__(256)
+repack_pi_kernel(int n, const double4* __restrict__ r1, const double* __restrict__ Pi, rec2* __restrict__ r3) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double4 w = r1[i];
+  r3[i].b = (6.0 * w.x) * (w.y * Pi[i]);
+}
+
+int launch_repack_pi(sphb200_ctx* ctx, int n, cudaStream_t st) {
+  repack_pi_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, bufp<double4>(ctx->r1), bufp<double>(ctx->pi_), bufp<rec2>(ctx->r3));
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
 int launch_pi(sphb200_ctx* ctx, int n, int k, const int32_t* list, const double* rho, cudaStream_t st) {
   SPH_TRY(devbuf_reserve(ctx->pi_, (size_t)(n + 1) * sizeof(double)));
   pi_kernel<HY_G><<<ceil_div(n, HY_THREADS / HY_G), HY_THREADS, 0, st>>>(
@@ -296,7 +312,8 @@ __global__ void __launch_bounds__(256) vel_pack_kernel(int n, const double* __re
 template <int G>
 __global__ void __launch_bounds__(HY_THREADS)
 crossing_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __restrict__ vrec,
-                const double* __restrict__ sizes, const double* __restrict__ ptype, unsigned long long* slot) {
+                const double* __restrict__ sizes, const double* __restrict__ ptype, const uint32_t* __restrict__ id,
+                int n_owned, unsigned long long* slot) {
   __shared__ unsigned long long smin;
   cg::thread_block_tile<G> tile = cg::tiled_partition<G>(cg::this_thread_block());
   const int i = min(blockIdx.x * (HY_THREADS / G) + (int)tile.meta_group_rank(), n - 1);   // tail groups repeat n-1
@@ -319,7 +336,8 @@ crossing_kernel(int n, int k, const int32_t* __restrict__ list, const double4* _
   mx = cg::reduce(tile, mx, cg::greater<double>());
   nan = tile.any(nan);
   unsigned long long u = 0xffffffffffffffffull;
-  if (lane == 0 && ptype[i] == 0.0) {
+  // ghost particles of a slab decomposition (caller index >= n_owned) belong to another rank's minimum
+  if (lane == 0 && ptype[i] == 0.0 && (!id || (int)id[i] < n_owned)) {
     double ct = nan ? 0.0 : sizes[i] / sqrt(mx);        // nan_to_num: NaN -> 0
     if (ct != ct) ct = 0.0;                             // 0/0
     if (ct > DBL_MAX) ct = DBL_MAX;                     // nan_to_num: +inf -> largest finite
@@ -344,14 +362,14 @@ __global__ void crossing_final_kernel(const unsigned long long* slot, double dt_
 }
 
 int launch_crossing_time(sphb200_ctx* ctx, int n, int k, const int32_t* list, const double* vel, const double* sizes,
-                         const double* ptype, double dt_0, double* out_dev, cudaStream_t st) {
+                         const double* ptype, double dt_0, double* out_dev, const uint32_t* id, int n_owned, cudaStream_t st) {
   SPH_TRY(devbuf_reserve(ctx->tmp0, 64));
   unsigned long long* slot = bufp<unsigned long long>(ctx->tmp0);
   SPH_TRY(devbuf_reserve(ctx->r2, (size_t)(n + 1) * sizeof(double4)));   // scratch here; pack() rewrites it later
   double4* vrec = bufp<double4>(ctx->r2);
   crossing_init_kernel<<<1, 1, 0, st>>>(slot);
   vel_pack_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, vel, vrec);
-  crossing_kernel<HY_G><<<ceil_div(n, HY_THREADS / HY_G), HY_THREADS, 0, st>>>(n, k, list, vrec, sizes, ptype, slot);
+  crossing_kernel<HY_G><<<ceil_div(n, HY_THREADS / HY_G), HY_THREADS, 0, st>>>(n, k, list, vrec, sizes, ptype, id, n_owned, slot);
   crossing_final_kernel<<<1, 1, 0, st>>>(slot, dt_0, out_dev);
   ctx->launches += 4;
   CUDA_TRY(cudaGetLastError());

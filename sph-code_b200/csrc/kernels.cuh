@@ -35,12 +35,13 @@ int launch_convert_list(sphb200_ctx* ctx, const int64_t* nb, int n, int k, int32
 int launch_density(sphb200_ctx* ctx, int n, int k, const int32_t* list, double* rho, double* dust, double* num,
                    cudaStream_t st);
 int launch_pi(sphb200_ctx* ctx, int n, int k, const int32_t* list, const double* rho, cudaStream_t st);
+int launch_repack_pi(sphb200_ctx* ctx, int n, cudaStream_t st);
 int launch_force(sphb200_ctx* ctx, int n, int k, const int32_t* list, const double* rho, const double* mass,
                  double* hydro_accel, double* visc_accel, double* visc_heat, cudaStream_t st);
 int launch_species(sphb200_ctx* ctx, int n, int k, int S, const int32_t* list, const double* f_un, double* out,
                    cudaStream_t st);
 int launch_crossing_time(sphb200_ctx* ctx, int n, int k, const int32_t* list, const double* vel, const double* sizes,
-                         const double* ptype, double dt_0, double* out_dev, cudaStream_t st);
+                         const double* ptype, double dt_0, double* out_dev, const uint32_t* id, int n_owned, cudaStream_t st);
 
 // loopgen.cu  (loop generation, nsc:673-816)
 struct LoopIn {

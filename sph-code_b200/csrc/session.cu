@@ -40,6 +40,7 @@ struct Session {
   int knnh_cur = 0;
   int has_list = 0;
   int use_guess = 1;
+  int64_t n_owned = -1;      // slab decomposition: caller indices >= n_owned are ghosts (-1: none)
   SessionScalars sc;
 };
 static Session g_sess[16];   // one per device
@@ -266,7 +267,8 @@ static int phase_crossing(sphb200_ctx* ctx, cudaStream_t st) {
   double* scal = bufp<double>(ctx->scal);
   if (!s.has_list) SPH_FAIL("session: no neighbour list yet (call startup first)");
   return launch_crossing_time(ctx, (int)s.n, s.k, bufp<int32_t>(ctx->list), fld(ctx, F_VEL), fld(ctx, F_H),
-                              fld(ctx, F_TYPE), s.sc.dt_0, scal + SC_CT, st);
+                              fld(ctx, F_TYPE), s.sc.dt_0, scal + SC_CT,
+                              s.n_owned >= 0 ? bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]) : nullptr, (int)s.n_owned, st);
 }
 
 static int phase_dt_clamp(sphb200_ctx* ctx, cudaStream_t st) {
@@ -337,30 +339,69 @@ static int phase_force(sphb200_ctx* ctx, cudaStream_t st) {
                       outp(ctx, O_VACC), outp(ctx, O_HEAT), st);
 }
 
-static int phase_integrate(sphb200_ctx* ctx, cudaStream_t st) {
+// A11: kick-drift + heating; also |x|^2 of the slow particles for A12
+static int phase_kick(sphb200_ctx* ctx, cudaStream_t st) {
   Session& s = sess(ctx);
   const int n = (int)s.n;
   SPH_TRY(devbuf_reserve(ctx->tmp0, 64));
   unsigned long long* nslow = bufp<unsigned long long>(ctx->tmp0) + 1;
   CUDA_TRY(cudaMemsetAsync(nslow, 0, sizeof(unsigned long long), st));
-  double* dsq = bufp<double>(ctx->sbuf[SB_DISTSQ]);
-  double* dsq_sorted = bufp<double>(ctx->sbuf[SB_DISTSQ_ALT]);
   integrate_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, bufp<double>(ctx->scal), ctx->phys.kB, ctx->m_h, fld(ctx, F_POS),
                                                      fld(ctx, F_VEL), fld(ctx, F_ACC), fld(ctx, F_E), fld(ctx, F_T),
                                                      fld(ctx, F_MASS), fld(ctx, F_MU), fld(ctx, F_GAMMA), fld(ctx, F_TYPE),
                                                      outp(ctx, O_HACC), outp(ctx, O_VACC), outp(ctx, O_HEAT),
-                                                     outp(ctx, O_PACC), dsq, nslow);
+                                                     outp(ctx, O_PACC), bufp<double>(ctx->sbuf[SB_DISTSQ]), nslow);
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// A12: global length scale d from the 90th percentile of |x|^2 (single-GPU form; the slab-decomposed
+// driver computes d across ranks and sets the scalar instead)
+static int phase_length(sphb200_ctx* ctx, cudaStream_t st) {
+  Session& s = sess(ctx);
+  const int n = (int)s.n;
+  unsigned long long* nslow = bufp<unsigned long long>(ctx->tmp0) + 1;
+  double* dsq = bufp<double>(ctx->sbuf[SB_DISTSQ]);
+  double* dsq_sorted = bufp<double>(ctx->sbuf[SB_DISTSQ_ALT]);
   size_t tmp = 0;
   cub::DeviceRadixSort::SortKeys(nullptr, tmp, dsq, dsq_sorted, n, 0, 64, st);
   SPH_TRY(devbuf_reserve(ctx->cub_tmp, tmp));
   CUDA_TRY(cub::DeviceRadixSort::SortKeys(ctx->cub_tmp.p, tmp, dsq, dsq_sorted, n, 0, 64, st));
   length_scale_kernel<<<1, 1, 0, st>>>(dsq_sorted, nslow, bufp<double>(ctx->scal), s.sc.n_int);
+  ctx->launches += 1 + 9;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// A12: smoothing-length update with the current d
+static int phase_smooth(sphb200_ctx* ctx, cudaStream_t st) {
+  Session& s = sess(ctx);
+  const int n = (int)s.n;
   smoothing_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, bufp<double>(ctx->scal), cbrt(s.sc.raise_factor), outp(ctx, O_RHO),
                                                      fld(ctx, F_RHO0), bufp<int32_t>(ctx->sbuf[SB_NONTRIV]), fld(ctx, F_TYPE),
                                                      fld(ctx, F_H));
-  ctx->launches += 3 + 9;
+  ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;
+}
+
+static int phase_integrate(sphb200_ctx* ctx, cudaStream_t st) {
+  SPH_TRY(phase_kick(ctx, st));
+  SPH_TRY(phase_length(ctx, st));
+  return phase_smooth(ctx, st);
+}
+
+// Arrays that are not driver state but that the slab-decomposed driver must read or overwrite for
+// ghost particles between the passes: the owner-computed density and viscosity Pi of a ghost
+// (nsc:646,651 read the NEIGHBOUR's rho and Pi), the k-NN trial radius, |x|^2 of the slow particles.
+static double* aux_field(sphb200_ctx* ctx, const char* name, bool for_upload) {
+  Session& s = sess(ctx);
+  if (!strcmp(name, "densities")) return outp(ctx, O_RHO);
+  if (!strcmp(name, "knn_h")) return bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]);
+  if (!strcmp(name, "visc_pi")) return (ctx->pi_.bytes >= (size_t)s.n * sizeof(double)) ? bufp<double>(ctx->pi_) : nullptr;
+  if (!for_upload && !strcmp(name, "dist_sq")) return bufp<double>(ctx->sbuf[SB_DISTSQ]);
+  return nullptr;
 }
 
 extern "C" {
@@ -411,12 +452,14 @@ int sphb200_session_upload(sphb200_ctx* ctx, const char* name, const void* src, 
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   Session& s = sess(ctx);
   const int f = find_field(name);
-  if (f < 0) SPH_FAIL("session_upload: unknown field '%s'", name);
-  if (count != s.n * kFieldWidth[f]) SPH_FAIL("session_upload: '%s' needs %lld values, got %lld", name,
-                                              (long long)(s.n * kFieldWidth[f]), (long long)count);
+  double* dstp = (f >= 0) ? fld(ctx, f) : aux_field(ctx, name, true);
+  const int w = (f >= 0) ? kFieldWidth[f] : 1;
+  if (!dstp) SPH_FAIL("session_upload: unknown field '%s'", name);
+  if (count != s.n * w) SPH_FAIL("session_upload: '%s' needs %lld values, got %lld", name, (long long)(s.n * w), (long long)count);
   const uint32_t* id = bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]);
-  sort_in_kernel<<<ceil_div(count, 256), 256, 0, st>>>((int)s.n, kFieldWidth[f], id, (const double*)src, fld(ctx, f));
+  sort_in_kernel<<<ceil_div(count, 256), 256, 0, st>>>((int)s.n, w, id, (const double*)src, dstp);
   ctx->launches += 1;
+  if (!strcmp(name, "visc_pi")) SPH_TRY(launch_repack_pi(ctx, (int)s.n, st));   // force-pass coefficients follow Pi
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -443,6 +486,7 @@ int sphb200_session_download(sphb200_ctx* ctx, const char* name, void* dst, int6
     const int f = find_field(name);
     if (f >= 0) { src = fld(ctx, f); w = kFieldWidth[f]; }
     for (int o = 0; o < O_NOUT && !src; ++o) if (!strcmp(name, kOutName[o])) { src = outp(ctx, o); w = kOutWidth[o]; }
+    if (!src) { src = aux_field(ctx, name, false); w = 1; }
     if (!src) SPH_FAIL("session_download: unknown field '%s'", name);
     if (count != s.n * w) SPH_FAIL("session_download: '%s' needs %lld values, got %lld", name, (long long)(s.n * w), (long long)count);
     unsort_kernel<<<ceil_div(count, 256), 256, 0, st>>>(n, w, id, src, (double*)dst);
@@ -464,9 +508,11 @@ int sphb200_session_set_scalar(sphb200_ctx* ctx, const char* name, double value)
   else if (!strcmp(name, "AU")) s.sc.au = value;
   else if (!strcmp(name, "dist")) s.dist = value;
   else if (!strcmp(name, "use_guess")) s.use_guess = (int)value;
+  else if (!strcmp(name, "n_owned")) s.n_owned = (int64_t)value;
   else if (!strcmp(name, "age")) CUDA_TRY(cudaMemcpy(scal + SC_AGE, &value, sizeof(double), cudaMemcpyHostToDevice));
   else if (!strcmp(name, "d")) CUDA_TRY(cudaMemcpy(scal + SC_D, &value, sizeof(double), cudaMemcpyHostToDevice));
   else if (!strcmp(name, "dt")) CUDA_TRY(cudaMemcpy(scal + SC_DT, &value, sizeof(double), cudaMemcpyHostToDevice));
+  else if (!strcmp(name, "ct")) CUDA_TRY(cudaMemcpy(scal + SC_CT, &value, sizeof(double), cudaMemcpyHostToDevice));
   else SPH_FAIL("session_set_scalar: unknown scalar '%s'", name);
   return 0;
 }
@@ -536,6 +582,16 @@ int sphb200_session_phase(sphb200_ctx* ctx, const char* phase, void* stream) {
   if (!strcmp(phase, "pi")) return phase_pi(ctx, st);
   if (!strcmp(phase, "force")) return phase_force(ctx, st);
   if (!strcmp(phase, "integrate")) return phase_integrate(ctx, st);
+  if (!strcmp(phase, "kick")) return phase_kick(ctx, st);
+  if (!strcmp(phase, "length")) return phase_length(ctx, st);
+  if (!strcmp(phase, "smooth")) return phase_smooth(ctx, st);
+  if (!strcmp(phase, "rho0")) {               // densities_0 <- densities (end of start-up, code_running.py:183)
+    Session& s = sess(ctx);
+    copy_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>(s.n, outp(ctx, O_RHO), fld(ctx, F_RHO0));
+    ctx->launches += 1;
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+  }
   SPH_FAIL("session_phase: unknown phase '%s'", phase);
 }
 

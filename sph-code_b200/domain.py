@@ -1,0 +1,431 @@
+"""Slab domain decomposition of the particle time-step over 1..8 GPUs.
+
+The reference has no distributed path at all: its SLURM script launches ten independent replicas
+(/root/reference/sph/code_script_3.sl:19).  Here ONE box is cut into slabs along x, one process per
+GPU (torch.distributed: NCCL on GPUs, gloo in the CPU tests), and every step exchanges what the
+reference's formulas need from the other side of a slab face:
+
+  * particles that crossed a face migrate to their new owner;
+  * particles within the halo width `w` of a rank's slab are sent to it as GHOSTS (full state rows);
+    w = 1.25 x the largest smoothing length, and after the search every owned particle is checked to
+    have its k-th neighbour inside the region the ghosts cover (otherwise w doubles and the step's
+    exchange is redone), so owned particles get exactly the neighbour rows of the single-GPU run;
+  * the kernel weights use the NEIGHBOUR's smoothing length, density and viscosity Pi
+    (navier_stokes_cleaned.py:588, 646, 651), which only the owner can compute: after the k-NN, the
+    density pass and the Pi pass the owners' values overwrite the ghosts' (three 8-byte fields);
+  * the crossing time is reduced with all_reduce(MIN) (nsc:776-786 is a global minimum) and the 90th
+    percentile of |x|^2 behind the global length scale d (code_running.py:515-521) is found exactly by
+    a distributed radix select over all_reduce(SUM)'d counts.
+
+`SlabExchange` and `distributed_percentile` are pure torch + torch.distributed and run on CPU tensors
+(tests/test_domain_gloo.py, world_size 2); `DistributedSession` drives the CUDA phases of
+libsphb200 (include/sphb200.h: sphb200_session_*) between the exchanges.
+"""
+import math
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+# columns of a particle row (everything that travels with a particle)
+COLS = {"points": (0, 3), "velocities": (3, 6), "total_accel": (6, 9), "mass": (9, 10), "sizes": (10, 11), "T": (11, 12),
+        "E_internal": (12, 13), "mu_array": (13, 14), "gamma_array": (14, 15), "particle_type": (15, 16),
+        "densities_0": (16, 17), "knn_h": (17, 18), "gid": (18, 19)}
+NCOL = 19
+STATE_FIELDS = ("points", "velocities", "total_accel", "mass", "sizes", "T", "E_internal", "mu_array", "gamma_array",
+                "particle_type", "densities_0")
+
+
+def rows_from_state(state, gid=None):
+    """(N, NCOL) float64 matrix from a dict of host arrays keyed by the driver's variable names."""
+    n = len(state["points"])
+    rows = np.zeros((n, NCOL))
+    for name in STATE_FIELDS:
+        a, b = COLS[name]
+        if name in state and state[name] is not None:
+            rows[:, a:b] = np.asarray(state[name], dtype=np.float64).reshape(n, b - a)
+    rows[:, 18] = np.arange(n) if gid is None else gid
+    return rows
+
+
+class SlabExchange(object):
+    """Ownership by x-slab, migration, ghost selection and ghost refresh.  Works on any device."""
+
+    def __init__(self, bounds, rank=None, world=None, group=None):
+        self.group = group
+        self.rank = dist.get_rank(group) if rank is None else rank
+        self.world = dist.get_world_size(group) if world is None else world
+        self.bounds = [float(b) for b in bounds]                  # world + 1 ascending; ends may be +-inf
+        assert len(self.bounds) == self.world + 1
+        self.lo, self.hi = self.bounds[self.rank], self.bounds[self.rank + 1]
+        self.send_idx = None          # per destination rank: indices of owned rows sent as ghosts
+        self.recv_counts = None
+        self.w = None
+
+    # -- plumbing -----------------------------------------------------------------------------
+    def _all_to_all_rows(self, parts, recv_counts=None):
+        """parts[r] = rows for rank r.  Returns (received rows, counts per source rank)."""
+        dev, dtype = parts[0].device, parts[0].dtype
+        ncol = parts[0].shape[1]
+        send_counts = [int(p.shape[0]) for p in parts]
+        if recv_counts is None:
+            sc = torch.tensor(send_counts, dtype=torch.int64, device=dev)
+            rc = torch.empty_like(sc)
+            dist.all_to_all_single(rc, sc, group=self.group)
+            recv_counts = [int(v) for v in rc.tolist()]
+        send = torch.cat(parts, dim=0).contiguous()
+        recv = torch.empty((sum(recv_counts), ncol), dtype=dtype, device=dev)
+        dist.all_to_all_single(recv, send, output_split_sizes=recv_counts, input_split_sizes=send_counts, group=self.group)
+        return recv, recv_counts
+
+    def owner_of(self, x):
+        inner = torch.tensor(self.bounds[1:-1], dtype=x.dtype, device=x.device)
+        return torch.bucketize(x, inner, right=True)              # x == bound belongs to the upper slab
+
+    # -- the three exchanges --------------------------------------------------------------------
+    def migrate(self, rows):
+        """Send every row to the rank whose slab holds its x (column 0); returns the new owned rows."""
+        dest = self.owner_of(rows[:, 0].contiguous())
+        order = torch.argsort(dest, stable=True)
+        counts = torch.bincount(dest, minlength=self.world).tolist()
+        parts = list(torch.split(rows[order], counts, dim=0))
+        recv, _ = self._all_to_all_rows(parts)
+        return recv
+
+    def build_halo(self, rows, w):
+        """Select, for every other rank, the owned rows within `w` of its slab; exchange them.
+        Remembers the send lists so that `update_ghosts` can refresh single fields later."""
+        x = rows[:, 0]
+        self.w = float(w)
+        self.send_idx = []
+        for r in range(self.world):
+            if r == self.rank:
+                self.send_idx.append(torch.zeros(0, dtype=torch.int64, device=rows.device))
+                continue
+            m = (x >= self.bounds[r] - w) & (x < self.bounds[r + 1] + w)
+            self.send_idx.append(torch.nonzero(m, as_tuple=False).flatten())
+        parts = [rows[i] for i in self.send_idx]
+        ghosts, self.recv_counts = self._all_to_all_rows(parts)
+        return ghosts
+
+    def update_ghosts(self, owned_values):
+        """owned_values (n_own, c): returns the owners' current values for this rank's ghosts, in ghost order."""
+        v = owned_values if owned_values.dim() == 2 else owned_values[:, None]
+        parts = [v[i] for i in self.send_idx]
+        recv, _ = self._all_to_all_rows(parts, self.recv_counts)
+        return recv if owned_values.dim() == 2 else recv[:, 0]
+
+    def covered(self, x, h):
+        """True where the ball (x, h) of an owned particle lies inside the region owned + ghosts cover."""
+        ok = torch.ones_like(x, dtype=torch.bool)
+        if self.rank > 0:
+            ok &= (x - h) >= (self.lo - self.w)
+        if self.rank < self.world - 1:
+            ok &= (x + h) < (self.hi + self.w)
+        return ok
+
+
+def equal_count_bounds(x, world):
+    """Slab faces with equal particle counts (host array of all x); outer faces are +-inf."""
+    xs = np.sort(np.asarray(x, dtype=np.float64))
+    inner = [0.5 * (xs[(len(xs) * r) // world - 1] + xs[(len(xs) * r) // world]) for r in range(1, world)]
+    return [-np.inf] + inner + [np.inf]
+
+
+def distributed_order_statistic(sorted_local, k, group=None):
+    """Exact k-th smallest (0-based) of the union of every rank's `sorted_local` (ascending float64,
+    values >= 0, no NaN).  Radix select on the IEEE bit patterns (monotone for non-negative doubles):
+    four rounds of 16 bits, each one searchsorted of 65537 bin edges and one all_reduce(SUM)."""
+    keys = sorted_local.contiguous().view(torch.int64)
+    dev = keys.device
+    n_local = torch.tensor([keys.numel()], dtype=torch.int64, device=dev)
+    prefix = 0
+    for shift in (48, 32, 16, 0):
+        nb = 32768 if shift == 48 else 65536                       # bit 63 is the sign: never set here
+        edges = prefix + (torch.arange(nb, dtype=torch.int64, device=dev) << shift)
+        cnt = torch.searchsorted(keys, edges)
+        cnt = torch.cat([cnt, n_local])                            # last edge = +infinity of this prefix range
+        if shift != 48:                                            # elements beyond this prefix's range
+            top = prefix + (1 << (shift + 16))
+            cnt[-1] = torch.searchsorted(keys, torch.tensor([top], dtype=torch.int64, device=dev))[0] if top < (1 << 63) else n_local[0]
+        if dist.is_initialized():
+            dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=group)
+        j = int(torch.searchsorted(cnt, torch.tensor([k], dtype=torch.int64, device=dev), right=True)[0]) - 1
+        j = max(0, min(nb - 1, j))
+        prefix += j << shift
+    return torch.tensor([prefix], dtype=torch.int64).view(torch.float64).item()
+
+
+def distributed_percentile(sorted_local, q=90.0, group=None):
+    """numpy.percentile(values, q) (linear interpolation, numpy's _lerp) of the union of all ranks'
+    values; returns (percentile, global count).  code_running.py:515-518."""
+    dev = sorted_local.device
+    ns_t = torch.tensor([sorted_local.numel()], dtype=torch.int64, device=dev)
+    if dist.is_initialized():
+        dist.all_reduce(ns_t, op=dist.ReduceOp.SUM, group=group)
+    ns = int(ns_t.item())
+    if ns == 0:
+        return float("nan"), 0
+    pos = q / 100.0 * (ns - 1)
+    lo = int(math.floor(pos))
+    t = pos - lo
+    a = distributed_order_statistic(sorted_local, lo, group)
+    b = a
+    if lo + 1 < ns:
+        av = torch.tensor([a], dtype=torch.float64, device=dev)
+        i_gt = torch.searchsorted(sorted_local, av, right=True)     # local count of values <= a
+        c_le = i_gt.clone()
+        nxt = torch.where(i_gt < sorted_local.numel(), sorted_local[i_gt.clamp(max=max(sorted_local.numel() - 1, 0))]
+                          if sorted_local.numel() else av, torch.full_like(av, float("inf")))
+        if dist.is_initialized():
+            dist.all_reduce(c_le, op=dist.ReduceOp.SUM, group=group)
+            dist.all_reduce(nxt, op=dist.ReduceOp.MIN, group=group)
+        b = a if int(c_le.item()) >= lo + 2 else float(nxt.item())
+    diff = b - a
+    v = a + diff * t
+    if t >= 0.5:
+        v = b - diff * (1.0 - t)
+    return v, ns
+
+
+class DistributedSession(object):
+    """The device-resident time step (session.Session) over slabs: same phases, with the exchanges the
+    reference's formulas need folded into them.  State between steps lives in the rank's session
+    (owned rows first, ghosts after them, in the session's caller order)."""
+
+    PHASES = ("crossing", "dt_clamp", "exchange", "sort", "knn", "pack", "density", "pi", "force", "integrate")
+
+    def __init__(self, rows, bounds, k, dist_cut, dt_0, device, n_total=None, group=None):
+        from . import constants as C
+        from .session import Session
+        self._Session = Session
+        self.C = C
+        self.device = torch.device("cuda", device) if not isinstance(device, torch.device) else device
+        self.group = group
+        self.ex = SlabExchange(bounds, group=group)
+        self.k, self.dist_cut, self.dt_0 = int(k), float(dist_cut), float(dt_0)
+        self.rows = rows.to(self.device).contiguous()             # owned rows until the first session exists
+        self.sess = None
+        self.n_own = int(self.rows.shape[0])
+        self.age, self.dt, self.d, self.ct = 0.0, self.dt_0, float(C.d_default), 0.0
+        self.w = None
+        self.halo_redo = 0
+        self.hmax = 0.0
+
+    # -- construction helpers -----------------------------------------------------------------
+    @classmethod
+    def from_global_state(cls, state, device, dt_0=None, group=None):
+        """Every rank passes the same full initial conditions; each keeps its equal-count slab."""
+        from . import constants as C
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        bounds = equal_count_bounds(state["points"][:, 0], world)
+        rows = rows_from_state(state)
+        x = rows[:, 0]
+        mine = (x >= bounds[rank]) & (x < bounds[rank + 1])
+        self = cls(torch.from_numpy(rows[mine]), bounds, state["N_NEIGH"], state["dist"],
+                   dt_0 if dt_0 is not None else state.get("dt_0", C.dt_0), device, group=group)
+        if "d" in state:
+            self.d = float(state["d"])
+        return self
+
+    @classmethod
+    def uniform_slabs(cls, n_per_rank, seed, k, dt_scale, device, group=None):
+        """Weak-scaling workload of bench.py: the uniform box of ics.uniform_box, `world` times longer
+        along x; every rank generates the particles of its own slab (seed + rank)."""
+        from . import constants as C, ics
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        st = ics.uniform_box(n_per_rank, seed + rank)
+        side = st["side"]
+        st["points"][:, 0] += side * (rank - 0.5 * (world - 1))   # slab r spans [(r - W/2) side, (r + 1 - W/2) side)
+        bounds = [-np.inf] + [side * (r - 0.5 * world) for r in range(1, world)] + [np.inf]
+        rows = rows_from_state(st, gid=np.arange(n_per_rank) + rank * n_per_rank)
+        return cls(torch.from_numpy(rows), bounds, k, st["dist"], C.dt_0 * dt_scale, device, group=group)
+
+    # -- small collectives --------------------------------------------------------------------
+    def _allreduce(self, value, op):
+        t = torch.tensor([value], dtype=torch.float64, device=self.device)
+        dist.all_reduce(t, op=op, group=self.group)
+        return float(t.item())
+
+    def _refresh_ghosts(self, name):
+        """Overwrite the ghosts' `name` with their owners' current values."""
+        full = self.sess.download_tensor(name)
+        full[self.n_own:] = self.ex.update_ghosts(full[:self.n_own])
+        self.sess.upload_tensor(name, full)
+
+    # -- (re)building the local particle set ----------------------------------------------------
+    def _open_session(self, rows, w):
+        """Ghost exchange for halo width w, then a session over owned + ghost rows."""
+        ghosts = self.ex.build_halo(rows, w)
+        local = torch.cat([rows, ghosts], dim=0).contiguous()
+        self.rows = rows
+        self.n_own = int(rows.shape[0])
+        s = self._Session(int(local.shape[0]), self.k, self.dist_cut, device=self.device.index, dt_0=self.dt_0)
+        for name in STATE_FIELDS + ("knn_h",):
+            a, b = COLS[name]
+            col = local[:, a:b].contiguous() if b - a > 1 else local[:, a].contiguous()
+            s.upload_tensor(name, col)
+        for name, v in (("age", self.age), ("d", self.d), ("dt", self.dt), ("ct", self.ct), ("n_owned", self.n_own)):
+            s.set_scalar(name, v)
+        self.gid = local[:, 18].contiguous()
+        self.sess = s
+        self.w = w
+
+    def _owned_rows(self):
+        """Current owned rows (state columns + trial radius + gid) out of the session."""
+        cols = []
+        for name in STATE_FIELDS + ("knn_h",):
+            t = self.sess.download_tensor(name)[:self.n_own]
+            cols.append(t if t.dim() == 2 else t[:, None])
+        cols.append(self.gid[:self.n_own, None])
+        return torch.cat(cols, dim=1)
+
+    def _initial_halo_width(self, rows):
+        """1.6 x the k-th-neighbour distance expected at the mean number density of the global box."""
+        lo = rows[:, :3].min(dim=0).values if rows.shape[0] else torch.full((3,), float("inf"), device=self.device, dtype=torch.float64)
+        hi = rows[:, :3].max(dim=0).values if rows.shape[0] else torch.full((3,), float("-inf"), device=self.device, dtype=torch.float64)
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=self.group)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=self.group)
+        n_tot = self._allreduce(float(rows.shape[0]), dist.ReduceOp.SUM)
+        vol = float(torch.prod(torch.clamp(hi - lo, min=1e-300)).item())
+        return 1.6 * (self.k * vol / (4.1887902047863905 * max(n_tot, 1.0))) ** (1.0 / 3.0)
+
+    # -- phases -------------------------------------------------------------------------------
+    def _search(self):
+        """sort + k-NN on owned + ghosts; widen the halo and redo until every owned particle's k-th
+        neighbour provably lies inside the covered region; then fetch the ghosts' owner-computed h."""
+        while True:
+            self.sess.phase("sort")
+            self.sess.phase("knn")
+            h = self.sess.download_tensor("sizes")[:self.n_own]
+            x = self.sess.download_tensor("points")[:self.n_own, 0]
+            bad = float((~self.ex.covered(x, h)).sum().item())
+            hmax = float(h.max().item()) if self.n_own else 0.0
+            bad = self._allreduce(bad, dist.ReduceOp.SUM)
+            self.hmax = self._allreduce(hmax, dist.ReduceOp.MAX)
+            if bad == 0:
+                break
+            self.halo_redo += 1
+            self._open_session(self.rows, 2.0 * self.w)
+        self._refresh_ghosts("sizes")
+
+    def startup(self):
+        """code_running.py:171-179 on slabs: first neighbour query + hydro_update, densities_0 <- densities."""
+        rows = self.ex.migrate(self.rows)
+        self._open_session(rows, self._initial_halo_width(rows))
+        self._search()
+        for ph in ("pack", "density", "pi", "force"):
+            self.phase(ph)
+        self.sess.phase("rho0")
+
+    def phase(self, name):
+        s = self.sess
+        if name == "crossing":
+            self._refresh_ghosts("velocities")                    # nsc:780 needs the neighbours' current velocities
+            s.phase("crossing")
+            self.ct = self._allreduce(s.scalar("ct"), dist.ReduceOp.MIN)
+            s.set_scalar("ct", self.ct)
+        elif name == "dt_clamp":
+            s.phase("dt_clamp")
+        elif name == "exchange":
+            self.age, self.dt = s.scalar("age"), s.scalar("dt")
+            rows = self.ex.migrate(self._owned_rows())
+            self._open_session(rows, 1.25 * self.hmax)
+        elif name == "sort":
+            pass                                                  # part of "knn" here (the search may be redone)
+        elif name == "knn":
+            self._search()
+        elif name == "pack":
+            s.phase("pack")
+        elif name == "density":
+            s.phase("density")
+            self._refresh_ghosts("densities")                     # nsc:646 needs the neighbours' density
+        elif name == "pi":
+            s.phase("pi")
+            self._refresh_ghosts("visc_pi")                       # nsc:651 needs the neighbours' Pi
+        elif name == "force":
+            s.phase("force")
+        elif name == "integrate":
+            s.phase("kick")
+            dsq = s.download_tensor("dist_sq")[:self.n_own]
+            slow = torch.sort(dsq[torch.isfinite(dsq)]).values
+            v, ns = distributed_percentile(slow, 90.0, self.group)             # code_running.py:515-518
+            self.n_slow, self.max_dist = ns, v
+            self.d = (v ** 1.5 / ns / 0.9 * self.C.N_INT_PER_PARTICLE) ** (1. / 3.) if ns else float("nan")   # :520-521
+            s.set_scalar("d", self.d)
+            s.phase("smooth")
+        else:
+            raise ValueError("unknown phase %r" % name)
+
+    def step(self):
+        for ph in self.PHASES:
+            self.phase(ph)
+
+    # -- the Session interface bench.py and the tests use ---------------------------------------
+    def phases(self):
+        return self.PHASES
+
+    def n_owned(self):
+        return self.n_own
+
+    def check(self):
+        self.sess.check()
+
+    def launches(self):
+        return self.sess.launches()               # the context's counter is cumulative across sessions
+
+    def scalar(self, name):
+        if name in ("ct", "d"):
+            return {"ct": self.ct, "d": self.d}[name]
+        return self.sess.scalar(name)
+
+    # -- host-resident state (bench.py's e2e leg) ------------------------------------------------
+    def make_host_state(self, upload_fields=None, download_fields=None):
+        rows = self._owned_rows()
+        cap = int(rows.shape[0] * 1.25) + 1024
+        buf = torch.empty((cap, NCOL), dtype=torch.float64).pin_memory()
+        buf[:rows.shape[0]].copy_(rows)
+        return {"buf": buf, "n": int(rows.shape[0]), "h2d_bytes": int(rows.shape[0]) * NCOL * 8,
+                "d2h_bytes": int(rows.shape[0]) * NCOL * 8}
+
+    def step_host(self, hs):
+        """One step of a host-resident slab: the owned rows are uploaded from pinned memory into the
+        session, the step runs (with its exchanges), the new owned rows come back to pinned memory."""
+        rows = hs["buf"][:hs["n"]].to(self.device, non_blocking=True)
+        for name in STATE_FIELDS + ("knn_h",):
+            a, b = COLS[name]
+            full = self.sess.download_tensor(name)
+            full[:self.n_own] = rows[:, a:b] if b - a > 1 else rows[:, a]
+            self.sess.upload_tensor(name, full)
+        self.step()
+        out = self._owned_rows()
+        if out.shape[0] > hs["buf"].shape[0]:
+            hs["buf"] = torch.empty((int(out.shape[0] * 1.25), NCOL), dtype=torch.float64).pin_memory()
+        hs["n"] = int(out.shape[0])
+        hs["buf"][:hs["n"]].copy_(out, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        hs["h2d_bytes"] = hs["d2h_bytes"] = hs["n"] * NCOL * 8
+
+    def download_owned(self, name):
+        """(gid, values) of this rank's owned particles."""
+        return self.gid[:self.n_own].to(torch.int64), self.sess.download_tensor(name)[:self.n_own]
+
+    def gather(self, name):
+        """Field `name` of ALL particles ordered by gid, on every rank (tests / small runs only)."""
+        gid, val = self.download_owned(name)
+        world = dist.get_world_size(self.group)
+        counts = [None] * world
+        dist.all_gather_object(counts, int(gid.numel()), group=self.group)
+        v2 = val if val.dim() == 2 else val[:, None]
+        nmax = max(counts)
+        pad_g = torch.full((nmax,), -1, dtype=torch.int64, device=self.device); pad_g[:gid.numel()] = gid
+        pad_v = torch.zeros((nmax, v2.shape[1]), dtype=v2.dtype, device=self.device); pad_v[:gid.numel()] = v2
+        gs = [torch.empty_like(pad_g) for _ in range(world)]
+        vs = [torch.empty_like(pad_v) for _ in range(world)]
+        dist.all_gather(gs, pad_g, group=self.group)
+        dist.all_gather(vs, pad_v, group=self.group)
+        g = torch.cat([gs[r][:counts[r]] for r in range(world)])
+        v = torch.cat([vs[r][:counts[r]] for r in range(world)])
+        out = torch.empty_like(v)
+        out[g] = v
+        return out.cpu().numpy() if val.dim() == 2 else out[:, 0].cpu().numpy()

@@ -18,6 +18,8 @@ STATE_FIELDS = {"points": 3, "velocities": 3, "total_accel": 3, "mass": 1, "size
                 "mu_array": 1, "gamma_array": 1, "particle_type": 1, "densities_0": 1}
 RESULT_FIELDS = {"densities": 1, "num_densities": 1, "dust_densities": 1, "visc_heat": 1, "hydro_accel": 3,
                  "visc_accel": 3, "pressure_accel": 3}
+# owner-computed per-particle arrays the slab-decomposed driver reads / overwrites for ghosts (domain.py)
+AUX_FIELDS = {"densities": 1, "visc_pi": 1, "knn_h": 1, "dist_sq": 1}
 PHASES = ("crossing", "dt_clamp", "sort", "knn", "pack", "density", "pi", "force", "integrate")
 
 
@@ -47,7 +49,7 @@ class Session(object):
 
     def upload_tensor(self, name, t):
         """t: contiguous float64 CUDA tensor in the caller's particle order."""
-        w = STATE_FIELDS[name]
+        w = STATE_FIELDS.get(name) or AUX_FIELDS[name]
         if t.numel() != self.n * w or t.dtype != torch.float64 or not t.is_cuda:
             raise ValueError("field %s needs a float64 CUDA tensor of %d values" % (name, self.n * w))
         _lib.check(self.lib.sphb200_session_upload(self.ctx.handle, name.encode(), ctypes.c_void_p(t.data_ptr()),
@@ -68,7 +70,7 @@ class Session(object):
         elif name == "num_nontrivial":
             out = torch.empty((self.n,), dtype=torch.int64, device=self.device)
         else:
-            w = STATE_FIELDS.get(name) or RESULT_FIELDS[name]
+            w = STATE_FIELDS.get(name) or RESULT_FIELDS.get(name) or AUX_FIELDS[name]
             out = torch.empty((self.n, w) if w > 1 else (self.n,), dtype=torch.float64, device=self.device)
         _lib.check(self.lib.sphb200_session_download(self.ctx.handle, name.encode(), ctypes.c_void_p(out.data_ptr()),
                                                      out.numel(), self._stream()))
