@@ -244,6 +244,10 @@ def run_ours(args):
     total_ms = ev[0][0].elapsed_time(ev[K - 1][-1])
     launches = sess.launches() - launches0
     phase_ms = {ph: sum(ev[s][i].elapsed_time(ev[s][i + 1]) for s in range(K)) / K for i, ph in enumerate(phases)}
+    if os.environ.get("BENCH_VERBOSE") and rank == 0:
+        for s in range(K):
+            sys.stderr.write("step %d: %s\n" % (s, " ".join("%s=%.3f" % (ph, ev[s][i].elapsed_time(ev[s][i + 1]))
+                                                              for i, ph in enumerate(phases))))
     n_local = float(sess.n_owned() if hasattr(sess, "n_owned") else n)
     stats = torch.tensor([total_ms, n_local], dtype=torch.float64, device=dev)
     if world > 1:

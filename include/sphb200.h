@@ -90,7 +90,20 @@ int sphb200_artificial_viscosity(sphb200_ctx* ctx, int64_t n, int k, const int64
 int sphb200_session_create(sphb200_ctx* ctx, int64_t n, int k, double dist);
 int sphb200_session_upload(sphb200_ctx* ctx, const char* field, const void* src, int64_t count, void* stream);
 int sphb200_session_download(sphb200_ctx* ctx, const char* field, void* dst, int64_t count, void* stream);
-/* run parameters: "dt_0", "MAX_AGE", "N_INT_PER_PARTICLE", "raise_factor", "AU", "dist", "age", "d", "dt" */
+/* Whole particle rows, (n_rows, ncol >= 18) doubles in the caller's order: columns 0-16 are the eleven
+ * state fields in the order listed above, column 17 the k-NN trial radius (previous k-th distance);
+ * further columns belong to the caller.  download writes rows [0, n_rows); upload needs n_rows == N.
+ * Also accepted by upload/download by name: "densities", "visc_pi", "knn_h" (owner-computed values a
+ * slab decomposition overwrites for ghost particles) and, download only, "dist_sq".
+ * Extra phases: "kick", "length", "smooth" (the three parts of "integrate"), "rho0". */
+/* one field at `count` caller indices (device int64): out/in is (count, width) doubles */
+int sphb200_session_gather(sphb200_ctx* ctx, const char* field, const int64_t* idx, int64_t count, double* out, void* stream);
+int sphb200_session_scatter(sphb200_ctx* ctx, const char* field, const int64_t* idx, int64_t count, const double* in, void* stream);
+int sphb200_session_download_rows(sphb200_ctx* ctx, double* rows, int64_t n_rows, int ncol, void* stream);
+int sphb200_session_upload_rows(sphb200_ctx* ctx, const double* rows, int64_t n_rows, int ncol, void* stream);
+/* run parameters: "dt_0", "MAX_AGE", "N_INT_PER_PARTICLE", "raise_factor", "AU", "dist", "age", "d", "dt", "ct",
+ * "n_owned" (caller indices >= n_owned are ghosts of a slab decomposition: excluded from the crossing-time
+ * minimum and from the percentile behind d) */
 int sphb200_session_set_scalar(sphb200_ctx* ctx, const char* name, double value);
 /* device scalars of the last step: "ct", "dt", "d", "age", "max_dist", "n_slow" (synchronises) */
 int sphb200_session_scalar(sphb200_ctx* ctx, const char* name, double* value_host, void* stream);

@@ -32,6 +32,10 @@ SIGNATURES = {
     "sphb200_session_create": [c_ptr, c_i64, c_int, c_dbl],
     "sphb200_session_upload": [c_ptr, ctypes.c_char_p, c_ptr, c_i64, c_ptr],
     "sphb200_session_download": [c_ptr, ctypes.c_char_p, c_ptr, c_i64, c_ptr],
+    "sphb200_session_gather": [c_ptr, ctypes.c_char_p, c_ptr, c_i64, c_ptr, c_ptr],
+    "sphb200_session_scatter": [c_ptr, ctypes.c_char_p, c_ptr, c_i64, c_ptr, c_ptr],
+    "sphb200_session_download_rows": [c_ptr, c_ptr, c_i64, c_int, c_ptr],
+    "sphb200_session_upload_rows": [c_ptr, c_ptr, c_i64, c_int, c_ptr],
     "sphb200_session_startup": [c_ptr, c_ptr],
     "sphb200_session_step": [c_ptr, c_ptr],
     "sphb200_session_scalar": [c_ptr, ctypes.c_char_p, ctypes.POINTER(c_dbl), c_ptr],

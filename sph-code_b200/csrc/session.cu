@@ -26,6 +26,7 @@ static const char* kOutName[O_NOUT] = {"densities", "num_densities", "dust_densi
 #define SB_DISTSQ_ALT 36
 #define SB_KNNH 37           // k-th neighbour distance of the last search (guess for the next one)
 #define SB_KNNH_ALT 38
+#define SB_POS 39            // caller index -> sorted position (inverse of id), built on demand
 
 struct SessionScalars {      // host mirror of the run parameters
   double dt_0, max_age, n_int, raise_factor, au;
@@ -40,6 +41,7 @@ struct Session {
   int knnh_cur = 0;
   int has_list = 0;
   int use_guess = 1;
+  int pos_valid = 0;         // SB_POS matches the current id
   int64_t n_owned = -1;      // slab decomposition: caller indices >= n_owned are ghosts (-1: none)
   SessionScalars sc;
 };
@@ -117,7 +119,7 @@ integrate_kernel(int n, const double* __restrict__ scal, double kB, double m_h, 
                  const double* __restrict__ mass, const double* __restrict__ mu, const double* __restrict__ gamma,
                  const double* __restrict__ ptype, const double* __restrict__ hacc, double* __restrict__ vacc,
                  const double* __restrict__ heat, double* __restrict__ pacc, double* __restrict__ distsq,
-                 unsigned long long* __restrict__ nslow) {
+                 unsigned long long* __restrict__ nslow, const uint32_t* __restrict__ id, int n_owned) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   int slow = 0;
   if (i < n) {
@@ -154,7 +156,7 @@ integrate_kernel(int n, const double* __restrict__ scal, double kB, double m_h, 
     const double e = nan_to_num_d(E[i]) + nan_to_num_d(heat[i] * dt);            // :490
     E[i] = e;
     T[i] = nan_to_num_d(e * (mu[i] * m_h) / (gamma[i] * mass[i] * kB));          // :491
-    slow = (v2 < 80000.0 * 80000.0);                                             // :493
+    slow = (v2 < 80000.0 * 80000.0) && (!id || (int)id[i] < n_owned);            // :493 (ghosts belong to their owner)
     distsq[i] = slow ? x2 : INFINITY;
   }
   const int cnt = __syncthreads_count(slow);
@@ -261,6 +263,69 @@ sort_in_kernel(int n, int w, const uint32_t* __restrict__ id, const double* __re
   dst[t] = src[(int64_t)id[i] * w + c];
 }
 
+// Single-field access at given caller indices (ghost refresh of a slab decomposition): a handful of
+// particles per call, so no full-array permutation.
+__global__ void __launch_bounds__(256) invert_id_kernel(int n, const uint32_t* __restrict__ id, uint32_t* __restrict__ pos) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) pos[id[i]] = (uint32_t)i;
+}
+__global__ void __launch_bounds__(256)
+gather_at_kernel(int64_t count, int w, int n, const int64_t* __restrict__ cidx, const uint32_t* __restrict__ pos,
+                 const double* __restrict__ field, double* __restrict__ out, int* __restrict__ flags) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= count * w) return;
+  const int64_t e = t / w; const int q = (int)(t % w);
+  const int64_t c = cidx[e];
+  if (c < 0 || c >= n) { atomicAdd(&flags[FL_BAD_INDEX], 1); return; }
+  out[t] = field[(int64_t)pos[c] * w + q];
+}
+__global__ void __launch_bounds__(256)
+scatter_at_kernel(int64_t count, int w, int n, const int64_t* __restrict__ cidx, const uint32_t* __restrict__ pos,
+                  const double* __restrict__ in, double* __restrict__ field, int* __restrict__ flags) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= count * w) return;
+  const int64_t e = t / w; const int q = (int)(t % w);
+  const int64_t c = cidx[e];
+  if (c < 0 || c >= n) { atomicAdd(&flags[FL_BAD_INDEX], 1); return; }
+  field[(int64_t)pos[c] * w + q] = in[t];
+}
+
+// Whole particle rows (AoS, `ncol` doubles per particle: the eleven state fields in kFieldName order,
+// then the k-NN trial radius) <-> the session's sorted struct of arrays, in one pass.  The slab
+// decomposition moves particles between ranks as such rows (domain.py).
+struct RowArgs { double* f[F_NFIELDS]; double* knnh; };
+#define ROW_STATE_COLS 18
+
+__global__ void __launch_bounds__(256)
+rows_out_kernel(int n, int64_t n_rows, int ncol, const uint32_t* __restrict__ id, RowArgs a, double* __restrict__ dst) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int64_t c = id[i];
+  if (c >= n_rows) return;
+  double* o = dst + c * ncol;
+  int col = 0;
+#pragma unroll
+  for (int f = 0; f < 3; ++f)
+    for (int q = 0; q < 3; ++q) o[col++] = a.f[f][3 * (int64_t)i + q];
+#pragma unroll
+  for (int f = 3; f < F_NFIELDS; ++f) o[col++] = a.f[f][i];
+  o[col] = a.knnh[i];
+}
+
+__global__ void __launch_bounds__(256)
+rows_in_kernel(int n, int ncol, const uint32_t* __restrict__ id, const double* __restrict__ src, RowArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double* r = src + (int64_t)id[i] * ncol;
+  int col = 0;
+#pragma unroll
+  for (int f = 0; f < 3; ++f)
+    for (int q = 0; q < 3; ++q) a.f[f][3 * (int64_t)i + q] = r[col++];
+#pragma unroll
+  for (int f = 3; f < F_NFIELDS; ++f) a.f[f][i] = r[col++];
+  a.knnh[i] = r[col];
+}
+
 // ------------------------------------------------------------------------------------------------
 static int phase_crossing(sphb200_ctx* ctx, cudaStream_t st) {
   Session& s = sess(ctx);
@@ -296,6 +361,7 @@ static int phase_sort(sphb200_ctx* ctx, cudaStream_t st) {
   s.id_cur ^= 1;
   s.knnh_cur ^= 1;
   s.has_list = 0;
+  s.pos_valid = 0;
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -350,7 +416,9 @@ static int phase_kick(sphb200_ctx* ctx, cudaStream_t st) {
                                                      fld(ctx, F_VEL), fld(ctx, F_ACC), fld(ctx, F_E), fld(ctx, F_T),
                                                      fld(ctx, F_MASS), fld(ctx, F_MU), fld(ctx, F_GAMMA), fld(ctx, F_TYPE),
                                                      outp(ctx, O_HACC), outp(ctx, O_VACC), outp(ctx, O_HEAT),
-                                                     outp(ctx, O_PACC), bufp<double>(ctx->sbuf[SB_DISTSQ]), nslow);
+                                                     outp(ctx, O_PACC), bufp<double>(ctx->sbuf[SB_DISTSQ]), nslow,
+                                                     s.n_owned >= 0 ? bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]) : nullptr,
+                                                     (int)s.n_owned);
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;
@@ -440,6 +508,19 @@ int sphb200_session_create(sphb200_ctx* ctx, int64_t n, int k, double dist) {
   return 0;
 }
 
+// device scalars addressable as "scalar:<name>" by upload / download (one double, device to device, no
+// host synchronisation: the slab driver all_reduces the crossing time in place)
+static int find_scalar(const char* name) {
+  if (strncmp(name, "scalar:", 7)) return -1;
+  name += 7;
+  if (!strcmp(name, "ct")) return SC_CT;
+  if (!strcmp(name, "dt")) return SC_DT;
+  if (!strcmp(name, "d")) return SC_D;
+  if (!strcmp(name, "age")) return SC_AGE;
+  if (!strcmp(name, "n_slow")) return SC_NSLOW;
+  return -1;
+}
+
 static int find_field(const char* name) {
   for (int f = 0; f < F_NFIELDS; ++f) if (!strcmp(name, kFieldName[f])) return f;
   return -1;
@@ -451,6 +532,12 @@ int sphb200_session_upload(sphb200_ctx* ctx, const char* name, const void* src, 
   CUDA_TRY(cudaSetDevice(ctx->device));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   Session& s = sess(ctx);
+  const int sc = find_scalar(name);
+  if (sc >= 0) {
+    if (count != 1) SPH_FAIL("session_upload: '%s' is one value", name);
+    CUDA_TRY(cudaMemcpyAsync(bufp<double>(ctx->scal) + sc, src, sizeof(double), cudaMemcpyDeviceToDevice, st));
+    return 0;
+  }
   const int f = find_field(name);
   double* dstp = (f >= 0) ? fld(ctx, f) : aux_field(ctx, name, true);
   const int w = (f >= 0) ? kFieldWidth[f] : 1;
@@ -472,11 +559,25 @@ int sphb200_session_download(sphb200_ctx* ctx, const char* name, void* dst, int6
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const uint32_t* id = bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]);
   const int n = (int)s.n;
+  const int sc = find_scalar(name);
+  if (sc >= 0) {
+    if (count != 1) SPH_FAIL("session_download: '%s' is one value", name);
+    CUDA_TRY(cudaMemcpyAsync(dst, bufp<double>(ctx->scal) + sc, sizeof(double), cudaMemcpyDeviceToDevice, st));
+    return 0;
+  }
   if (!strcmp(name, "neighbor")) {
     if (!s.has_list) SPH_FAIL("session_download: no neighbour list");
     if (count != s.n * s.k) SPH_FAIL("session_download: neighbor needs %lld values", (long long)(s.n * s.k));
     unsort_list_sorted_kernel<<<ceil_div(n, 128), 128, 0, st>>>(n, s.k, id, bufp<int32_t>(ctx->list), bufp<double4>(ctx->r0),
                                                               (int64_t*)dst);
+  } else if (!strcmp(name, "scalars")) {               // raw device scalars: [6] ct, [7] dt, [8] d, [9] age, [10] max_dist, [11] n_slow
+    if (count < 0 || count > SC_COUNT) SPH_FAIL("session_download: scalars holds %d values", SC_COUNT);
+    CUDA_TRY(cudaMemcpyAsync(dst, ctx->scal.p, (size_t)count * sizeof(double), cudaMemcpyDeviceToDevice, st));
+    return 0;
+  } else if (!strcmp(name, "dist_sq_sorted")) {        // ascending |x|^2 of the slow (owned) particles, raw
+    if (count < 0 || count > s.n) SPH_FAIL("session_download: dist_sq_sorted holds at most %lld values", (long long)s.n);
+    CUDA_TRY(cudaMemcpyAsync(dst, ctx->sbuf[SB_DISTSQ_ALT].p, (size_t)count * sizeof(double), cudaMemcpyDeviceToDevice, st));
+    return 0;
   } else if (!strcmp(name, "num_nontrivial")) {
     if (count != s.n) SPH_FAIL("session_download: num_nontrivial needs %lld values", (long long)s.n);
     unsort_i32_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, id, bufp<int32_t>(ctx->sbuf[SB_NONTRIV]), (int64_t*)dst);
@@ -491,6 +592,75 @@ int sphb200_session_download(sphb200_ctx* ctx, const char* name, void* dst, int6
     if (count != s.n * w) SPH_FAIL("session_download: '%s' needs %lld values, got %lld", name, (long long)(s.n * w), (long long)count);
     unsort_kernel<<<ceil_div(count, 256), 256, 0, st>>>(n, w, id, src, (double*)dst);
   }
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+static int find_field(const char* name);
+
+static int field_at(sphb200_ctx* ctx, const char* name, const int64_t* idx, int64_t count, double* buf, bool scatter,
+                    cudaStream_t st) {
+  Session& s = sess(ctx);
+  const int f = find_field(name);
+  double* p = (f >= 0) ? fld(ctx, f) : aux_field(ctx, name, scatter);
+  const int w = (f >= 0) ? kFieldWidth[f] : 1;
+  if (!p) SPH_FAIL("session gather/scatter: unknown field '%s'", name);
+  if (count <= 0) return 0;
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_POS], s.n * sizeof(uint32_t)));
+  uint32_t* pos = bufp<uint32_t>(ctx->sbuf[SB_POS]);
+  if (!s.pos_valid) {
+    invert_id_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]), pos);
+    s.pos_valid = 1;
+    ctx->launches += 1;
+  }
+  if (scatter) scatter_at_kernel<<<ceil_div(count * w, 256), 256, 0, st>>>(count, w, (int)s.n, idx, pos, buf, p, bufp<int>(ctx->flags));
+  else gather_at_kernel<<<ceil_div(count * w, 256), 256, 0, st>>>(count, w, (int)s.n, idx, pos, p, buf, bufp<int>(ctx->flags));
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  if (scatter && !strcmp(name, "visc_pi")) SPH_TRY(launch_repack_pi(ctx, (int)s.n, st));
+  return 0;
+}
+
+// out (count, w) <- field at caller indices idx (device int64)
+int sphb200_session_gather(sphb200_ctx* ctx, const char* field, const int64_t* idx, int64_t count, double* out, void* stream) {
+  if (!ctx || !field || (count > 0 && (!idx || !out))) SPH_FAIL("session_gather: null argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  return field_at(ctx, field, idx, count, out, false, reinterpret_cast<cudaStream_t>(stream));
+}
+// field at caller indices idx <- in (count, w)
+int sphb200_session_scatter(sphb200_ctx* ctx, const char* field, const int64_t* idx, int64_t count, const double* in, void* stream) {
+  if (!ctx || !field || (count > 0 && (!idx || !in))) SPH_FAIL("session_scatter: null argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  return field_at(ctx, field, idx, count, const_cast<double*>(in), true, reinterpret_cast<cudaStream_t>(stream));
+}
+
+// rows: device pointer, (n_rows, ncol) doubles, caller order; ncol >= 18 (extra columns are the caller's)
+int sphb200_session_download_rows(sphb200_ctx* ctx, double* rows, int64_t n_rows, int ncol, void* stream) {
+  if (!ctx || !rows) SPH_FAIL("session_download_rows: null argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  Session& s = sess(ctx);
+  if (ncol < ROW_STATE_COLS || n_rows < 0 || n_rows > s.n) SPH_FAIL("session_download_rows: bad shape (%lld, %d)", (long long)n_rows, ncol);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  RowArgs a;
+  for (int f = 0; f < F_NFIELDS; ++f) a.f[f] = fld(ctx, f);
+  a.knnh = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]);
+  rows_out_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, n_rows, ncol, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]), a, rows);
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int sphb200_session_upload_rows(sphb200_ctx* ctx, const double* rows, int64_t n_rows, int ncol, void* stream) {
+  if (!ctx || !rows) SPH_FAIL("session_upload_rows: null argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  Session& s = sess(ctx);
+  if (ncol < ROW_STATE_COLS || n_rows != s.n) SPH_FAIL("session_upload_rows: needs (%lld, >=18) rows, got (%lld, %d)", (long long)s.n, (long long)n_rows, ncol);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  RowArgs a;
+  for (int f = 0; f < F_NFIELDS; ++f) a.f[f] = fld(ctx, f);
+  a.knnh = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]);
+  rows_in_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, ncol, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]), rows, a);
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;

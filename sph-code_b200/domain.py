@@ -84,13 +84,17 @@ class SlabExchange(object):
 
     # -- the three exchanges --------------------------------------------------------------------
     def migrate(self, rows):
-        """Send every row to the rank whose slab holds its x (column 0); returns the new owned rows."""
+        """Send every row to the rank whose slab holds its x (column 0); returns the new owned rows.
+        Only the movers are sorted and split; the rows that stay are taken with one mask."""
         dest = self.owner_of(rows[:, 0].contiguous())
-        order = torch.argsort(dest, stable=True)
-        counts = torch.bincount(dest, minlength=self.world).tolist()
-        parts = list(torch.split(rows[order], counts, dim=0))
+        stay = dest == self.rank
+        mv = torch.nonzero(~stay, as_tuple=False).flatten()
+        mdest = dest[mv]
+        order = torch.argsort(mdest, stable=True)
+        counts = torch.bincount(mdest, minlength=self.world).tolist()
+        parts = list(torch.split(rows[mv[order]], counts, dim=0))
         recv, _ = self._all_to_all_rows(parts)
-        return recv
+        return torch.cat([rows[stay], recv], dim=0) if recv.shape[0] else rows[stay]
 
     def build_halo(self, rows, w):
         """Select, for every other rank, the owned rows within `w` of its slab; exchange them.
@@ -99,8 +103,8 @@ class SlabExchange(object):
         self.w = float(w)
         self.send_idx = []
         for r in range(self.world):
-            if r == self.rank:
-                self.send_idx.append(torch.zeros(0, dtype=torch.int64, device=rows.device))
+            if r == self.rank or not (self.bounds[r] - w < self.hi and self.bounds[r + 1] + w > self.lo):
+                self.send_idx.append(torch.zeros(0, dtype=torch.int64, device=rows.device))   # out of reach
                 continue
             m = (x >= self.bounds[r] - w) & (x < self.bounds[r + 1] + w)
             self.send_idx.append(torch.nonzero(m, as_tuple=False).flatten())
@@ -156,35 +160,80 @@ def distributed_order_statistic(sorted_local, k, group=None):
     return torch.tensor([prefix], dtype=torch.int64).view(torch.float64).item()
 
 
-def distributed_percentile(sorted_local, q=90.0, group=None):
+def distributed_percentile(sorted_local, q=90.0, group=None, pivots=1024, cap_hint=None):
     """numpy.percentile(values, q) (linear interpolation, numpy's _lerp) of the union of all ranks'
-    values; returns (percentile, global count).  code_running.py:515-518."""
+    ascending `sorted_local`; returns (percentile, global count).  code_running.py:515-518.
+
+    Exact selection in three small collectives and one host sync: (1) all_gather `pivots` evenly spaced
+    local order statistics per rank; (2) all_reduce the local counts below / up to every pivot, which
+    brackets the two wanted global ranks between neighbouring pivots a <= b; (3) all_gather the few
+    local elements inside [a, b] (at most ~2 pivot gaps per rank) and pick the two order statistics
+    from their merge.  Falls back to the radix select if a rank holds too many duplicates of a or b."""
     dev = sorted_local.device
-    ns_t = torch.tensor([sorted_local.numel()], dtype=torch.int64, device=dev)
-    if dist.is_initialized():
-        dist.all_reduce(ns_t, op=dist.ReduceOp.SUM, group=group)
-    ns = int(ns_t.item())
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    n_loc = sorted_local.numel()
+    P = pivots
+    inf = torch.full((1,), float("inf"), dtype=torch.float64, device=dev)
+    if n_loc:
+        pidx = torch.linspace(0, n_loc - 1, P, dtype=torch.float64, device=dev).round().to(torch.int64)
+        mine = torch.cat([sorted_local[pidx], torch.full((1,), float(n_loc), dtype=torch.float64, device=dev)])
+    else:
+        mine = torch.cat([inf.expand(P), torch.zeros(1, dtype=torch.float64, device=dev)])
+    if world > 1:
+        allp = torch.empty(world * (P + 1), dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(allp, mine.contiguous(), group=group)
+        allp = allp.view(world, P + 1)
+    else:
+        allp = mine[None, :]
+    piv = allp[:, :P].reshape(-1)
+    cnt = torch.cat([torch.searchsorted(sorted_local, piv), torch.searchsorted(sorted_local, piv, right=True)])
+    if world > 1:
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=group)
+    c_lt, c_le = cnt[:world * P], cnt[world * P:]
+    counts = allp[:, P]
+    ns_t = counts.sum().to(torch.int64)
+    pos_lo = torch.floor(q / 100.0 * (ns_t - 1).to(torch.float64)).to(torch.int64).clamp(min=0)
+    pos_hi = torch.minimum(pos_lo + 1, (ns_t - 1).clamp(min=0))
+    # a = largest pivot with fewer than pos_lo+1 elements below it; b = smallest pivot with > pos_hi elements up to it
+    a = torch.where(c_lt <= pos_lo, piv, -inf).max()
+    b = torch.where(c_le >= pos_hi + 1, piv, inf).min()
+    base = torch.where((piv == a), c_lt, torch.zeros_like(c_lt)).max()          # global count of elements < a
+    i0 = torch.searchsorted(sorted_local, a.reshape(1))[0]
+    i1 = torch.searchsorted(sorted_local, b.reshape(1), right=True)[0]
+    # fixed-size window (no host sync): cap elements starting at i0, +inf beyond i1
+    cap = 3 * int(math.ceil(max(float(n_loc), 1.0) / max(P - 1, 1))) + 64
+    if cap_hint is not None:                                       # same on every rank by construction: no collective
+        cap = int(cap_hint)
+    elif world > 1:
+        capt = torch.tensor([cap], dtype=torch.int64, device=dev)
+        dist.all_reduce(capt, op=dist.ReduceOp.MAX, group=group)
+        cap = int(capt.item())
+    widx = i0 + torch.arange(cap, dtype=torch.int64, device=dev)
+    vals = sorted_local[widx.clamp(max=max(n_loc - 1, 0))] if n_loc else inf.expand(cap)
+    win = torch.where(widx < i1, vals, inf.expand(cap))
+    win = torch.cat([win, (i1 - i0).to(torch.float64).reshape(1)])
+    if world > 1:
+        allw = torch.empty(world * (cap + 1), dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(allw, win.contiguous(), group=group)
+        allw = allw.view(world, cap + 1)
+    else:
+        allw = win[None, :]
+    merged = torch.sort(allw[:, :cap].reshape(-1)).values
+    k0 = (pos_lo - base).clamp(min=0, max=merged.numel() - 1)
+    k1 = (pos_hi - base).clamp(min=0, max=merged.numel() - 1)
+    res = torch.stack([merged[k0], merged[k1], ns_t.to(torch.float64), pos_lo.to(torch.float64),
+                       (allw[:, cap] > cap).any().to(torch.float64)]).tolist()          # the one host sync
+    va, vb, ns, lo, overflow = res[0], res[1], int(res[2]), int(res[3]), res[4] != 0.0
     if ns == 0:
         return float("nan"), 0
-    pos = q / 100.0 * (ns - 1)
-    lo = int(math.floor(pos))
-    t = pos - lo
-    a = distributed_order_statistic(sorted_local, lo, group)
-    b = a
-    if lo + 1 < ns:
-        av = torch.tensor([a], dtype=torch.float64, device=dev)
-        i_gt = torch.searchsorted(sorted_local, av, right=True)     # local count of values <= a
-        c_le = i_gt.clone()
-        nxt = torch.where(i_gt < sorted_local.numel(), sorted_local[i_gt.clamp(max=max(sorted_local.numel() - 1, 0))]
-                          if sorted_local.numel() else av, torch.full_like(av, float("inf")))
-        if dist.is_initialized():
-            dist.all_reduce(c_le, op=dist.ReduceOp.SUM, group=group)
-            dist.all_reduce(nxt, op=dist.ReduceOp.MIN, group=group)
-        b = a if int(c_le.item()) >= lo + 2 else float(nxt.item())
-    diff = b - a
-    v = a + diff * t
+    if overflow:                                                   # a window did not fit: exact radix select instead
+        va = distributed_order_statistic(sorted_local, lo, group)
+        vb = distributed_order_statistic(sorted_local, min(lo + 1, ns - 1), group)
+    t = q / 100.0 * (ns - 1) - lo
+    diff = vb - va
+    v = va + diff * t
     if t >= 0.5:
-        v = b - diff * (1.0 - t)
+        v = vb - diff * (1.0 - t)
     return v, ns
 
 
@@ -211,6 +260,11 @@ class DistributedSession(object):
         self.w = None
         self.halo_redo = 0
         self.hmax = 0.0
+        nt = torch.tensor([float(self.n_own)], dtype=torch.float64, device=self.device)
+        dist.all_reduce(nt, op=dist.ReduceOp.SUM, group=group)
+        self.n_total = int(nt.item())
+        # window size of the percentile's last gather: 3 pivot gaps of a rank holding 1.5x its share
+        self._cap_hint = 3 * int(math.ceil(1.5 * self.n_total / dist.get_world_size(group) / 1023.0)) + 64
 
     # -- construction helpers -----------------------------------------------------------------
     @classmethod
@@ -248,10 +302,13 @@ class DistributedSession(object):
         return float(t.item())
 
     def _refresh_ghosts(self, name):
-        """Overwrite the ghosts' `name` with their owners' current values."""
-        full = self.sess.download_tensor(name)
-        full[self.n_own:] = self.ex.update_ghosts(full[:self.n_own])
-        self.sess.upload_tensor(name, full)
+        """Overwrite the ghosts' `name` with their owners' current values: gather at the send lists,
+        one all_to_all, scatter into the ghost slots (no full-array traffic)."""
+        send = self.sess.gather(name, self._send_cat)
+        recv = torch.empty((self._n_ghost, send.shape[1]), dtype=torch.float64, device=self.device)
+        dist.all_to_all_single(recv, send, output_split_sizes=self.ex.recv_counts, input_split_sizes=self._send_counts,
+                               group=self.group)
+        self.sess.scatter(name, self._ghost_idx, recv)
 
     # -- (re)building the local particle set ----------------------------------------------------
     def _open_session(self, rows, w):
@@ -261,24 +318,22 @@ class DistributedSession(object):
         self.rows = rows
         self.n_own = int(rows.shape[0])
         s = self._Session(int(local.shape[0]), self.k, self.dist_cut, device=self.device.index, dt_0=self.dt_0)
-        for name in STATE_FIELDS + ("knn_h",):
-            a, b = COLS[name]
-            col = local[:, a:b].contiguous() if b - a > 1 else local[:, a].contiguous()
-            s.upload_tensor(name, col)
+        s.upload_rows(local)
         for name, v in (("age", self.age), ("d", self.d), ("dt", self.dt), ("ct", self.ct), ("n_owned", self.n_own)):
             s.set_scalar(name, v)
         self.gid = local[:, 18].contiguous()
+        self._send_cat = torch.cat(self.ex.send_idx)
+        self._send_counts = [int(i.numel()) for i in self.ex.send_idx]
+        self._n_ghost = int(ghosts.shape[0])
+        self._ghost_idx = torch.arange(self.n_own, self.n_own + self._n_ghost, dtype=torch.int64, device=self.device)
         self.sess = s
         self.w = w
 
     def _owned_rows(self):
         """Current owned rows (state columns + trial radius + gid) out of the session."""
-        cols = []
-        for name in STATE_FIELDS + ("knn_h",):
-            t = self.sess.download_tensor(name)[:self.n_own]
-            cols.append(t if t.dim() == 2 else t[:, None])
-        cols.append(self.gid[:self.n_own, None])
-        return torch.cat(cols, dim=1)
+        rows = self.sess.download_rows(self.n_own, NCOL)
+        rows[:, 18] = self.gid[:self.n_own]
+        return rows
 
     def _initial_halo_width(self, rows):
         """1.6 x the k-th-neighbour distance expected at the mean number density of the global box."""
@@ -299,10 +354,10 @@ class DistributedSession(object):
             self.sess.phase("knn")
             h = self.sess.download_tensor("sizes")[:self.n_own]
             x = self.sess.download_tensor("points")[:self.n_own, 0]
-            bad = float((~self.ex.covered(x, h)).sum().item())
-            hmax = float(h.max().item()) if self.n_own else 0.0
-            bad = self._allreduce(bad, dist.ReduceOp.SUM)
-            self.hmax = self._allreduce(hmax, dist.ReduceOp.MAX)
+            chk = torch.stack([(~self.ex.covered(x, h)).any().to(torch.float64),
+                               h.max() if self.n_own else torch.zeros((), dtype=torch.float64, device=self.device)])
+            dist.all_reduce(chk, op=dist.ReduceOp.MAX, group=self.group)            # one collective, one host sync
+            bad, self.hmax = chk.tolist()
             if bad == 0:
                 break
             self.halo_redo += 1
@@ -323,12 +378,15 @@ class DistributedSession(object):
         if name == "crossing":
             self._refresh_ghosts("velocities")                    # nsc:780 needs the neighbours' current velocities
             s.phase("crossing")
-            self.ct = self._allreduce(s.scalar("ct"), dist.ReduceOp.MIN)
-            s.set_scalar("ct", self.ct)
+            ct = s.download_raw("scalar:ct", 1)                    # device scalar, reduced in place: no host sync
+            dist.all_reduce(ct, op=dist.ReduceOp.MIN, group=self.group)
+            s.upload_raw("scalar:ct", ct)
+            self._ct_dev = ct
         elif name == "dt_clamp":
             s.phase("dt_clamp")
         elif name == "exchange":
-            self.age, self.dt = s.scalar("age"), s.scalar("dt")
+            sc = s.download_raw("scalars", 12).tolist()            # one host sync for ct, dt, age
+            self.ct, self.dt, self.age = sc[6], sc[7], sc[9]
             rows = self.ex.migrate(self._owned_rows())
             self._open_session(rows, 1.25 * self.hmax)
         elif name == "sort":
@@ -347,9 +405,9 @@ class DistributedSession(object):
             s.phase("force")
         elif name == "integrate":
             s.phase("kick")
-            dsq = s.download_tensor("dist_sq")[:self.n_own]
-            slow = torch.sort(dsq[torch.isfinite(dsq)]).values
-            v, ns = distributed_percentile(slow, 90.0, self.group)             # code_running.py:515-518
+            s.phase("length")                                      # local sort of the owned slow particles' |x|^2
+            slow = s.download_raw("dist_sq_sorted", int(s.download_raw("scalars", 12)[11].item()))
+            v, ns = distributed_percentile(slow, 90.0, self.group, cap_hint=self._cap_hint)   # code_running.py:515-518
             self.n_slow, self.max_dist = ns, v
             self.d = (v ** 1.5 / ns / 0.9 * self.C.N_INT_PER_PARTICLE) ** (1. / 3.) if ns else float("nan")   # :520-521
             s.set_scalar("d", self.d)
@@ -375,9 +433,7 @@ class DistributedSession(object):
         return self.sess.launches()               # the context's counter is cumulative across sessions
 
     def scalar(self, name):
-        if name in ("ct", "d"):
-            return {"ct": self.ct, "d": self.d}[name]
-        return self.sess.scalar(name)
+        return self.d if name == "d" else self.sess.scalar(name)
 
     # -- host-resident state (bench.py's e2e leg) ------------------------------------------------
     def make_host_state(self, upload_fields=None, download_fields=None):
@@ -392,11 +448,9 @@ class DistributedSession(object):
         """One step of a host-resident slab: the owned rows are uploaded from pinned memory into the
         session, the step runs (with its exchanges), the new owned rows come back to pinned memory."""
         rows = hs["buf"][:hs["n"]].to(self.device, non_blocking=True)
-        for name in STATE_FIELDS + ("knn_h",):
-            a, b = COLS[name]
-            full = self.sess.download_tensor(name)
-            full[:self.n_own] = rows[:, a:b] if b - a > 1 else rows[:, a]
-            self.sess.upload_tensor(name, full)
+        full = self.sess.download_rows(self.sess.n, NCOL)          # ghosts keep their rows (refreshed in the step)
+        full[:self.n_own] = rows
+        self.sess.upload_rows(full)
         self.step()
         out = self._owned_rows()
         if out.shape[0] > hs["buf"].shape[0]:

@@ -76,6 +76,43 @@ class Session(object):
                                                      out.numel(), self._stream()))
         return out
 
+    def download_raw(self, name, count):
+        """First `count` doubles of an internal array that has no particle order ("dist_sq_sorted")."""
+        out = torch.empty((count,), dtype=torch.float64, device=self.device)
+        _lib.check(self.lib.sphb200_session_download(self.ctx.handle, name.encode(), ctypes.c_void_p(out.data_ptr()),
+                                                     int(count), self._stream()))
+        return out
+
+    def upload_raw(self, name, t):
+        """Device-to-device write of "scalar:<name>" from a 1-element float64 CUDA tensor (no host sync)."""
+        _lib.check(self.lib.sphb200_session_upload(self.ctx.handle, name.encode(), ctypes.c_void_p(t.data_ptr()),
+                                                   int(t.numel()), self._stream()))
+
+    def gather(self, name, idx):
+        """Field `name` at caller indices idx (int64 CUDA tensor) -> (len(idx), width) float64 tensor."""
+        w = STATE_FIELDS.get(name) or RESULT_FIELDS.get(name) or AUX_FIELDS[name]
+        out = torch.empty((idx.numel(), w), dtype=torch.float64, device=self.device)
+        _lib.check(self.lib.sphb200_session_gather(self.ctx.handle, name.encode(), ctypes.c_void_p(idx.data_ptr()),
+                                                   int(idx.numel()), ctypes.c_void_p(out.data_ptr()), self._stream()))
+        return out
+
+    def scatter(self, name, idx, values):
+        _lib.check(self.lib.sphb200_session_scatter(self.ctx.handle, name.encode(), ctypes.c_void_p(idx.data_ptr()),
+                                                    int(idx.numel()), ctypes.c_void_p(values.data_ptr()), self._stream()))
+
+    def download_rows(self, n_rows, ncol):
+        """(n_rows, ncol) float64 CUDA tensor: state fields + trial radius of caller rows [0, n_rows)."""
+        out = torch.zeros((n_rows, ncol), dtype=torch.float64, device=self.device)
+        _lib.check(self.lib.sphb200_session_download_rows(self.ctx.handle, ctypes.c_void_p(out.data_ptr()), int(n_rows),
+                                                          int(ncol), self._stream()))
+        return out
+
+    def upload_rows(self, rows):
+        if rows.shape[0] != self.n or rows.dtype != torch.float64 or not rows.is_cuda or not rows.is_contiguous():
+            raise ValueError("upload_rows needs a contiguous float64 CUDA tensor of %d rows" % self.n)
+        _lib.check(self.lib.sphb200_session_upload_rows(self.ctx.handle, ctypes.c_void_p(rows.data_ptr()), self.n,
+                                                        int(rows.shape[1]), self._stream()))
+
     def download(self, name):
         return self.download_tensor(name).cpu().numpy()
 
