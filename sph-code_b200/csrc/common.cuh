@@ -43,6 +43,16 @@ extern thread_local char g_sphb200_err[SPHB200_MAX_ERR];
 // ---------------------------------------------------------------------------------------------
 struct __align__(16) rec2 { double a, b; };
 
+#ifdef __CUDACC__
+// One 256-bit read-only load of a 32-byte record (LDG.E.256 on sm_100a): a gathered neighbour costs one
+// L1 tag lookup per record instead of the two of a pair of 128-bit loads.  p must be 32-byte aligned.
+__device__ __forceinline__ double4 ldg256(const double4* p) {
+  double4 v;
+  asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v.x), "=d"(v.y), "=d"(v.z), "=d"(v.w) : "l"(p));
+  return v;
+}
+#endif
+
 struct PhysConst { double kB, amu; };
 
 struct GridSpec {

@@ -96,8 +96,8 @@ density_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __
   for (int s = lane; s < k; s += G) {
     const int j = row[s];
     if (j < 0 || j >= n) continue;
-    const double4 q = r0[j];
-    const double4 w = r1[j];
+    const double4 q = ldg256(r0 + j);
+    const double4 w = ldg256(r1 + j);
     const double dx = q.x - ps.x, dy = q.y - ps.y, dz = q.z - ps.z;
     const double r2 = dx * dx + dy * dy + dz * dz;
     const double t = q.w - r2;
@@ -144,8 +144,8 @@ pi_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __restr
   for (int s = lane; s < k; s += G) {
     const int j = row[s];
     if (j < 0 || j >= n) continue;
-    const double4 q = r0[j];
-    const double4 v = r2[j];
+    const double4 q = ldg256(r0 + j);
+    const double4 v = ldg256(r2 + j);
     const double dx = q.x - ps.x, dy = q.y - ps.y, dz = q.z - ps.z;
     const double dvx = v.x - vs.x, dvy = v.y - vs.y, dvz = v.z - vs.z;
     const double r2_ = dx * dx + dy * dy + dz * dz;
@@ -217,8 +217,8 @@ force_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __re
   for (int s = lane; s < k; s += G) {
     const int j = row[s];
     if (j < 0 || j >= n) continue;
-    const double4 q = r0[j];
-    const double4 v = r2[j];
+    const double4 q = ldg256(r0 + j);
+    const double4 v = ldg256(r2 + j);
     const rec2 cj = r3[j];
     const double dx = q.x - ps.x, dy = q.y - ps.y, dz = q.z - ps.z;
     const double r2_ = dx * dx + dy * dy + dz * dz;
@@ -276,8 +276,8 @@ species_kernel(int n, int k, int S, const int32_t* __restrict__ list, const doub
     for (int s = 0; s < k; ++s) {
       const int j = row[s];
       if (j < 0 || j >= n) continue;
-      const double4 q = r0[j];
-      const double4 w = r1[j];
+      const double4 q = ldg256(r0 + j);
+      const double4 w = ldg256(r1 + j);
       const double dx = q.x - ps.x, dy = q.y - ps.y, dz = q.z - ps.z;
       const double t = q.w - (dx * dx + dy * dy + dz * dz);
       double W = w.x * (t * t * t);
@@ -327,7 +327,7 @@ crossing_kernel(int n, int k, const int32_t* __restrict__ list, const double4* _
   for (int s = lane; s < k; s += G) {
     const int j = row[s];
     if (j < 0 || j >= n) continue;
-    const double4 vj = vrec[j];
+    const double4 vj = ldg256(vrec + j);
     const double ax = vj.x - vi.x, ay = vj.y - vi.y, az = vj.z - vi.z;
     const double v2 = ax * ax + ay * ay + az * az;
     if (v2 != v2) nan = true;                           // np.max propagates NaN
