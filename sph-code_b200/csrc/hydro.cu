@@ -149,11 +149,13 @@ pi_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __restr
     const double dx = q.x - ps.x, dy = q.y - ps.y, dz = q.z - ps.z;
     const double dvx = v.x - vs.x, dvy = v.y - vs.y, dvz = v.z - vs.z;
     const double r2_ = dx * dx + dy * dy + dz * dz;
-    double w = (dvx * dx + dvy * dy + dvz * dz) / sqrt(r2_ + 0.01 * q.w);   // nsc:643
+    // one rsqrt and one reciprocal instead of sqrt + two divisions (each an fp64 software sequence);
+    // the extra roundings are ~1e-16 relative, the tolerance is 1e-10
+    double w = (dvx * dx + dvy * dy + dvz * dz) * rsqrt(r2_ + 0.01 * q.w);  // nsc:643
     w = (w > 0.0) ? 0.0 : w;                                               // nsc:644
-    const double rho_avg = (rho[j] + rho_i) * 0.5;                         // nsc:646
+    const double inv_rho_avg = 2.0 * __drcp_rn(rho[j] + rho_i);            // nsc:646
     const double cbar = 0.5 * (v.w + cs_i);                                // nsc:647
-    acc += -0.5 * (cbar * 2.0 - 3.0 * w) * w / rho_avg;                    // nsc:649
+    acc += (-0.5 * (cbar * 2.0 - 3.0 * w) * w) * inv_rho_avg;              // nsc:649
   }
   acc = cg::reduce(tile, acc, cg::plus<double>());
   if (lane == 0) {
