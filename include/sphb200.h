@@ -88,6 +88,9 @@ int sphb200_artificial_viscosity(sphb200_ctx* ctx, int64_t n, int k, const int64
  * "visc_accel", "pressure_accel" (N,3); "neighbor" (N,k) int64; "num_nontrivial" (N) int64.
  * upload/download take DEVICE pointers in the caller's particle order. */
 int sphb200_session_create(sphb200_ctx* ctx, int64_t n, int k, double dist);
+/* same run, new particle set of n particles (the first n_owned are owned, the rest ghosts; -1 = all owned):
+ * keeps k, dist, run parameters and device scalars; fill the arrays with sphb200_session_upload_rows */
+int sphb200_session_resize(sphb200_ctx* ctx, int64_t n, int64_t n_owned, void* stream);
 int sphb200_session_upload(sphb200_ctx* ctx, const char* field, const void* src, int64_t count, void* stream);
 int sphb200_session_download(sphb200_ctx* ctx, const char* field, void* dst, int64_t count, void* stream);
 /* Whole particle rows, (n_rows, ncol >= 18) doubles in the caller's order: columns 0-16 are the eleven

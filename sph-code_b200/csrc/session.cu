@@ -296,34 +296,55 @@ scatter_at_kernel(int64_t count, int w, int n, const int64_t* __restrict__ cidx,
 struct RowArgs { double* f[F_NFIELDS]; double* knnh; };
 #define ROW_STATE_COLS 18
 
+// One warp per 32 sorted particles: the 18 values of each particle are read field by field (coalesced)
+// into shared memory, then every row goes out as one contiguous 144-byte piece (lanes 0..17).
 __global__ void __launch_bounds__(256)
 rows_out_kernel(int n, int64_t n_rows, int ncol, const uint32_t* __restrict__ id, RowArgs a, double* __restrict__ dst) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const int64_t c = id[i];
-  if (c >= n_rows) return;
-  double* o = dst + c * ncol;
-  int col = 0;
+  __shared__ double tile[8][32][ROW_STATE_COLS + 1];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int base = (blockIdx.x * 8 + warp) * 32;
+  if (base >= n) return;
+  const int i = base + lane;
+  int64_t c = -1;
+  if (i < n) {
+    c = id[i];
+    int col = 0;
 #pragma unroll
-  for (int f = 0; f < 3; ++f)
-    for (int q = 0; q < 3; ++q) o[col++] = a.f[f][3 * (int64_t)i + q];
+    for (int f = 0; f < 3; ++f)
+      for (int q = 0; q < 3; ++q) tile[warp][lane][col++] = a.f[f][3 * (int64_t)i + q];
 #pragma unroll
-  for (int f = 3; f < F_NFIELDS; ++f) o[col++] = a.f[f][i];
-  o[col] = a.knnh[i];
+    for (int f = 3; f < F_NFIELDS; ++f) tile[warp][lane][col++] = a.f[f][i];
+    tile[warp][lane][col] = a.knnh[i];
+  }
+  __syncwarp();
+  for (int r = 0; r < 32; ++r) {
+    const int64_t cr = __shfl_sync(0xffffffffu, c, r);
+    if (cr >= 0 && cr < n_rows && lane < ROW_STATE_COLS) dst[cr * ncol + lane] = tile[warp][r][lane];
+  }
 }
 
 __global__ void __launch_bounds__(256)
 rows_in_kernel(int n, int ncol, const uint32_t* __restrict__ id, const double* __restrict__ src, RowArgs a) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const double* r = src + (int64_t)id[i] * ncol;
-  int col = 0;
+  __shared__ double tile[8][32][ROW_STATE_COLS + 1];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int base = (blockIdx.x * 8 + warp) * 32;
+  if (base >= n) return;
+  const int i = base + lane;
+  const int64_t c = (i < n) ? (int64_t)id[i] : -1;
+  for (int r = 0; r < 32; ++r) {
+    const int64_t cr = __shfl_sync(0xffffffffu, c, r);
+    if (cr >= 0 && lane < ROW_STATE_COLS) tile[warp][r][lane] = src[cr * ncol + lane];
+  }
+  __syncwarp();
+  if (i < n) {
+    int col = 0;
 #pragma unroll
-  for (int f = 0; f < 3; ++f)
-    for (int q = 0; q < 3; ++q) a.f[f][3 * (int64_t)i + q] = r[col++];
+    for (int f = 0; f < 3; ++f)
+      for (int q = 0; q < 3; ++q) a.f[f][3 * (int64_t)i + q] = tile[warp][lane][col++];
 #pragma unroll
-  for (int f = 3; f < F_NFIELDS; ++f) a.f[f][i] = r[col++];
-  a.knnh[i] = r[col];
+    for (int f = 3; f < F_NFIELDS; ++f) a.f[f][i] = tile[warp][lane][col++];
+    a.knnh[i] = tile[warp][lane][col];
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -505,6 +526,37 @@ int sphb200_session_create(sphb200_ctx* ctx, int64_t n, int k, double dist) {
   iota_kernel<<<ceil_div(n, 256), 256>>>((int)n, bufp<uint32_t>(ctx->sbuf[SB_ID]));
   CUDA_TRY(cudaMemset(ctx->scal.p, 0, SC_COUNT * sizeof(double)));
   CUDA_TRY(cudaDeviceSynchronize());
+  return 0;
+}
+
+// Same run, different particle set: the slab decomposition rebuilds its local set (owned + ghosts)
+// every step.  Keeps k, dist, the run parameters and the device scalars (age, dt, ct, d); the state
+// arrays are to be filled by sphb200_session_upload_rows (nothing is cleared, nothing synchronises).
+int sphb200_session_resize(sphb200_ctx* ctx, int64_t n, int64_t n_owned, void* stream) {
+  if (!ctx) SPH_FAIL("null context");
+  if (n <= 0 || n >= (int64_t)0x7fffffff) SPH_FAIL("session_resize: bad particle count %lld", (long long)n);
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  Session& s = sess(ctx);
+  if (s.k <= 0) SPH_FAIL("session_resize: no session to resize");
+  s.n = n; s.n_owned = n_owned;
+  s.has_list = 0; s.pos_valid = 0; s.id_cur = 0; s.knnh_cur = 0;
+  for (int f = 0; f < F_NFIELDS; ++f) {
+    s.cur[f] = 0;
+    SPH_TRY(devbuf_reserve(ctx->sbuf[2 * f], (size_t)n * kFieldWidth[f] * sizeof(double)));
+    SPH_TRY(devbuf_reserve(ctx->sbuf[2 * f + 1], (size_t)n * kFieldWidth[f] * sizeof(double)));
+  }
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_ID], n * sizeof(uint32_t)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_ID_ALT], n * sizeof(uint32_t)));
+  for (int o = 0; o < O_NOUT; ++o) SPH_TRY(devbuf_reserve(ctx->sbuf[SB_OUT + o], (size_t)n * kOutWidth[o] * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_NONTRIV], n * sizeof(int32_t)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_DISTSQ], n * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_DISTSQ_ALT], n * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_KNNH], n * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_KNNH_ALT], n * sizeof(double)));
+  iota_kernel<<<ceil_div(n, 256), 256, 0, st>>>((int)n, bufp<uint32_t>(ctx->sbuf[SB_ID]));
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
   return 0;
 }
 

@@ -63,19 +63,23 @@ class SlabExchange(object):
         self.w = None
 
     # -- plumbing -----------------------------------------------------------------------------
-    def _all_to_all_rows(self, parts, recv_counts=None):
-        """parts[r] = rows for rank r.  Returns (received rows, counts per source rank)."""
-        dev, dtype = parts[0].device, parts[0].dtype
-        ncol = parts[0].shape[1]
-        send_counts = [int(p.shape[0]) for p in parts]
+    def _all_to_all_rows(self, parts, recv_counts=None, send_counts=None):
+        """parts[r] = rows for rank r (or one tensor already ordered by destination, with `send_counts`).
+        Returns (received rows, counts per source rank).  One host sync when the counts are unknown."""
+        if send_counts is None:
+            send = torch.cat(parts, dim=0).contiguous()
+            sc = torch.tensor([int(p.shape[0]) for p in parts], dtype=torch.int64, device=send.device)
+        else:
+            send, sc = parts.contiguous(), send_counts                 # sc: device int64 tensor [world]
         if recv_counts is None:
-            sc = torch.tensor(send_counts, dtype=torch.int64, device=dev)
             rc = torch.empty_like(sc)
             dist.all_to_all_single(rc, sc, group=self.group)
-            recv_counts = [int(v) for v in rc.tolist()]
-        send = torch.cat(parts, dim=0).contiguous()
-        recv = torch.empty((sum(recv_counts), ncol), dtype=dtype, device=dev)
-        dist.all_to_all_single(recv, send, output_split_sizes=recv_counts, input_split_sizes=send_counts, group=self.group)
+            both = torch.cat([sc, rc]).tolist()                        # the one sync
+            send_list, recv_counts = both[:self.world], both[self.world:]
+        else:
+            send_list = sc.tolist() if torch.is_tensor(sc) else list(sc)
+        recv = torch.empty((sum(recv_counts), send.shape[1]), dtype=send.dtype, device=send.device)
+        dist.all_to_all_single(recv, send, output_split_sizes=recv_counts, input_split_sizes=send_list, group=self.group)
         return recv, recv_counts
 
     def owner_of(self, x):
@@ -91,9 +95,8 @@ class SlabExchange(object):
         mv = torch.nonzero(~stay, as_tuple=False).flatten()
         mdest = dest[mv]
         order = torch.argsort(mdest, stable=True)
-        counts = torch.bincount(mdest, minlength=self.world).tolist()
-        parts = list(torch.split(rows[mv[order]], counts, dim=0))
-        recv, _ = self._all_to_all_rows(parts)
+        counts = torch.bincount(mdest, minlength=self.world)           # stays on the device
+        recv, _ = self._all_to_all_rows(rows[mv[order]], send_counts=counts)
         return torch.cat([rows[stay], recv], dim=0) if recv.shape[0] else rows[stay]
 
     def build_halo(self, rows, w):
@@ -116,7 +119,7 @@ class SlabExchange(object):
         """owned_values (n_own, c): returns the owners' current values for this rank's ghosts, in ghost order."""
         v = owned_values if owned_values.dim() == 2 else owned_values[:, None]
         parts = [v[i] for i in self.send_idx]
-        recv, _ = self._all_to_all_rows(parts, self.recv_counts)
+        recv, _ = self._all_to_all_rows(parts, self.recv_counts, None)
         return recv if owned_values.dim() == 2 else recv[:, 0]
 
     def covered(self, x, h):
@@ -160,60 +163,58 @@ def distributed_order_statistic(sorted_local, k, group=None):
     return torch.tensor([prefix], dtype=torch.int64).view(torch.float64).item()
 
 
-def distributed_percentile(sorted_local, q=90.0, group=None, pivots=1024, cap_hint=None):
-    """numpy.percentile(values, q) (linear interpolation, numpy's _lerp) of the union of all ranks'
-    ascending `sorted_local`; returns (percentile, global count).  code_running.py:515-518.
+def percentile_on_device(sorted_local, q=90.0, group=None, pivots=1024, cap=None):
+    """Core of `distributed_percentile`, free of host synchronisation.  `sorted_local` is ascending and may
+    be padded with +inf at the end (entries that do not take part).  Returns a float64 tensor
+    [value at rank lo, value at rank lo+1, global count, lo, window-overflow flag].
 
-    Exact selection in three small collectives and one host sync: (1) all_gather `pivots` evenly spaced
-    local order statistics per rank; (2) all_reduce the local counts below / up to every pivot, which
-    brackets the two wanted global ranks between neighbouring pivots a <= b; (3) all_gather the few
-    local elements inside [a, b] (at most ~2 pivot gaps per rank) and pick the two order statistics
-    from their merge.  Falls back to the radix select if a rank holds too many duplicates of a or b."""
+    Exact selection in three small collectives: (1) all_gather `pivots` evenly spaced local order
+    statistics per rank; (2) all_reduce the local counts below / up to every pivot, which brackets the
+    two wanted global ranks between neighbouring pivots a <= b; (3) all_gather the few local elements
+    inside [a, b] (at most ~2 pivot gaps per rank, `cap` slots) and pick the two order statistics from
+    their merge."""
     dev = sorted_local.device
     world = dist.get_world_size(group) if dist.is_initialized() else 1
-    n_loc = sorted_local.numel()
     P = pivots
-    inf = torch.full((1,), float("inf"), dtype=torch.float64, device=dev)
-    if n_loc:
-        pidx = torch.linspace(0, n_loc - 1, P, dtype=torch.float64, device=dev).round().to(torch.int64)
-        mine = torch.cat([sorted_local[pidx], torch.full((1,), float(n_loc), dtype=torch.float64, device=dev)])
-    else:
-        mine = torch.cat([inf.expand(P), torch.zeros(1, dtype=torch.float64, device=dev)])
+    f64 = dict(dtype=torch.float64, device=dev)
+    inf = torch.full((1,), float("inf"), **f64)
+    if sorted_local.numel() == 0:
+        sorted_local = inf
+    n_loc = torch.searchsorted(sorted_local, inf)[0]                          # finite entries (device scalar)
+    last = (n_loc - 1).clamp(min=0)
+    pidx = torch.round(torch.arange(P, **f64) / (P - 1) * last.to(torch.float64)).to(torch.int64)
+    mine = torch.cat([torch.where(n_loc > 0, sorted_local[pidx], inf.expand(P)), n_loc.to(torch.float64).reshape(1)])
     if world > 1:
-        allp = torch.empty(world * (P + 1), dtype=torch.float64, device=dev)
+        allp = torch.empty(world * (P + 1), **f64)
         dist.all_gather_into_tensor(allp, mine.contiguous(), group=group)
         allp = allp.view(world, P + 1)
     else:
         allp = mine[None, :]
     piv = allp[:, :P].reshape(-1)
-    cnt = torch.cat([torch.searchsorted(sorted_local, piv), torch.searchsorted(sorted_local, piv, right=True)])
+    finite = sorted_local                                                      # +inf padding sorts after every pivot
+    cnt = torch.cat([torch.searchsorted(finite, piv), torch.minimum(torch.searchsorted(finite, piv, right=True), n_loc)])
     if world > 1:
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=group)
     c_lt, c_le = cnt[:world * P], cnt[world * P:]
-    counts = allp[:, P]
-    ns_t = counts.sum().to(torch.int64)
+    ns_t = allp[:, P].sum().to(torch.int64)
     pos_lo = torch.floor(q / 100.0 * (ns_t - 1).to(torch.float64)).to(torch.int64).clamp(min=0)
     pos_hi = torch.minimum(pos_lo + 1, (ns_t - 1).clamp(min=0))
-    # a = largest pivot with fewer than pos_lo+1 elements below it; b = smallest pivot with > pos_hi elements up to it
+    # a = largest pivot with at most pos_lo elements below it; b = smallest pivot with more than pos_hi elements up to it
     a = torch.where(c_lt <= pos_lo, piv, -inf).max()
-    b = torch.where(c_le >= pos_hi + 1, piv, inf).min()
-    base = torch.where((piv == a), c_lt, torch.zeros_like(c_lt)).max()          # global count of elements < a
-    i0 = torch.searchsorted(sorted_local, a.reshape(1))[0]
-    i1 = torch.searchsorted(sorted_local, b.reshape(1), right=True)[0]
-    # fixed-size window (no host sync): cap elements starting at i0, +inf beyond i1
-    cap = 3 * int(math.ceil(max(float(n_loc), 1.0) / max(P - 1, 1))) + 64
-    if cap_hint is not None:                                       # same on every rank by construction: no collective
-        cap = int(cap_hint)
-    elif world > 1:
-        capt = torch.tensor([cap], dtype=torch.int64, device=dev)
-        dist.all_reduce(capt, op=dist.ReduceOp.MAX, group=group)
+    b = torch.where((c_le >= pos_hi + 1) & (piv < float("inf")), piv, inf).min()
+    base = torch.where(piv == a, c_lt, torch.zeros_like(c_lt)).max()           # global count of elements < a
+    i0 = torch.searchsorted(finite, a.reshape(1))[0]
+    i1 = torch.minimum(torch.searchsorted(finite, b.reshape(1), right=True)[0], n_loc)
+    if cap is None:                                                            # needs the largest local count: one collective + sync
+        capt = (3 * torch.ceil(n_loc.to(torch.float64) / max(P - 1, 1)) + 64).to(torch.int64).reshape(1)
+        if world > 1:
+            dist.all_reduce(capt, op=dist.ReduceOp.MAX, group=group)
         cap = int(capt.item())
     widx = i0 + torch.arange(cap, dtype=torch.int64, device=dev)
-    vals = sorted_local[widx.clamp(max=max(n_loc - 1, 0))] if n_loc else inf.expand(cap)
-    win = torch.where(widx < i1, vals, inf.expand(cap))
-    win = torch.cat([win, (i1 - i0).to(torch.float64).reshape(1)])
+    vals = sorted_local[torch.minimum(widx, torch.tensor(sorted_local.numel() - 1, dtype=torch.int64, device=dev))]
+    win = torch.cat([torch.where(widx < i1, vals, inf.expand(cap)), (i1 - i0).to(torch.float64).reshape(1)])
     if world > 1:
-        allw = torch.empty(world * (cap + 1), dtype=torch.float64, device=dev)
+        allw = torch.empty(world * (cap + 1), **f64)
         dist.all_gather_into_tensor(allw, win.contiguous(), group=group)
         allw = allw.view(world, cap + 1)
     else:
@@ -221,20 +222,32 @@ def distributed_percentile(sorted_local, q=90.0, group=None, pivots=1024, cap_hi
     merged = torch.sort(allw[:, :cap].reshape(-1)).values
     k0 = (pos_lo - base).clamp(min=0, max=merged.numel() - 1)
     k1 = (pos_hi - base).clamp(min=0, max=merged.numel() - 1)
-    res = torch.stack([merged[k0], merged[k1], ns_t.to(torch.float64), pos_lo.to(torch.float64),
-                       (allw[:, cap] > cap).any().to(torch.float64)]).tolist()          # the one host sync
-    va, vb, ns, lo, overflow = res[0], res[1], int(res[2]), int(res[3]), res[4] != 0.0
-    if ns == 0:
-        return float("nan"), 0
-    if overflow:                                                   # a window did not fit: exact radix select instead
-        va = distributed_order_statistic(sorted_local, lo, group)
-        vb = distributed_order_statistic(sorted_local, min(lo + 1, ns - 1), group)
+    return torch.stack([merged[k0], merged[k1], ns_t.to(torch.float64), pos_lo.to(torch.float64),
+                        (allw[:, cap] > cap).any().to(torch.float64)])
+
+
+def lerp_percentile(va, vb, ns, lo, q=90.0):
+    """numpy's _lerp between the two order statistics (works on floats and on tensors)."""
     t = q / 100.0 * (ns - 1) - lo
     diff = vb - va
-    v = va + diff * t
-    if t >= 0.5:
-        v = vb - diff * (1.0 - t)
-    return v, ns
+    if torch.is_tensor(t):
+        return torch.where(t >= 0.5, vb - diff * (1.0 - t), va + diff * t)
+    return vb - diff * (1.0 - t) if t >= 0.5 else va + diff * t
+
+
+def distributed_percentile(sorted_local, q=90.0, group=None, pivots=1024, cap_hint=None):
+    """numpy.percentile(values, q) (linear interpolation) of the union of all ranks' ascending
+    `sorted_local`; returns (percentile, global count) as Python numbers.  code_running.py:515-518.
+    Falls back to the radix select when a rank holds too many duplicates of a bracket value."""
+    va, vb, ns, lo, overflow = percentile_on_device(sorted_local, q, group, pivots, cap_hint).tolist()
+    ns, lo = int(ns), int(lo)
+    if ns == 0:
+        return float("nan"), 0
+    if overflow:
+        fin = sorted_local[torch.isfinite(sorted_local)]
+        va = distributed_order_statistic(fin, lo, group)
+        vb = distributed_order_statistic(fin, min(lo + 1, ns - 1), group)
+    return lerp_percentile(va, vb, ns, lo, q), ns
 
 
 class DistributedSession(object):
@@ -256,10 +269,11 @@ class DistributedSession(object):
         self.rows = rows.to(self.device).contiguous()             # owned rows until the first session exists
         self.sess = None
         self.n_own = int(self.rows.shape[0])
-        self.age, self.dt, self.d, self.ct = 0.0, self.dt_0, float(C.d_default), 0.0
+        self.d = float(C.d_default)
         self.w = None
         self.halo_redo = 0
         self.hmax = 0.0
+        self._pct_overflow = None
         nt = torch.tensor([float(self.n_own)], dtype=torch.float64, device=self.device)
         dist.all_reduce(nt, op=dist.ReduceOp.SUM, group=group)
         self.n_total = int(nt.item())
@@ -317,10 +331,14 @@ class DistributedSession(object):
         local = torch.cat([rows, ghosts], dim=0).contiguous()
         self.rows = rows
         self.n_own = int(rows.shape[0])
-        s = self._Session(int(local.shape[0]), self.k, self.dist_cut, device=self.device.index, dt_0=self.dt_0)
+        if self.sess is None:
+            s = self._Session(int(local.shape[0]), self.k, self.dist_cut, device=self.device.index, dt_0=self.dt_0)
+            for name, v in (("age", 0.0), ("d", self.d), ("dt", self.dt_0), ("ct", 0.0), ("n_owned", self.n_own)):
+                s.set_scalar(name, v)
+        else:
+            s = self.sess
+            s.resize(int(local.shape[0]), self.n_own)                  # keeps the device scalars: no host traffic
         s.upload_rows(local)
-        for name, v in (("age", self.age), ("d", self.d), ("dt", self.dt), ("ct", self.ct), ("n_owned", self.n_own)):
-            s.set_scalar(name, v)
         self.gid = local[:, 18].contiguous()
         self._send_cat = torch.cat(self.ex.send_idx)
         self._send_counts = [int(i.numel()) for i in self.ex.send_idx]
@@ -385,8 +403,6 @@ class DistributedSession(object):
         elif name == "dt_clamp":
             s.phase("dt_clamp")
         elif name == "exchange":
-            sc = s.download_raw("scalars", 12).tolist()            # one host sync for ct, dt, age
-            self.ct, self.dt, self.age = sc[6], sc[7], sc[9]
             rows = self.ex.migrate(self._owned_rows())
             self._open_session(rows, 1.25 * self.hmax)
         elif name == "sort":
@@ -405,12 +421,12 @@ class DistributedSession(object):
             s.phase("force")
         elif name == "integrate":
             s.phase("kick")
-            s.phase("length")                                      # local sort of the owned slow particles' |x|^2
-            slow = s.download_raw("dist_sq_sorted", int(s.download_raw("scalars", 12)[11].item()))
-            v, ns = distributed_percentile(slow, 90.0, self.group, cap_hint=self._cap_hint)   # code_running.py:515-518
-            self.n_slow, self.max_dist = ns, v
-            self.d = (v ** 1.5 / ns / 0.9 * self.C.N_INT_PER_PARTICLE) ** (1. / 3.) if ns else float("nan")   # :520-521
-            s.set_scalar("d", self.d)
+            s.phase("length")                                      # local sort: owned slow particles' |x|^2, then +inf
+            r = percentile_on_device(s.download_raw("dist_sq_sorted", s.n), 90.0, self.group, cap=self._cap_hint)
+            v, ns = lerp_percentile(r[0], r[1], r[2], r[3], 90.0), r[2]        # code_running.py:515-518
+            d = torch.pow(torch.pow(v, 1.5) / ns / 0.9 * self.C.N_INT_PER_PARTICLE, 1. / 3.)   # :520-521
+            s.upload_raw("scalar:d", d.reshape(1).contiguous())    # stays on the device: no host sync in this phase
+            self._pct_overflow = torch.maximum(self._pct_overflow, r[4]) if self._pct_overflow is not None else r[4]
             s.phase("smooth")
         else:
             raise ValueError("unknown phase %r" % name)
@@ -428,12 +444,14 @@ class DistributedSession(object):
 
     def check(self):
         self.sess.check()
+        if self._pct_overflow is not None and float(self._pct_overflow.item()) != 0.0:
+            raise RuntimeError("distributed percentile: a rank's window overflowed (too many equal |x|^2 values)")
 
     def launches(self):
         return self.sess.launches()               # the context's counter is cumulative across sessions
 
     def scalar(self, name):
-        return self.d if name == "d" else self.sess.scalar(name)
+        return self.sess.scalar(name)
 
     # -- host-resident state (bench.py's e2e leg) ------------------------------------------------
     def make_host_state(self, upload_fields=None, download_fields=None):

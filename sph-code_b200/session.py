@@ -35,6 +35,11 @@ class Session(object):
                           ("raise_factor", C.raise_factor), ("AU", C.AU)):
             self.set_scalar(name, val)
 
+    def resize(self, n, n_owned=-1):
+        """Same run, new particle set (slab decomposition): keeps scalars and run parameters."""
+        _lib.check(self.lib.sphb200_session_resize(self.ctx.handle, int(n), int(n_owned), self._stream()))
+        self.n = int(n)
+
     # -- plumbing ---------------------------------------------------------------------------
     def _stream(self):
         return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
