@@ -78,6 +78,16 @@ int sphb200_artificial_viscosity(sphb200_ctx* ctx, int64_t n, int k, const int64
                                  const double* gamma_array, const double* mu_array, double d, double* visc_accel,
                                  double* visc_heat, void* stream);
 
+/* ---- F1: net_impulse(points,mass,sizes,velocities,particle_type,neighbor,f_un)   nsc:719-742 ----
+ * Dust-gas drag: accel_onto (N,3) = sum over each row's dust neighbours with positive Weigh2_dust;
+ * accel_reaction (N,3) = the opposite push scattered onto those neighbours (self excluded).
+ * f_un is (N, n_species) row-major on the device; grain_mass_host / sigma_effective_host are the
+ * n_species-long HOST tables of nsc:69-79 (grain_mass(), sigma_effective()), n_species <= 64. */
+int sphb200_net_impulse(sphb200_ctx* ctx, int64_t n, int k, const int64_t* neighbor, const double* points,
+                        const double* mass, const double* sizes, const double* velocities,
+                        const double* particle_type, const double* f_un, int n_species, const double* grain_mass_host,
+                        const double* sigma_effective_host, double* accel_onto, double* accel_reaction, void* stream);
+
 /* ---- A10-A13: device-resident particle state and the whole time step ---------------------------
  * The reference keeps its particle state as module-level numpy arrays in the driver
  * (sph/code_running.py:121-167) and advances it inline (:217-540).  A session holds the same
@@ -108,11 +118,17 @@ int sphb200_session_upload_rows(sphb200_ctx* ctx, const double* rows, int64_t n_
  * "n_owned" (caller indices >= n_owned are ghosts of a slab decomposition: excluded from the crossing-time
  * minimum and from the percentile behind d) */
 int sphb200_session_set_scalar(sphb200_ctx* ctx, const char* name, double value);
+/* F1 inside the step: with f_un (device, (N, n_species) row-major, caller order) the force phase adds
+ * the dust-gas drag of code_running.py:455,462-463,473 to visc_accel (tables as in sphb200_net_impulse);
+ * f_un == NULL switches it off (the default).  Not available on a slab session with ghosts. */
+int sphb200_session_set_drag(sphb200_ctx* ctx, const void* f_un, int n_species, const double* grain_mass_host,
+                             const double* sigma_effective_host, void* stream);
 /* device scalars of the last step: "ct", "dt", "d", "age", "max_dist", "n_slow" (synchronises) */
 int sphb200_session_scalar(sphb200_ctx* ctx, const char* name, double* value_host, void* stream);
 /* code_running.py:171-179: first neighbour query + hydro_update, densities_0 <- densities */
 int sphb200_session_startup(sphb200_ctx* ctx, void* stream);
-/* one pass of the while-body, code_running.py:217-540 (gas/dust only, gravity/drag/chemistry zero) */
+/* one pass of the while-body, code_running.py:217-540 (gas/dust only, gravity and chemistry zero; drag as
+ * set by sphb200_session_set_drag, off by default) */
 int sphb200_session_step(sphb200_ctx* ctx, void* stream);
 /* one phase of the step, for per-kernel timing: "crossing", "dt_clamp", "sort", "knn", "pack",
  * "density", "pi", "force", "integrate" */

@@ -27,10 +27,11 @@ NSC_PATH = os.path.join(REF_ROOT, "sph", "navier_stokes_cleaned.py")
 # (first, last) 1-based inclusive line ranges of navier_stokes_cleaned.py that are exec'd
 _RANGES = (
     (21, 52),    # physical constants, species tables
+    (69, 79),    # sigma_effective, grain_mass
     (541, 552),  # neighbors
     (556, 671),  # hydro_update
     (673, 690),  # Weigh2, Weigh2_dust, grad_weight
-    (693, 717),  # density, dust_density
+    (693, 742),  # density, dust_density, net_impulse
     (744, 816),  # num_dens, del_pressure, crossing_time, artificial_viscosity
 )
 

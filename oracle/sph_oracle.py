@@ -274,6 +274,51 @@ def artificial_viscosity(neighbor, points, particle_type, sizes, mass, densities
 
 
 # --------------------------------------------------------------------------------------------
+# F1  dust-gas drag                                               navier_stokes_cleaned.py:44,52,69-79,719-742
+mu_specie = np.array([2.0158, 4.0026, 1.0079, 1.0074, 4.0021, 4.0016, 0.0005, 140.69, 60.08, 12.0107, 28.0855,
+                      55.834, 100.39, 131.93, 40.096])                               # nsc:41
+mineral_densities = np.array([1.e19, 1e19, 1e19, 1e19, 1e19, 1e19, 1e19, 3320, 2260, 2266, 2329, 7870, 3250,
+                              3250., 3166.])                                          # nsc:44
+mrn_constants = np.array([50e-10, 5000e-10])                                          # nsc:52
+
+
+def sigma_effective(mineral_densities=mineral_densities, mrn_constants=mrn_constants, mu_specie=mu_specie):  # nsc:69-74
+    return mu_specie * amu / mineral_densities * (3. / 4.) * -np.diff(mrn_constants ** -0.5) / np.diff(mrn_constants ** 0.5)
+
+
+def grain_mass(mineral_densities=mineral_densities, mrn_constants=mrn_constants):    # nsc:76-79
+    return mineral_densities * -np.diff(mrn_constants ** 0.5) / np.diff(mrn_constants ** -2.5) * (4. / 5.) * 4 * np.pi / 3.
+
+
+def net_impulse(points, mass, sizes, velocities, particle_type, neighbor, f_un, d=None):   # nsc:719-742
+    """Drag of the dust neighbours on each particle (`accel_onto`) and the opposite push on those
+    dust particles (`accel_reaction`, a scatter over the rows).  Rows are visited in order like the
+    reference's loop, so the scatter adds in the same sequence."""
+    meff, seff = grain_mass(), sigma_effective()
+    nb, vec, n2 = _rows(points, neighbor)
+    f = np.asarray(f_un, dtype=np.float64)
+    onto = np.zeros(points.shape)
+    reaction = np.zeros(points.shape)
+    n = len(points)
+    for a in range(0, n, 4096):
+        b = min(n, a + 4096)
+        r = nb[a:b]
+        mg = np.sum(meff * f[r], axis=2)                                              # :727
+        mc = np.sum(seff * f[r], axis=2)                                              # :728
+        nv = velocities[r] - velocities[a:b, None, :]                                 # :729
+        ds = sizes[r]
+        with np.errstate(divide='ignore', invalid='ignore', over='ignore'):
+            wf = mass[r] * 315 * (ds ** 2 - n2[a:b]) ** 3 / (64 * np.pi * ds ** 9)    # :736 (Weigh2_dust, :678-681)
+            net = (wf / mg * mc * np.sum(nv ** 2, axis=2) ** 0.5)[..., None] * nv \
+                * (particle_type[r] == 2)[..., None] * (wf > 0)[..., None]            # :738
+        onto[a:b] = np.sum(net, axis=1)                                               # :740
+        back = -(net * (r != np.arange(a, b)[:, None])[..., None])                    # :741
+        for c in range(3):                                                            # row after row, as the loop does
+            np.add.at(reaction[:, c], r.ravel(), back[..., c].ravel())
+    return onto, reaction
+
+
+# --------------------------------------------------------------------------------------------
 # A9-A12  one time step in the driver's order                    code_running.py:217-540
 # Harness conventions (SURVEY.md §8c.3): gas/dust only (no stars, so the radiative / supernova block
 # :243-397 is skipped by its own guard), gravity, drag and chemistry zero, the start-up search radius
@@ -297,10 +342,11 @@ def startup(state, neighbors_fn=neighbors, hydro_fn=hydro_update):
     return s
 
 
-def step(s, neighbors_fn=neighbors, hydro_fn=hydro_update, crossing_fn=None):
+def step(s, neighbors_fn=neighbors, hydro_fn=hydro_update, crossing_fn=None, drag_fn=None):
     """One pass of the `while` body; returns a new state dict (inputs are not mutated).
-    The three hooks let tests/golden/make_golden.py drive the same harness with the reference's own
-    (extracted) functions."""
+    The hooks let tests/golden/make_golden.py drive the same harness with the reference's own
+    (extracted) functions.  `drag_fn` (net_impulse's signature) switches the dust-gas drag of
+    code_running.py:455,462-463,473 on; the state then needs `f_un`."""
     s = dict(s)
     points = s['points'].copy(); velocities = s['velocities'].copy()
     ptype = s['particle_type']; mass = s['mass']; mu = s['mu_array']; gam = s['gamma_array']
@@ -325,6 +371,11 @@ def step(s, neighbors_fn=neighbors, hydro_fn=hydro_update, crossing_fn=None):
     pressure_accel = np.nan_to_num(hydro_accel * gas.astype('float')[:, None])            # :460
     old_accel = s['total_accel']                                                          # :471
     visc_accel = av0.copy()                                                               # :473 (drag = 0)
+    if drag_fn is not None:
+        onto, reaction = drag_fn(points, mass, sizes, velocities, ptype, nb, s['f_un'])  # :455
+        with np.errstate(divide='ignore', invalid='ignore'):
+            drag_gas = np.nan_to_num(((onto.T) * dust_d / densities * gas.astype('float')).T)   # :462
+        visc_accel = drag_gas + np.nan_to_num(reaction) + av0                             # :463, :473
     vmag = np.sum(velocities ** 2, axis=1) ** 0.5
     with np.errstate(invalid='ignore'):
         clamp = vmag - np.sum(visc_accel ** 2, axis=1) ** 0.5 * dt < 0                    # :475

@@ -32,6 +32,9 @@ mu_specie = np.array([2.0158, 4.0026, 1.0079, 1.0074, 4.0021, 4.0016, 0.0005, 14
                       55.834, 100.39, 131.93, 40.096])
 gamma = np.array([7. / 5, 5. / 3, 5. / 3, 5. / 3, 5. / 3, 5. / 3, 5. / 3, 15.6354113, 4.913, 1.0125, 2.364, 3.02,
                   10., 10., 10.])
+mineral_densities = np.array([1.e19, 1e19, 1e19, 1e19, 1e19, 1e19, 1e19, 3320, 2260, 2266, 2329, 7870, 3250, 3250.,
+                              3166.])                                   # navier_stokes_cleaned.py:44
+mrn_constants = np.array([50e-10, 5000e-10])                            # :52, MRN grain radius range
 f_u = np.array([.86, .14, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0])
 N_SPECIES = 15
 

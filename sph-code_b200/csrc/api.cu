@@ -227,4 +227,28 @@ int sphb200_artificial_viscosity(sphb200_ctx* ctx, int64_t n, int k, const int64
   return launch_loop_viscosity(ctx, (int)n, k, bufp<int32_t>(ctx->list), in, visc_accel, visc_heat, st);
 }
 
+// ---- F1 ----------------------------------------------------------------------------------------
+int sphb200_net_impulse(sphb200_ctx* ctx, int64_t n, int k, const int64_t* neighbor, const double* points,
+                        const double* mass, const double* sizes, const double* velocities,
+                        const double* particle_type, const double* f_un, int n_species, const double* grain_mass_host,
+                        const double* sigma_effective_host, double* accel_onto, double* accel_reaction, void* stream) {
+  if (!ctx || !neighbor || !points || !mass || !sizes || !velocities || !particle_type || !f_un || !grain_mass_host ||
+      !sigma_effective_host || !accel_onto || !accel_reaction)
+    SPH_FAIL("sphb200_net_impulse: null argument");
+  if (n_species <= 0 || n_species > SPHB200_MAX_SPECIES)
+    SPH_FAIL("sphb200_net_impulse: n_species=%d outside 1..%d", n_species, SPHB200_MAX_SPECIES);
+  SPH_TRY(check_nk(n, k));
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  cudaStream_t st = as_stream(stream);
+  SPH_TRY(prep_list(ctx, neighbor, n, k, st));
+  SPH_TRY(devbuf_reserve(ctx->tmp1, (size_t)n * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->tmp2, (size_t)n * sizeof(double)));
+  SPH_TRY(launch_grain_means(ctx, (int)n, n_species, f_un, grain_mass_host, sigma_effective_host, bufp<double>(ctx->tmp1),
+                             bufp<double>(ctx->tmp2), st));
+  LoopIn in = {};
+  in.points = points; in.vel = velocities; in.mass = mass; in.sizes = sizes; in.ptype = particle_type;
+  return launch_loop_net_impulse(ctx, (int)n, k, bufp<int32_t>(ctx->list), in, bufp<double>(ctx->tmp1),
+                                 bufp<double>(ctx->tmp2), accel_onto, accel_reaction, st);
+}
+
 }  // extern "C"

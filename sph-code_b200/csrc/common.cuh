@@ -64,6 +64,8 @@ struct GridSpec {
 };
 
 // A growable device buffer owned by the context.
+#define SPHB200_MAX_SPECIES 64   // species columns of f_un the drag tables can hold (the reference has 15)
+
 struct DevBuf {
   void* p = nullptr;
   size_t bytes = 0;

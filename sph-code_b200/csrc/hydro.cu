@@ -377,3 +377,88 @@ int launch_crossing_time(sphb200_ctx* ctx, int n, int k, const int32_t* list, co
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// F1 in the device-resident step: dust-gas drag on the packed records          nsc:719-742
+// (code_running.py:455,462-463,473).  Only dust neighbours carry a term, so the per-particle MRN
+// means stay in the caller's order and are fetched through `id` for those neighbours alone; the
+// reaction on the dust particle is a sparse fp64 RED.
+template <int G>
+__global__ void __launch_bounds__(HY_THREADS)
+drag_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __restrict__ r0,
+            const double4* __restrict__ r1, const double4* __restrict__ r2, const uint32_t* __restrict__ id,
+            const double* __restrict__ mg, const double* __restrict__ mc, double* __restrict__ onto,
+            double* __restrict__ reaction) {
+  cg::thread_block_tile<G> tile = cg::tiled_partition<G>(cg::this_thread_block());
+  const int i = blockIdx.x * (HY_THREADS / G) + tile.meta_group_rank();
+  if (i >= n) return;
+  const int lane = tile.thread_rank();
+  const int32_t* row = list + (int64_t)i * k;
+  const double4 ps = r0[i];
+  const double4 vs = r2[i];
+  double ax = 0, ay = 0, az = 0;
+  for (int s = lane; s < k; s += G) {
+    const int j = row[s];
+    if (j < 0 || j >= n) continue;
+    const double4 w = ldg256(r1 + j);
+    if (w.w == 0.0) continue;                             // [type_j == 2] (m_dust of the record)
+    const double4 q = ldg256(r0 + j);
+    const double4 v = ldg256(r2 + j);
+    const double dx = q.x - ps.x, dy = q.y - ps.y, dz = q.z - ps.z;
+    const double r2_ = dx * dx + dy * dy + dz * dz;
+    const double t = q.w - r2_;
+    const double wf = w.w * w.x * (t * t * t);            // Weigh2_dust: m c6(h_j) (h_j^2 - r^2)^3, nsc:678-681
+    if (!(wf > 0.0)) continue;                            // [weight_factor > 0]
+    const double du = v.x - vs.x, dv = v.y - vs.y, dw = v.z - vs.z;
+    const double speed = sqrt(du * du + dv * dv + dw * dw);
+    const uint32_t g = id ? id[j] : (uint32_t)j;
+    const double c = wf / mg[g] * mc[g] * speed;          // nsc:738
+    const double gx = c * du, gy = c * dv, gz = c * dw;
+    ax += gx; ay += gy; az += gz;
+    if (j != i) {                                         // nsc:741
+      if (gx != 0.0) atomicAdd(reaction + 3 * (int64_t)j, -gx);
+      if (gy != 0.0) atomicAdd(reaction + 3 * (int64_t)j + 1, -gy);
+      if (gz != 0.0) atomicAdd(reaction + 3 * (int64_t)j + 2, -gz);
+    }
+  }
+  ax = cg::reduce(tile, ax, cg::plus<double>());
+  ay = cg::reduce(tile, ay, cg::plus<double>());
+  az = cg::reduce(tile, az, cg::plus<double>());
+  if (lane == 0) { onto[3 * (int64_t)i] = ax; onto[3 * (int64_t)i + 1] = ay; onto[3 * (int64_t)i + 2] = az; }
+}
+
+__device__ __forceinline__ double drag_nan_to_num(double v) {
+  if (v != v) return 0.0;
+  if (v > DBL_MAX) return DBL_MAX;
+  if (v < -DBL_MAX) return -DBL_MAX;
+  return v;
+}
+
+// visc_accel = drag_accel_gas + drag_accel_dust + av[0]                    code_running.py:462-463,473
+__global__ void __launch_bounds__(256)
+drag_apply_kernel(int n, const double* __restrict__ onto, const double* __restrict__ reaction,
+                  const double* __restrict__ rho, const double* __restrict__ rho_dust, const double* __restrict__ ptype,
+                  double* __restrict__ visc_accel) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double gas = (ptype[i] == 0.0) ? 1.0 : 0.0;
+  const double rd = rho_dust[i], r = rho[i];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const double dg = drag_nan_to_num(onto[3 * (int64_t)i + c] * rd / r * gas);
+    const double dd = drag_nan_to_num(reaction[3 * (int64_t)i + c]);
+    visc_accel[3 * (int64_t)i + c] = (dg + dd) + visc_accel[3 * (int64_t)i + c];
+  }
+}
+
+int launch_drag(sphb200_ctx* ctx, int n, int k, const int32_t* list, const uint32_t* id, const double* mg,
+                const double* mc, const double* rho, const double* rho_dust, const double* ptype, double* onto,
+                double* reaction, double* visc_accel, cudaStream_t st) {
+  CUDA_TRY(cudaMemsetAsync(reaction, 0, (size_t)n * 3 * sizeof(double), st));
+  drag_kernel<HY_G><<<ceil_div(n, HY_THREADS / HY_G), HY_THREADS, 0, st>>>(
+      n, k, list, bufp<double4>(ctx->r0), bufp<double4>(ctx->r1), bufp<double4>(ctx->r2), id, mg, mc, onto, reaction);
+  drag_apply_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, onto, reaction, rho, rho_dust, ptype, visc_accel);
+  ctx->launches += 2;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}

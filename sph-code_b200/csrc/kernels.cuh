@@ -55,3 +55,10 @@ int launch_loop_del_pressure(sphb200_ctx* ctx, int n, int k, const int32_t* list
                              cudaStream_t st);
 int launch_loop_viscosity(sphb200_ctx* ctx, int n, int k, const int32_t* list, const LoopIn& in, double* accel,
                           double* heat, cudaStream_t st);
+int launch_drag(sphb200_ctx* ctx, int n, int k, const int32_t* list, const uint32_t* id, const double* mg,
+                const double* mc, const double* rho, const double* rho_dust, const double* ptype, double* onto,
+                double* reaction, double* visc_accel, cudaStream_t st);
+int launch_grain_means(sphb200_ctx* ctx, int n, int ns, const double* f_un, const double* meff, const double* seff,
+                       double* mg, double* mc, cudaStream_t st);
+int launch_loop_net_impulse(sphb200_ctx* ctx, int n, int k, const int32_t* list, const LoopIn& in, const double* mg,
+                            const double* mc, double* onto, double* reaction, cudaStream_t st);

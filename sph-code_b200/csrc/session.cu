@@ -27,6 +27,10 @@ static const char* kOutName[O_NOUT] = {"densities", "num_densities", "dust_densi
 #define SB_KNNH 37           // k-th neighbour distance of the last search (guess for the next one)
 #define SB_KNNH_ALT 38
 #define SB_POS 39            // caller index -> sorted position (inverse of id), built on demand
+#define SB_GM 40             // drag: mean grain mass / cross-section per particle, CALLER order (nsc:727-728)
+#define SB_GC 41
+#define SB_ONTO 42           // drag: accel_onto, accel_reaction (sorted order, scratch of the force phase)
+#define SB_REACT 43
 
 struct SessionScalars {      // host mirror of the run parameters
   double dt_0, max_age, n_int, raise_factor, au;
@@ -42,6 +46,7 @@ struct Session {
   int has_list = 0;
   int use_guess = 1;
   int pos_valid = 0;         // SB_POS matches the current id
+  int drag = 0;              // dust-gas drag (net_impulse) folded into the force phase
   int64_t n_owned = -1;      // slab decomposition: caller indices >= n_owned are ghosts (-1: none)
   SessionScalars sc;
 };
@@ -422,8 +427,15 @@ static int phase_pi(sphb200_ctx* ctx, cudaStream_t st) {
 }
 static int phase_force(sphb200_ctx* ctx, cudaStream_t st) {
   Session& s = sess(ctx);
-  return launch_force(ctx, (int)s.n, s.k, bufp<int32_t>(ctx->list), outp(ctx, O_RHO), fld(ctx, F_MASS), outp(ctx, O_HACC),
-                      outp(ctx, O_VACC), outp(ctx, O_HEAT), st);
+  SPH_TRY(launch_force(ctx, (int)s.n, s.k, bufp<int32_t>(ctx->list), outp(ctx, O_RHO), fld(ctx, F_MASS), outp(ctx, O_HACC),
+                       outp(ctx, O_VACC), outp(ctx, O_HEAT), st));
+  if (!s.drag) return 0;
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_ONTO], (size_t)s.n * 3 * sizeof(double)));      // code_running.py:455,462-463,473
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_REACT], (size_t)s.n * 3 * sizeof(double)));
+  return launch_drag(ctx, (int)s.n, s.k, bufp<int32_t>(ctx->list), bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]),
+                     bufp<double>(ctx->sbuf[SB_GM]), bufp<double>(ctx->sbuf[SB_GC]), outp(ctx, O_RHO), outp(ctx, O_DUST),
+                     fld(ctx, F_TYPE), bufp<double>(ctx->sbuf[SB_ONTO]), bufp<double>(ctx->sbuf[SB_REACT]),
+                     outp(ctx, O_VACC), st);
 }
 
 // A11: kick-drift + heating; also |x|^2 of the slow particles for A12
@@ -540,7 +552,7 @@ int sphb200_session_resize(sphb200_ctx* ctx, int64_t n, int64_t n_owned, void* s
   Session& s = sess(ctx);
   if (s.k <= 0) SPH_FAIL("session_resize: no session to resize");
   s.n = n; s.n_owned = n_owned;
-  s.has_list = 0; s.pos_valid = 0; s.id_cur = 0; s.knnh_cur = 0;
+  s.has_list = 0; s.pos_valid = 0; s.id_cur = 0; s.knnh_cur = 0; s.drag = 0;
   for (int f = 0; f < F_NFIELDS; ++f) {
     s.cur[f] = 0;
     SPH_TRY(devbuf_reserve(ctx->sbuf[2 * f], (size_t)n * kFieldWidth[f] * sizeof(double)));
@@ -771,6 +783,27 @@ int sphb200_session_startup(sphb200_ctx* ctx, void* stream) {
   copy_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>(s.n, outp(ctx, O_RHO), fld(ctx, F_RHO0));
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// F1: switch the dust-gas drag of code_running.py:455,462-463,473 on (f_un != NULL) or off.
+int sphb200_session_set_drag(sphb200_ctx* ctx, const void* f_un, int n_species, const double* grain_mass_host,
+                             const double* sigma_effective_host, void* stream) {
+  if (!ctx) SPH_FAIL("null context");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  Session& s = sess(ctx);
+  if (s.k <= 0) SPH_FAIL("session_set_drag: no session");
+  if (!f_un) { s.drag = 0; return 0; }
+  if (!grain_mass_host || !sigma_effective_host) SPH_FAIL("session_set_drag: null table");
+  if (n_species <= 0 || n_species > SPHB200_MAX_SPECIES)
+    SPH_FAIL("session_set_drag: n_species=%d outside 1..%d", n_species, SPHB200_MAX_SPECIES);
+  if (s.n_owned >= 0) SPH_FAIL("session_set_drag: not available on a slab with ghosts (the reaction on a ghost is not returned to its owner)");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_GM], (size_t)s.n * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_GC], (size_t)s.n * sizeof(double)));
+  SPH_TRY(launch_grain_means(ctx, (int)s.n, n_species, static_cast<const double*>(f_un), grain_mass_host,
+                             sigma_effective_host, bufp<double>(ctx->sbuf[SB_GM]), bufp<double>(ctx->sbuf[SB_GC]), st));
+  s.drag = 1;
   return 0;
 }
 

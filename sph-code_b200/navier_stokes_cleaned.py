@@ -22,7 +22,8 @@ import torch
 
 from . import _lib
 from .constants import (G, k, sb, AU, amu, h, c, wien, m_h, solar_mass, solar_luminosity, solar_lifespan,  # noqa: F401
-                        t_cmb, t_solar, supernova_energy, m_0, year, species_labels, mu_specie, gamma, f_u)
+                        t_cmb, t_solar, supernova_energy, m_0, year, species_labels, mu_specie, gamma, f_u,
+                        mineral_densities, mrn_constants)
 from . import constants as _C
 
 # module globals assigned by the caller, exactly as with the reference module
@@ -188,3 +189,35 @@ def artificial_viscosity(neighbor, points, particle_type, sizes, mass, densities
         _ptr(mu), float(d), _ptr(va), _ptr(vh), _stream()))
     _check_bad_index(ctx, n)
     return va.cpu().numpy(), vh.cpu().numpy()
+
+
+def sigma_effective(mineral_densities, mrn_constants, mu_specie):
+    """nsc:69-74: effective cross-section per dust particle for an MRN size distribution (host table)."""
+    return mu_specie * amu / mineral_densities * (3. / 4.) * -np.diff(mrn_constants ** -0.5) / np.diff(mrn_constants ** 0.5)
+
+
+def grain_mass(mineral_densities, mrn_constants):
+    """nsc:76-79: mean grain mass per species for an MRN size distribution (host table)."""
+    return mineral_densities * -np.diff(mrn_constants ** 0.5) / np.diff(mrn_constants ** -2.5) * (4. / 5.) * 4 * np.pi / 3.
+
+
+def net_impulse(points, mass, sizes, velocities, particle_type, neighbor, f_un):
+    """nsc:719-742, dust-gas drag.  Returns (accel_onto (N,3), accel_reaction (N,3))."""
+    ctx = _lib.context()
+    nb = _dev(_neighbor_array(neighbor, len(points)), np.int64)
+    n, kk = nb.shape
+    pts = _dev(points); m = _dev(mass); hs = _dev(sizes); vel = _dev(velocities); pt = _dev(particle_type)
+    f = _dev(np.ascontiguousarray(np.asarray(f_un, dtype=np.float64)))
+    if f.dim() != 2 or f.shape[0] != n:
+        raise ValueError("f_un must be (N, n_species)")
+    ns = int(f.shape[1])
+    meff = np.ascontiguousarray(np.broadcast_to(grain_mass(mineral_densities, mrn_constants), (ns,)), dtype=np.float64)
+    seff = np.ascontiguousarray(np.broadcast_to(sigma_effective(mineral_densities, mrn_constants, mu_specie), (ns,)),
+                                dtype=np.float64)
+    onto = torch.empty((n, 3), dtype=torch.float64, device=pts.device)
+    reaction = torch.empty((n, 3), dtype=torch.float64, device=pts.device)
+    _lib.check(_lib.load().sphb200_net_impulse(
+        ctx.handle, n, kk, _ptr(nb), _ptr(pts), _ptr(m), _ptr(hs), _ptr(vel), _ptr(pt), _ptr(f), ns,
+        meff.ctypes.data_as(ctypes.c_void_p), seff.ctypes.data_as(ctypes.c_void_p), _ptr(onto), _ptr(reaction), _stream()))
+    _check_bad_index(ctx, n)
+    return onto.cpu().numpy(), reaction.cpu().numpy()

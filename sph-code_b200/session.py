@@ -122,6 +122,25 @@ class Session(object):
         return self.download_tensor(name).cpu().numpy()
 
     # -- the path ---------------------------------------------------------------------------
+    def set_drag(self, f_un):
+        """Dust-gas drag of code_running.py:455,462-463,473 in the force phase (`net_impulse`, nsc:719-742):
+        f_un is the (N, n_species) composition in the caller's order; None switches the drag off."""
+        if f_un is None:
+            _lib.check(self.lib.sphb200_session_set_drag(self.ctx.handle, None, 0, None, None, self._stream()))
+            return
+        from . import navier_stokes_cleaned as nsc
+        f = torch.as_tensor(np.ascontiguousarray(np.asarray(f_un, dtype=np.float64)) if not torch.is_tensor(f_un) else f_un)
+        f = f.to(device=self.device, dtype=torch.float64).contiguous()
+        if f.dim() != 2 or f.shape[0] != self.n:
+            raise ValueError("f_un must be (N, n_species)")
+        ns = int(f.shape[1])
+        meff = np.ascontiguousarray(np.broadcast_to(nsc.grain_mass(C.mineral_densities, C.mrn_constants), (ns,)), dtype=np.float64)
+        seff = np.ascontiguousarray(np.broadcast_to(nsc.sigma_effective(C.mineral_densities, C.mrn_constants, C.mu_specie), (ns,)),
+                                    dtype=np.float64)
+        _lib.check(self.lib.sphb200_session_set_drag(self.ctx.handle, f.data_ptr(), ns, meff.ctypes.data_as(ctypes.c_void_p),
+                                                     seff.ctypes.data_as(ctypes.c_void_p), self._stream()))
+        torch.cuda.current_stream(self.device).synchronize()       # f lives until the means are computed
+
     def startup(self):
         """code_running.py:171-179: first neighbour query + hydro_update; densities_0 <- densities."""
         _lib.check(self.lib.sphb200_session_startup(self.ctx.handle, self._stream()))

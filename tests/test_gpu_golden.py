@@ -100,3 +100,51 @@ def test_full_size_properties(built_lib):
     W[W < 0] = 0
     assert rel(rho[sub], np.sum(st["mass"][idx[sub]] * W, axis=1)) < RTOL
     assert np.all(rho > 0) and np.all(np.isfinite(out[0]))
+
+
+def test_net_impulse_against_reference_outputs(built_lib):
+    """F1, dust-gas drag (nsc:719-742).  `accel_onto` is a gather (same tolerance as the other sums);
+    `accel_reaction` is a scatter accumulated with fp64 atomics, so the order of the adds differs."""
+    from sphb200 import ics
+    from sphb200 import navier_stokes_cleaned as nsc
+    g = np.load(os.path.join(GOLD, "drag_n2000.npz"))
+    st = ics.uniform_box(2000, 3, n_dust=150)
+    assert np.array_equal(nsc.grain_mass(nsc.mineral_densities, nsc.mrn_constants), g["grain_mass"])
+    assert np.array_equal(nsc.sigma_effective(nsc.mineral_densities, nsc.mrn_constants, nsc.mu_specie), g["sigma_effective"])
+    idx = g["idx"].astype(np.int64)
+    onto, reaction = nsc.net_impulse(st["points"], st["mass"], g["sizes"], st["velocities"], st["particle_type"], idx,
+                                     st["f_un"])
+    assert rel(onto, g["accel_onto"]) < RTOL and rel(reaction, g["accel_reaction"]) < RTOL
+    assert np.array_equal(onto == 0, g["accel_onto"] == 0) and np.array_equal(reaction == 0, g["accel_reaction"] == 0)
+    # ragged rows (list of lists), as the loop generation allows
+    rs = np.random.RandomState(4)
+    ragged = [list(idx[i, : rs.randint(1, 41)]) for i in range(len(idx))]
+    from oracle import sph_oracle as O
+    got_o, got_r = nsc.net_impulse(st["points"], st["mass"], g["sizes"], st["velocities"], st["particle_type"], ragged,
+                                   st["f_un"])
+    pad = np.full(idx.shape, -1, dtype=np.int64)
+    for i, row in enumerate(ragged):
+        pad[i, :len(row)] = row
+    keep = pad >= 0
+    full_o, full_r = _drag_rows(O, st, g["sizes"], idx, keep)
+    assert rel(got_o, full_o) < RTOL and rel(got_r, full_r) < RTOL
+
+
+def _drag_rows(O, st, sizes, idx, keep):
+    """nsc:719-742 restated with a per-entry mask (ragged rows)."""
+    meff, seff = O.grain_mass(), O.sigma_effective()
+    p, v, m, pt, f = st["points"], st["velocities"], st["mass"], st["particle_type"], st["f_un"]
+    vec = p[idx] - p[:, None, :]
+    n2 = np.sum(vec ** 2, axis=2)
+    nv = v[idx] - v[:, None, :]
+    ds = sizes[idx]
+    with np.errstate(all="ignore"):
+        wf = m[idx] * 315 * (ds ** 2 - n2) ** 3 / (64 * np.pi * ds ** 9)
+        net = (wf / np.sum(meff * f[idx], axis=2) * np.sum(seff * f[idx], axis=2) * np.sum(nv ** 2, axis=2) ** 0.5)[..., None] \
+            * nv * (pt[idx] == 2)[..., None] * (wf > 0)[..., None] * keep[..., None]
+    onto = np.sum(net, axis=1)
+    back = -(net * (idx != np.arange(len(p))[:, None])[..., None])
+    reaction = np.zeros_like(onto)
+    for c in range(3):
+        np.add.at(reaction[:, c], idx.ravel(), back[..., c].ravel())
+    return onto, reaction

@@ -102,3 +102,37 @@ def test_default_dt0_blows_up_like_the_reference(built_lib):
     s.step()
     assert s.scalar("n_slow") == 0.0
     assert np.isnan(s.scalar("d"))
+
+
+def test_steps_with_drag(built_lib):
+    """the dust-gas drag of code_running.py:455,462-463,473 (nsc.net_impulse) inside the
+    step, against the oracle harness with its net_impulse plugged in.  The dust moves (with dust at rest
+    the clamp of :475 replaces any drag on it by -v/dt = 0)."""
+    from sphb200 import ics
+    from sphb200.session import Session
+    st = ics.uniform_box(5000, 5, n_dust=400)
+    dust = st["particle_type"] == 2
+    st["velocities"][dust] = np.random.RandomState(9).normal(size=(int(dust.sum()), 3)) * 1000.
+    st["dt_0"] = O.dt_0 * 1e-6
+    s = Session(len(st["points"]), st["N_NEIGH"], st["dist"], dt_0=st["dt_0"])
+    s.upload(st)
+    s.set_drag(st["f_un"])
+    s.startup()
+    ref = O.startup(st)
+    plain = O.startup(st)
+    for it in range(3):
+        s.step(); s.check()
+        ref = O.step(ref, drag_fn=O.net_impulse)
+        plain = O.step(plain)
+        assert np.array_equal(s.download("neighbor"), ref["neighbor"])
+        va = s.download("visc_accel")
+        assert rel(va, ref["visc_accel"]) < RTOL
+        assert rel(va[dust], ref["visc_accel"][dust]) < 1e-9          # pure drag reaction (atomics: order differs)
+        for name in ("points", "velocities", "total_accel", "E_internal", "T", "sizes"):
+            assert rel(s.download(name), ref[name]) < RTOL, (it, name)
+    assert np.abs(ref["visc_accel"][dust]).max() > 0                  # the drag is really there ...
+    assert rel(ref["velocities"], plain["velocities"]) > 1e-13        # ... and changes the trajectory
+    s.set_drag(None)
+    s.step(); s.check()
+    ref = O.step(ref)
+    assert rel(s.download("visc_accel"), ref["visc_accel"]) < RTOL
