@@ -96,7 +96,9 @@ int sphb200_net_impulse(sphb200_ctx* ctx, int64_t n, int k, const int64_t* neigh
  * "mass", "sizes", "T", "E_internal", "mu_array", "gamma_array", "particle_type", "densities_0" (N).
  * Read-only results: "densities", "num_densities", "dust_densities", "visc_heat" (N); "hydro_accel",
  * "visc_accel", "pressure_accel" (N,3); "neighbor" (N,k) int64; "num_nontrivial" (N) int64.
- * upload/download take DEVICE pointers in the caller's particle order. */
+ * upload/download take DEVICE pointers in the caller's particle order.  upload also accepts "neighbor"
+ * ((N,k) int64 rows in the caller's indices, N = missing): the list a checkpoint saved, so that the next
+ * step's crossing time (code_running.py:222) sees the same rows as the uninterrupted run. */
 int sphb200_session_create(sphb200_ctx* ctx, int64_t n, int k, double dist);
 /* same run, new particle set of n particles (the first n_owned are owned, the rest ghosts; -1 = all owned):
  * keeps k, dist, run parameters and device scalars; fill the arrays with sphb200_session_upload_rows */
@@ -114,6 +116,12 @@ int sphb200_session_gather(sphb200_ctx* ctx, const char* field, const int64_t* i
 int sphb200_session_scatter(sphb200_ctx* ctx, const char* field, const int64_t* idx, int64_t count, const double* in, void* stream);
 int sphb200_session_download_rows(sphb200_ctx* ctx, double* rows, int64_t n_rows, int ncol, void* stream);
 int sphb200_session_upload_rows(sphb200_ctx* ctx, const double* rows, int64_t n_rows, int ncol, void* stream);
+/* SURVEY row F4, variable-N state (code_running.py:361-381 grows every array when a supernova injects
+ * particles): append n_new rows (same layout) as caller indices N .. N+n_new-1, keeping the existing state
+ * and scalars.  Run the phases "sort" and "knn" afterwards (the driver's nsc.neighbors call at :386); the
+ * next step then takes dv = a dt (:484-485) and new_smoothing = 1 (:534-535), as the reference does while its
+ * old arrays are shorter.  Drag tables are dropped (call sphb200_session_set_drag again). */
+int sphb200_session_append_rows(sphb200_ctx* ctx, const double* rows, int64_t n_new, int ncol, void* stream);
 /* run parameters: "dt_0", "MAX_AGE", "N_INT_PER_PARTICLE", "raise_factor", "AU", "dist", "age", "d", "dt", "ct",
  * "n_owned" (caller indices >= n_owned are ghosts of a slab decomposition: excluded from the crossing-time
  * minimum and from the percentile behind d) */

@@ -342,6 +342,21 @@ def startup(state, neighbors_fn=neighbors, hydro_fn=hydro_update):
     return s
 
 
+def append(s, new, neighbors_fn=neighbors):
+    """Variable-N state: the concatenations of code_running.py:363-381 for a dict `new`
+    of per-particle arrays, then the neighbour query of :386 (start-up radius, as in step()).
+    `total_accel` and `densities_0` keep their OLD length, which is what makes the reference take
+    dv = a dt (:484-485) and new_smoothing = 1 (:534-535) in the following step."""
+    s = dict(s)
+    for name in ('points', 'velocities', 'mass', 'sizes', 'T', 'E_internal', 'mu_array', 'gamma_array', 'particle_type'):
+        s[name] = np.concatenate((s[name], np.asarray(new[name], dtype=np.float64)))
+    if s.get('f_un') is not None and new.get('f_un') is not None:
+        s['f_un'] = np.vstack([s['f_un'], new['f_un']])
+    nb, _, dd, nontriv, sizes = neighbors_fn(s['points'], s['dist'], s['N_NEIGH'])                 # :386
+    s.update(neighbor=nb, num_nontrivial=nontriv, sizes=sizes)
+    return s
+
+
 def step(s, neighbors_fn=neighbors, hydro_fn=hydro_update, crossing_fn=None, drag_fn=None):
     """One pass of the `while` body; returns a new state dict (inputs are not mutated).
     The hooks let tests/golden/make_golden.py drive the same harness with the reference's own
@@ -382,7 +397,10 @@ def step(s, neighbors_fn=neighbors, hydro_fn=hydro_update, crossing_fn=None, dra
     visc_accel[clamp] = (-velocities / dt)[clamp]
     total_accel = pressure_accel + visc_accel                                             # :477 (grav = 0)
     points = points + ((total_accel * dt ** 2) / 2. + velocities * dt)                    # :481
-    velocities = velocities + (total_accel + old_accel) / 2. * dt                         # :482-486
+    if np.shape(total_accel) == np.shape(old_accel):                                      # :482-486
+        velocities = velocities + (total_accel + old_accel) / 2. * dt
+    else:
+        velocities = velocities + total_accel * dt
     E_internal = np.nan_to_num(s['E_internal']) + np.nan_to_num(av1 * dt)                 # :490
     with np.errstate(divide='ignore', invalid='ignore'):
         T = np.nan_to_num(E_internal * (mu * m_h) / (gam * mass * k))                     # :491
@@ -393,9 +411,12 @@ def step(s, neighbors_fn=neighbors, hydro_fn=hydro_update, crossing_fn=None, dra
     V_new = max_dist ** (3. / 2.)
     d = (V_new / len(points[slow]) / 0.9 * N_INT_PER_PARTICLE) ** (1. / 3.)               # :521
     count = np.bincount(np.asarray(nb).ravel(), minlength=len(points))[:len(points)]      # :527-530
-    with np.errstate(divide='ignore', invalid='ignore'):
-        new_smoothing = (np.exp(np.nan_to_num(-(densities - s['densities_0']) / (3 * densities))) * 2) / 2. \
-            + (count + nontriv - 1 < 2) * 0.1                                             # :533
+    if len(s['densities_0']) == len(densities):                                           # :532
+        with np.errstate(divide='ignore', invalid='ignore'):
+            new_smoothing = (np.exp(np.nan_to_num(-(densities - s['densities_0']) / (3 * densities))) * 2) / 2. \
+                + (count + nontriv - 1 < 2) * 0.1                                         # :533
+    else:
+        new_smoothing = 1.                                                                # :535
     sizes = sizes.copy()
     sizes[gas] = (new_smoothing * sizes)[gas]                                             # :536
     sizes[gas & (sizes > d)] = d                                                          # :537

@@ -135,3 +135,53 @@ def save_output(outputs_dir, f_un, mass, particle_type, time_coord=(), dust_temp
 def load_output(outputs_dir, number):
     with np.load(os.path.join(outputs_dir, "%d.npz" % int(number))) as fh:
         return {k: fh[k] for k in fh.files}
+
+
+# -- particle checkpoint ---------------------------------------------------------------------------
+# The reference has none: code_running_2.py:162-166 only sketches reloading positions, and a run that
+# stops loses its particles.  One .npz holds everything a Session needs to continue bit-for-bit: the
+# eleven state arrays under the driver's variable names, the k-NN trial radii, and the scalars.
+CHECKPOINT_SCALARS = ("age", "dt", "d", "ct")
+CHECKPOINT_PARAMS = ("dt_0", "MAX_AGE", "N_INT_PER_PARTICLE", "raise_factor", "AU")
+
+
+def save_checkpoint(path, session, params=None, **extra):
+    """Write the device-resident state of `session` (sphb200.session.Session) to `path` (.npz).
+    `params` overrides the run parameters recorded (default: the module constants the session was
+    created with, plus its dt_0); `extra` arrays (e.g. f_un) are stored alongside."""
+    from .session import STATE_FIELDS
+    out = {name: session.download(name) for name in STATE_FIELDS}
+    out["knn_h"] = session.download_tensor("knn_h").cpu().numpy()
+    for name in CHECKPOINT_SCALARS:
+        out["scalar_" + name] = np.float64(session.scalar(name))
+    p = dict(dt_0=session.dt_0, MAX_AGE=C.MAX_AGE, N_INT_PER_PARTICLE=C.N_INT_PER_PARTICLE, raise_factor=C.raise_factor,
+             AU=C.AU)
+    p.update(params or {})
+    for name in CHECKPOINT_PARAMS:
+        out["param_" + name] = np.float64(p[name])
+    out["N_NEIGH"] = np.int64(session.k)
+    out["dist"] = np.float64(session.dist)
+    out["neighbor"] = session.download("neighbor").astype(np.int32)      # the list the next crossing time reads
+    for name, a in extra.items():
+        out["extra_" + name] = np.asarray(a)
+    np.savez(path, **out)
+    return path if str(path).endswith(".npz") else str(path) + ".npz"
+
+
+def load_checkpoint(path, device=None):
+    """Rebuild a Session from save_checkpoint's file: state uploaded, scalars restored, neighbour
+    list restored, ready for step().  Returns (session, extra)."""
+    from .session import Session, STATE_FIELDS
+    with np.load(path) as fh:
+        data = {k: fh[k] for k in fh.files}
+    n = len(data["points"])
+    s = Session(n, int(data["N_NEIGH"]), float(data["dist"]), device=device, dt_0=float(data["param_dt_0"]))
+    for name in CHECKPOINT_PARAMS:
+        s.set_scalar(name, float(data["param_" + name]))
+    s.upload({name: data[name] for name in STATE_FIELDS})
+    import torch
+    s.upload_tensor("knn_h", torch.from_numpy(np.ascontiguousarray(data["knn_h"], dtype=np.float64)).to(s.device))
+    for name in CHECKPOINT_SCALARS:
+        s.set_scalar(name, float(data["scalar_" + name]))
+    s.upload_neighbor(data["neighbor"])
+    return s, {k[len("extra_"):]: v for k, v in data.items() if k.startswith("extra_")}

@@ -47,6 +47,8 @@ struct Session {
   int use_guess = 1;
   int pos_valid = 0;         // SB_POS matches the current id
   int drag = 0;              // dust-gas drag (net_impulse) folded into the force phase
+  int grown = 0;             // particles were appended since the last kick: the old arrays have the old
+                             // length, so this step takes dv = a dt (:485) and new_smoothing = 1 (:535)
   int64_t n_owned = -1;      // slab decomposition: caller indices >= n_owned are ghosts (-1: none)
   SessionScalars sc;
 };
@@ -111,9 +113,9 @@ __global__ void __launch_bounds__(256) reorder_kernel(int n, const uint32_t* __r
   a.knnh_dst[i] = a.knnh_src[p];
 }
 
-__global__ void __launch_bounds__(256) iota_kernel(int n, uint32_t* id) {
+__global__ void __launch_bounds__(256) iota_kernel(int n, uint32_t* id, uint32_t first = 0) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) id[i] = (uint32_t)i;
+  if (i < n) id[i] = first + (uint32_t)i;
 }
 
 // ---- A11: force assembly, kick-drift, heating                        code_running.py:460-491 ----
@@ -124,7 +126,7 @@ integrate_kernel(int n, const double* __restrict__ scal, double kB, double m_h, 
                  const double* __restrict__ mass, const double* __restrict__ mu, const double* __restrict__ gamma,
                  const double* __restrict__ ptype, const double* __restrict__ hacc, double* __restrict__ vacc,
                  const double* __restrict__ heat, double* __restrict__ pacc, double* __restrict__ distsq,
-                 unsigned long long* __restrict__ nslow, const uint32_t* __restrict__ id, int n_owned) {
+                 unsigned long long* __restrict__ nslow, const uint32_t* __restrict__ id, int n_owned, int grown) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   int slow = 0;
   if (i < n) {
@@ -149,7 +151,8 @@ integrate_kernel(int n, const double* __restrict__ scal, double kB, double m_h, 
     for (int c = 0; c < 3; ++c) {
       a[c] = ap[c] + av[c];                                                      // :477 (gravity = 0)
       const double xn = x[c] + ((a[c] * (dt * dt)) / 2. + v[c] * dt);            // :481
-      const double vn = v[c] + (a[c] + acc[3 * (int64_t)i + c]) / 2. * dt;       // :482-486
+      const double vn = grown ? v[c] + a[c] * dt                                 // :484-485 (shapes differ)
+                              : v[c] + (a[c] + acc[3 * (int64_t)i + c]) / 2. * dt;       // :482-483
       pos[3 * (int64_t)i + c] = xn;
       vel[3 * (int64_t)i + c] = vn;
       acc[3 * (int64_t)i + c] = a[c];
@@ -195,7 +198,7 @@ __global__ void length_scale_kernel(const double* __restrict__ sorted, const uns
 __global__ void __launch_bounds__(256)
 smoothing_kernel(int n, const double* __restrict__ scal, double raise_cbrt, const double* __restrict__ rho,
                  double* __restrict__ rho0, const int32_t* __restrict__ nontriv, const double* __restrict__ ptype,
-                 double* __restrict__ sizes) {
+                 double* __restrict__ sizes, int grown) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const double d = scal[SC_D];
@@ -203,7 +206,8 @@ smoothing_kernel(int n, const double* __restrict__ scal, double raise_cbrt, cons
   const double t = ptype[i];
   double h = sizes[i];
   if (t == 0.0) {
-    const double ns = (exp(nan_to_num_d(-(r - rho0[i]) / (3 * r))) * 2) / 2. + ((nontriv[i] <= 1) ? 0.1 : 0.0);  // :533
+    const double ns = grown ? 1.0                       // :534-535 (len(densities_0) != len(densities))
+        : (exp(nan_to_num_d(-(r - rho0[i]) / (3 * r))) * 2) / 2. + ((nontriv[i] <= 1) ? 0.1 : 0.0);             // :533
     h = ns * h;                                         // :536
     if (h > d) h = d;                                   // :537
   } else if (t == 2.0) {
@@ -335,7 +339,7 @@ rows_in_kernel(int n, int ncol, const uint32_t* __restrict__ id, const double* _
   const int base = (blockIdx.x * 8 + warp) * 32;
   if (base >= n) return;
   const int i = base + lane;
-  const int64_t c = (i < n) ? (int64_t)id[i] : -1;
+  const int64_t c = (i < n) ? (id ? (int64_t)id[i] : (int64_t)i) : -1;       // id == nullptr: row r -> slot r
   for (int r = 0; r < 32; ++r) {
     const int64_t cr = __shfl_sync(0xffffffffu, c, r);
     if (cr >= 0 && lane < ROW_STATE_COLS) tile[warp][r][lane] = src[cr * ncol + lane];
@@ -451,7 +455,7 @@ static int phase_kick(sphb200_ctx* ctx, cudaStream_t st) {
                                                      outp(ctx, O_HACC), outp(ctx, O_VACC), outp(ctx, O_HEAT),
                                                      outp(ctx, O_PACC), bufp<double>(ctx->sbuf[SB_DISTSQ]), nslow,
                                                      s.n_owned >= 0 ? bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]) : nullptr,
-                                                     (int)s.n_owned);
+                                                     (int)s.n_owned, s.grown);
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;
@@ -481,7 +485,8 @@ static int phase_smooth(sphb200_ctx* ctx, cudaStream_t st) {
   const int n = (int)s.n;
   smoothing_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, bufp<double>(ctx->scal), cbrt(s.sc.raise_factor), outp(ctx, O_RHO),
                                                      fld(ctx, F_RHO0), bufp<int32_t>(ctx->sbuf[SB_NONTRIV]), fld(ctx, F_TYPE),
-                                                     fld(ctx, F_H));
+                                                     fld(ctx, F_H), s.grown);
+  s.grown = 0;
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;
@@ -552,7 +557,7 @@ int sphb200_session_resize(sphb200_ctx* ctx, int64_t n, int64_t n_owned, void* s
   Session& s = sess(ctx);
   if (s.k <= 0) SPH_FAIL("session_resize: no session to resize");
   s.n = n; s.n_owned = n_owned;
-  s.has_list = 0; s.pos_valid = 0; s.id_cur = 0; s.knnh_cur = 0; s.drag = 0;
+  s.has_list = 0; s.pos_valid = 0; s.id_cur = 0; s.knnh_cur = 0; s.drag = 0; s.grown = 0;
   for (int f = 0; f < F_NFIELDS; ++f) {
     s.cur[f] = 0;
     SPH_TRY(devbuf_reserve(ctx->sbuf[2 * f], (size_t)n * kFieldWidth[f] * sizeof(double)));
@@ -590,6 +595,18 @@ static int find_field(const char* name) {
   return -1;
 }
 
+// (N,k) int64 neighbour rows in the caller's order and index space -> int32 list in the session's order
+__global__ void __launch_bounds__(256)
+list_in_kernel(int n, int k, const uint32_t* __restrict__ id, const uint32_t* __restrict__ pos,
+               const int64_t* __restrict__ nb, int32_t* __restrict__ list, int* __restrict__ flags) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= (int64_t)n * k) return;
+  const int i = (int)(t / k), c = (int)(t % k);
+  const int64_t j = nb[(int64_t)id[i] * k + c];
+  if (j < 0 || j > n) { atomicAdd(&flags[FL_BAD_INDEX], 1); list[t] = n; return; }
+  list[t] = (j == n) ? n : (int32_t)pos[j];            // n = the reference's "missing neighbour" index
+}
+
 // src: device pointer, caller's particle order, `count` doubles
 int sphb200_session_upload(sphb200_ctx* ctx, const char* name, const void* src, int64_t count, void* stream) {
   if (!ctx || !name || !src) SPH_FAIL("session_upload: null argument");
@@ -600,6 +617,24 @@ int sphb200_session_upload(sphb200_ctx* ctx, const char* name, const void* src, 
   if (sc >= 0) {
     if (count != 1) SPH_FAIL("session_upload: '%s' is one value", name);
     CUDA_TRY(cudaMemcpyAsync(bufp<double>(ctx->scal) + sc, src, sizeof(double), cudaMemcpyDeviceToDevice, st));
+    return 0;
+  }
+  if (!strcmp(name, "neighbor")) {      // a saved neighbour array (checkpoint restart): (N,k) int64, caller's indices
+    if (count != s.n * s.k) SPH_FAIL("session_upload: neighbor needs %lld values", (long long)(s.n * s.k));
+    SPH_TRY(devbuf_reserve(ctx->list, (size_t)s.n * s.k * sizeof(int32_t)));
+    SPH_TRY(devbuf_reserve(ctx->sbuf[SB_POS], s.n * sizeof(uint32_t)));
+    const uint32_t* idp = bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]);
+    uint32_t* pos = bufp<uint32_t>(ctx->sbuf[SB_POS]);
+    if (!s.pos_valid) {
+      invert_id_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, idp, pos);
+      s.pos_valid = 1;
+      ctx->launches += 1;
+    }
+    list_in_kernel<<<ceil_div(s.n * s.k, 256), 256, 0, st>>>((int)s.n, s.k, idp, pos, (const int64_t*)src,
+                                                            bufp<int32_t>(ctx->list), bufp<int>(ctx->flags));
+    ctx->launches += 1;
+    CUDA_TRY(cudaGetLastError());
+    s.has_list = 1;
     return 0;
   }
   const int f = find_field(name);
@@ -727,6 +762,60 @@ int sphb200_session_upload_rows(sphb200_ctx* ctx, const double* rows, int64_t n_
   rows_in_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, ncol, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]), rows, a);
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// grow a buffer to `bytes`, keeping its first `keep` bytes (devbuf_reserve alone discards the content)
+static int devbuf_grow(DevBuf& b, size_t keep, size_t bytes, cudaStream_t st) {
+  if (bytes <= b.bytes) return 0;
+  DevBuf nb;
+  SPH_TRY(devbuf_reserve(nb, bytes + bytes / 4));          // head-room: injections come in bursts
+  if (b.p && keep) CUDA_TRY(cudaMemcpyAsync(nb.p, b.p, keep, cudaMemcpyDeviceToDevice, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  devbuf_free(b);
+  b = nb;
+  return 0;
+}
+
+// F4: variable-N state (the driver grows every array when a supernova injects particles,
+// code_running.py:361-381).  The new particles get caller indices N .. N+n_new-1; existing particles keep
+// theirs.  rows: (n_new, ncol >= 18) device doubles in the row layout of sphb200_session_upload_rows.
+// The neighbour list is invalid afterwards: run the phases "sort" and "knn" (the driver's own
+// nsc.neighbors call at :386) before the next step.  The first step after an append takes
+// dv = a dt and new_smoothing = 1 like the reference does when its old arrays are shorter (:484-485, :534-535).
+int sphb200_session_append_rows(sphb200_ctx* ctx, const double* rows, int64_t n_new, int ncol, void* stream) {
+  if (!ctx || (!rows && n_new > 0)) SPH_FAIL("session_append_rows: null argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  Session& s = sess(ctx);
+  if (s.k <= 0) SPH_FAIL("session_append_rows: no session");
+  if (n_new < 0 || ncol < ROW_STATE_COLS) SPH_FAIL("session_append_rows: needs (n_new >= 0, ncol >= 18), got (%lld, %d)", (long long)n_new, ncol);
+  if (s.n_owned >= 0) SPH_FAIL("session_append_rows: not available on a slab with ghosts (re-seat the slab instead)");
+  if (n_new == 0) return 0;
+  const int64_t n0 = s.n, n1 = s.n + n_new;
+  if (n1 >= (int64_t)0x7fffffff) SPH_FAIL("session_append_rows: too many particles");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  for (int f = 0; f < F_NFIELDS; ++f) {
+    const size_t w = kFieldWidth[f] * sizeof(double);
+    SPH_TRY(devbuf_grow(ctx->sbuf[2 * f + s.cur[f]], (size_t)n0 * w, (size_t)n1 * w, st));
+    SPH_TRY(devbuf_reserve(ctx->sbuf[2 * f + (s.cur[f] ^ 1)], (size_t)n1 * w + (size_t)n1 * w / 4));
+  }
+  SPH_TRY(devbuf_grow(ctx->sbuf[SB_ID + s.id_cur], n0 * sizeof(uint32_t), n1 * sizeof(uint32_t), st));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_ID + (s.id_cur ^ 1)], n1 * sizeof(uint32_t) + n1));
+  SPH_TRY(devbuf_grow(ctx->sbuf[SB_KNNH + s.knnh_cur], n0 * sizeof(double), n1 * sizeof(double), st));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_KNNH + (s.knnh_cur ^ 1)], n1 * sizeof(double) + 2 * n1));
+  for (int o = 0; o < O_NOUT; ++o) SPH_TRY(devbuf_reserve(ctx->sbuf[SB_OUT + o], (size_t)n1 * kOutWidth[o] * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_NONTRIV], n1 * sizeof(int32_t)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_DISTSQ], n1 * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_DISTSQ_ALT], n1 * sizeof(double)));
+  RowArgs a;
+  for (int f = 0; f < F_NFIELDS; ++f) a.f[f] = fld(ctx, f) + (size_t)n0 * kFieldWidth[f];
+  a.knnh = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]) + n0;
+  rows_in_kernel<<<ceil_div(n_new, 256), 256, 0, st>>>((int)n_new, ncol, nullptr, rows, a);
+  iota_kernel<<<ceil_div(n_new, 256), 256, 0, st>>>((int)n_new, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]) + n0, (uint32_t)n0);
+  ctx->launches += 2;
+  CUDA_TRY(cudaGetLastError());
+  s.n = n1;
+  s.has_list = 0; s.pos_valid = 0; s.drag = 0; s.grown = 1;
   return 0;
 }
 

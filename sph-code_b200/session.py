@@ -30,6 +30,7 @@ class Session(object):
         self.n = int(n)
         self.k = int(k)
         self.device = torch.device("cuda", self.ctx.device)
+        self.dist, self.dt_0 = float(dist), float(dt_0)
         _lib.check(self.lib.sphb200_session_create(self.ctx.handle, self.n, self.k, float(dist)))
         for name, val in (("dt_0", dt_0), ("MAX_AGE", C.MAX_AGE), ("N_INT_PER_PARTICLE", C.N_INT_PER_PARTICLE),
                           ("raise_factor", C.raise_factor), ("AU", C.AU)):
@@ -46,6 +47,8 @@ class Session(object):
 
     def set_scalar(self, name, value):
         _lib.check(self.lib.sphb200_session_set_scalar(self.ctx.handle, name.encode(), float(value)))
+        if name in ("dist", "dt_0"):
+            setattr(self, name, float(value))
 
     def scalar(self, name):
         out = ctypes.c_double(0.0)
@@ -118,10 +121,49 @@ class Session(object):
         _lib.check(self.lib.sphb200_session_upload_rows(self.ctx.handle, ctypes.c_void_p(rows.data_ptr()), self.n,
                                                         int(rows.shape[1]), self._stream()))
 
+    def append_rows(self, rows):
+        """SURVEY row F4 (code_running.py:361-381): append particles (rows in the layout of upload_rows) as
+        caller indices N .. N+n_new-1.  Call search() before the next step, as the driver calls
+        nsc.neighbors at :386."""
+        if (not torch.is_tensor(rows) or rows.dim() != 2 or rows.dtype != torch.float64 or not rows.is_cuda
+                or not rows.is_contiguous() or rows.shape[1] < 18):
+            raise ValueError("append_rows needs a contiguous float64 CUDA tensor (n_new, >=18)")
+        _lib.check(self.lib.sphb200_session_append_rows(self.ctx.handle, ctypes.c_void_p(rows.data_ptr()),
+                                                        int(rows.shape[0]), int(rows.shape[1]), self._stream()))
+        torch.cuda.current_stream(self.device).synchronize()      # `rows` may be freed by the caller
+        self.n += int(rows.shape[0])
+
+    def append(self, state):
+        """append() for a dict of host arrays keyed like upload() (missing fields are zero)."""
+        m = len(state["points"])
+        rows = np.zeros((m, 18))
+        col = 0
+        for name, w in STATE_FIELDS.items():
+            if state.get(name) is not None:
+                rows[:, col:col + w] = np.asarray(state[name], dtype=np.float64).reshape(m, w)
+            col += w
+        self.append_rows(torch.from_numpy(rows).to(self.device))
+
+    def search(self):
+        """Neighbour query on the current positions (nsc.neighbors, code_running.py:386): fills
+        neighbor / num_nontrivial and overwrites sizes with the k-th neighbour distance."""
+        self.phase("sort")
+        self.phase("knn")
+
     def download(self, name):
         return self.download_tensor(name).cpu().numpy()
 
     # -- the path ---------------------------------------------------------------------------
+    def upload_neighbor(self, neighbor):
+        """Restore a saved (N,k) neighbour array (caller's indices; N = missing neighbour)."""
+        nb = torch.as_tensor(np.ascontiguousarray(np.asarray(neighbor), dtype=np.int64)).to(self.device)
+        if tuple(nb.shape) != (self.n, self.k):
+            raise ValueError("neighbor must be (%d, %d)" % (self.n, self.k))
+        _lib.check(self.lib.sphb200_session_upload(self.ctx.handle, b"neighbor", ctypes.c_void_p(nb.data_ptr()),
+                                                   self.n * self.k, self._stream()))
+        torch.cuda.current_stream(self.device).synchronize()
+        self.check()
+
     def set_drag(self, f_un):
         """Dust-gas drag of code_running.py:455,462-463,473 in the force phase (`net_impulse`, nsc:719-742):
         f_un is the (N, n_species) composition in the caller's order; None switches the drag off."""

@@ -136,3 +136,82 @@ def test_steps_with_drag(built_lib):
     s.step(); s.check()
     ref = O.step(ref)
     assert rel(s.download("visc_accel"), ref["visc_accel"]) < RTOL
+
+
+def test_append_particles(built_lib):
+    """SURVEY row F4, variable-N state: particles injected mid-run the way code_running.py:361-386 grows
+    its arrays (concatenate, then nsc.neighbors).  The step after the injection takes dv = a dt and
+    new_smoothing = 1 (old arrays shorter, :484-485 / :534-535); later steps are ordinary again."""
+    from sphb200 import ics
+    from sphb200.session import Session
+    st = ics.uniform_box(4000, 6, n_dust=20)
+    st["dt_0"] = O.dt_0 * 1e-6
+    extra = ics.uniform_box(700, 7, n_dust=30)                 # the injected particles: same box, own draw
+    extra["points"] *= 0.5
+    s = Session(len(st["points"]), st["N_NEIGH"], st["dist"], dt_0=st["dt_0"])
+    s.upload(st)
+    s.startup()
+    ref = O.startup(st)
+    fields = ("points", "velocities", "total_accel", "E_internal", "T", "sizes", "densities", "densities_0")
+
+    def same(tag):
+        assert np.array_equal(s.download("neighbor"), ref["neighbor"]), tag
+        for name in fields:
+            assert rel(s.download(name), ref[name]) < RTOL, (tag, name)
+
+    for it in range(2):
+        s.step(); s.check(); ref = O.step(ref)
+    same("before")
+    s.append(extra)
+    s.search()
+    ref = O.append(ref, extra)
+    n1 = len(st["points"]) + len(extra["points"])
+    assert s.n == n1 and s.download("points").shape == (n1, 3)
+    assert np.array_equal(s.download("neighbor"), ref["neighbor"])
+    assert np.array_equal(s.download("sizes"), ref["sizes"])
+    assert np.array_equal(s.download("particle_type"), ref["particle_type"])
+    s.step(); s.check(); ref = O.step(ref)                     # the odd step
+    same("grown step")
+    for it in range(2):
+        s.step(); s.check(); ref = O.step(ref)
+    same("after")
+    # a second, larger injection forces the buffers to be re-allocated
+    big = ics.uniform_box(3000, 8)
+    s.append(big); s.search(); ref = O.append(ref, big)
+    s.step(); s.check(); ref = O.step(ref)
+    same("second injection")
+    with pytest.raises(ValueError):
+        s.append_rows(np.zeros((3, 18)))
+
+
+def test_checkpoint_restart(built_lib, tmp_path):
+    """Particle checkpoint (the reference has none): 2 steps, save, reload into a new
+    session, 3 more steps == 5 uninterrupted steps.  Neighbour rows identical; sums to 1e-13 (the reloaded
+    state enters the cell sort in the caller's order, so rows may list equal neighbours in another order)."""
+    from sphb200 import ics, config_io
+    from sphb200.session import Session
+    st = ics.uniform_box(6000, 11, n_dust=25)
+    st["dt_0"] = O.dt_0 * 1e-6
+    a = Session(len(st["points"]), st["N_NEIGH"], st["dist"], dt_0=st["dt_0"])
+    a.upload(st); a.startup()
+    for _ in range(2):
+        a.step()
+    path = config_io.save_checkpoint(str(tmp_path / "particles"), a, f_un=st["f_un"])
+    saved = {name: a.download(name) for name in ("points", "velocities", "sizes", "densities_0")}
+    for _ in range(3):
+        a.step()
+    a.check()
+    want = {name: a.download(name) for name in ("points", "velocities", "total_accel", "E_internal", "T", "sizes")}
+    want_nb = a.download("neighbor")
+    want_scal = [a.scalar(x) for x in ("age", "dt", "d", "ct")]
+    b, extra = config_io.load_checkpoint(path)
+    assert np.array_equal(extra["f_un"], st["f_un"])
+    for name, v in saved.items():
+        assert np.array_equal(b.download(name), v), name
+    for _ in range(3):
+        b.step()
+    b.check()
+    assert np.array_equal(b.download("neighbor"), want_nb)
+    for name, v in want.items():
+        assert rel(b.download(name), v) < 1e-13, name
+    assert [b.scalar(x) for x in ("age", "dt", "d", "ct")] == pytest.approx(want_scal, rel=1e-13)
