@@ -359,8 +359,9 @@ def run_e2e(sess, world, dev, K, W, n_total, barrier):
     ms = [float(x) for x in ms]
     return {"value": n_total * K / (ms[0] * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(ms[2]),
             "d2h_bytes_per_step": int(ms[3]), "ms_per_step": ms[0] / K, "wall_ms_per_step": ms[1] / K,
-            "api": "Session.step_host: pinned host state -> sphb200_session_upload -> sphb200_session_step -> "
-                   "sphb200_session_download -> pinned host"}
+            "api": "Session.step_host: pinned host state -> sphb200_session_upload -> sphb200_session_phase (the nine "
+                   "phases of the step; the copy of the late fields runs under the k-NN) -> sphb200_session_download "
+                   "-> pinned host"}
 
 
 def main():

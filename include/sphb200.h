@@ -110,7 +110,9 @@ int sphb200_session_download(sphb200_ctx* ctx, const char* field, void* dst, int
  * further columns belong to the caller.  download writes rows [0, n_rows); upload needs n_rows == N.
  * Also accepted by upload/download by name: "densities", "visc_pi", "knn_h" (owner-computed values a
  * slab decomposition overwrites for ghost particles) and, download only, "dist_sq".
- * Extra phases: "kick", "length", "smooth" (the three parts of "integrate"), "rho0". */
+ * Extra phases: "kick", "length", "smooth" (the three parts of "integrate"), "rho0"; "sort_keys" = "sort"
+ * that carries only points, velocities and particle_type into the new order: a host-resident step uploads
+ * the other fields afterwards (uploads land in the current order), overlapping the copy with the search. */
 /* one field at `count` caller indices (device int64): out/in is (count, width) doubles */
 int sphb200_session_gather(sphb200_ctx* ctx, const char* field, const int64_t* idx, int64_t count, double* out, void* stream);
 int sphb200_session_scatter(sphb200_ctx* ctx, const char* field, const int64_t* idx, int64_t count, const double* in, void* stream);

@@ -97,18 +97,19 @@ struct ReorderArgs {
   const double* knnh_src; double* knnh_dst;
 };
 
-__global__ void __launch_bounds__(256) reorder_kernel(int n, const uint32_t* __restrict__ perm, ReorderArgs a) {
+__global__ void __launch_bounds__(256) reorder_kernel(int n, const uint32_t* __restrict__ perm, ReorderArgs a, unsigned mask) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int64_t p = perm[i];
 #pragma unroll
   for (int f = 0; f < 3; ++f) {
+    if (!(mask >> f & 1u)) continue;
     a.dst[f][3 * (int64_t)i + 0] = a.src[f][3 * p + 0];
     a.dst[f][3 * (int64_t)i + 1] = a.src[f][3 * p + 1];
     a.dst[f][3 * (int64_t)i + 2] = a.src[f][3 * p + 2];
   }
 #pragma unroll
-  for (int f = 3; f < F_NFIELDS; ++f) a.dst[f][i] = a.src[f][p];
+  for (int f = 3; f < F_NFIELDS; ++f) if (mask >> f & 1u) a.dst[f][i] = a.src[f][p];
   a.id_dst[i] = a.id_src[p];
   a.knnh_dst[i] = a.knnh_src[p];
 }
@@ -376,7 +377,11 @@ static int phase_dt_clamp(sphb200_ctx* ctx, cudaStream_t st) {
 }
 
 // cell build + state reorder                                             (replaces nsc:542)
-static int phase_sort(sphb200_ctx* ctx, cudaStream_t st) {
+// `mask` selects the state fields that are carried into the new order (bit f = Field f).  The full step
+// carries all of them.  A host-resident step ("sort_keys") carries only what is already on the device and
+// still needed there -- positions, velocities, particle type -- and lets the remaining fields be uploaded
+// straight into the new order while the search runs (uploads gather through the current `id`).
+static int phase_sort(sphb200_ctx* ctx, cudaStream_t st, unsigned mask = ~0u) {
   Session& s = sess(ctx);
   SPH_TRY(build_cells(ctx, fld(ctx, F_POS), s.n, ctx->cell_edge, st));
   ReorderArgs a;
@@ -385,9 +390,9 @@ static int phase_sort(sphb200_ctx* ctx, cudaStream_t st) {
   a.id_dst = bufp<uint32_t>(ctx->sbuf[SB_ID + (s.id_cur ^ 1)]);
   a.knnh_src = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]);
   a.knnh_dst = bufp<double>(ctx->sbuf[SB_KNNH + (s.knnh_cur ^ 1)]);
-  reorder_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, bufp<uint32_t>(ctx->perm), a);
+  reorder_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, bufp<uint32_t>(ctx->perm), a, mask);
   ctx->launches += 1;
-  for (int f = 0; f < F_NFIELDS; ++f) s.cur[f] ^= 1;
+  for (int f = 0; f < F_NFIELDS; ++f) if (mask >> f & 1u) s.cur[f] ^= 1;
   s.id_cur ^= 1;
   s.knnh_cur ^= 1;
   s.has_list = 0;
@@ -920,6 +925,7 @@ int sphb200_session_phase(sphb200_ctx* ctx, const char* phase, void* stream) {
   if (!strcmp(phase, "crossing")) return phase_crossing(ctx, st);
   if (!strcmp(phase, "dt_clamp")) return phase_dt_clamp(ctx, st);
   if (!strcmp(phase, "sort")) return phase_sort(ctx, st);
+  if (!strcmp(phase, "sort_keys")) return phase_sort(ctx, st, 1u << F_POS | 1u << F_VEL | 1u << F_TYPE);
   if (!strcmp(phase, "knn")) return phase_knn(ctx, st);
   if (!strcmp(phase, "pack")) return phase_pack(ctx, st);
   if (!strcmp(phase, "density")) return phase_density(ctx, st);

@@ -20,6 +20,10 @@ RESULT_FIELDS = {"densities": 1, "num_densities": 1, "dust_densities": 1, "visc_
                  "visc_accel": 3, "pressure_accel": 3}
 # owner-computed per-particle arrays the slab-decomposed driver reads / overwrites for ghosts (domain.py)
 AUX_FIELDS = {"densities": 1, "visc_pi": 1, "knn_h": 1, "dist_sq": 1}
+# host-resident stepping (step_host): what crossing time / clamp / cell build / k-NN read, and what must
+# be re-uploaded after the early sort because "sort_keys" does not carry it into the new order
+HOST_EARLY_FIELDS = ("points", "velocities", "sizes", "particle_type")
+HOST_LATE_FIELDS = ("total_accel", "mass", "T", "E_internal", "mu_array", "gamma_array", "densities_0")
 PHASES = ("crossing", "dt_clamp", "sort", "knn", "pack", "density", "pi", "force", "integrate")
 
 
@@ -211,26 +215,59 @@ class Session(object):
 
     # -- host-resident state (the call a user of the reference makes: numpy arrays in, arrays out) --
     def make_host_state(self, upload_fields, download_fields):
-        """Pinned host buffers holding the current state (inputs) and room for the results."""
-        hs = {"in": {}, "out": {}, "upload": tuple(upload_fields), "download": tuple(download_fields)}
+        """Pinned host buffers holding the current state (inputs) and room for the results, plus the
+        device staging buffers and the copy stream step_host() uses."""
+        hs = {"in": {}, "out": {}, "stage": {}, "upload": tuple(upload_fields), "download": tuple(download_fields)}
         for f in upload_fields:
             hs["in"][f] = self.download_tensor(f).cpu().pin_memory()
+            hs["stage"][f] = torch.empty_like(hs["in"][f], device=self.device)
         for f in download_fields:
             w = STATE_FIELDS.get(f) or RESULT_FIELDS[f]
             hs["out"][f] = torch.empty((self.n, w) if w > 1 else (self.n,), dtype=torch.float64).pin_memory()
         hs["h2d_bytes"] = sum(t.numel() * 8 for t in hs["in"].values())
         hs["d2h_bytes"] = sum(t.numel() * 8 for t in hs["out"].values())
+        hs["copy_stream"] = torch.cuda.Stream(device=self.device)
+        # fields the step reads before / during the neighbour search; the rest may arrive while it runs
+        hs["early"] = tuple(f for f in upload_fields if f in HOST_EARLY_FIELDS)
+        hs["late"] = tuple(f for f in upload_fields if f not in HOST_EARLY_FIELDS)
+        hs["overlap"] = set(HOST_EARLY_FIELDS) <= set(upload_fields) and set(HOST_LATE_FIELDS) <= set(upload_fields)
         return hs
 
     def step_host(self, hs):
-        """One time step of a host-resident state: upload every input field from pinned memory, step,
-        download the advanced fields into pinned memory, and make them the next step's inputs."""
-        for f in hs["upload"]:
-            self.upload_tensor(f, hs["in"][f].to(self.device, non_blocking=True))
-        self.step()
+        """One time step of a host-resident state: every input field is copied from pinned memory, the step
+        runs, the advanced fields are copied back to pinned memory and become the next step's inputs.
+        The copy of the fields that are first read after the neighbour search (72 of the 136 B/particle)
+        runs on a second stream underneath crossing time, cell build and k-NN: the early phase "sort_keys"
+        carries only points / velocities / particle_type into the new order, and the late fields are then
+        uploaded straight into it."""
+        cur = torch.cuda.current_stream(self.device)
+        if not hs.get("overlap"):
+            for f in hs["upload"]:
+                self.upload_tensor(f, hs["in"][f].to(self.device, non_blocking=True))
+            self.step()
+        else:
+            cs = hs["copy_stream"]
+            cs.wait_stream(cur)                                   # the staging buffers are free again
+            with torch.cuda.stream(cs):
+                for f in hs["early"]:
+                    hs["stage"][f].copy_(hs["in"][f], non_blocking=True)
+                ev_early = cs.record_event()
+                for f in hs["late"]:
+                    hs["stage"][f].copy_(hs["in"][f], non_blocking=True)
+                ev_late = cs.record_event()
+            cur.wait_event(ev_early)
+            for f in hs["early"]:
+                self.upload_tensor(f, hs["stage"][f])
+            for ph in ("crossing", "dt_clamp", "sort_keys", "knn"):
+                self.phase(ph)
+            cur.wait_event(ev_late)
+            for f in hs["late"]:
+                self.upload_tensor(f, hs["stage"][f])             # gathers through the new id: lands in the new order
+            for ph in ("pack", "density", "pi", "force", "integrate"):
+                self.phase(ph)
         for f in hs["download"]:
             hs["out"][f].copy_(self.download_tensor(f), non_blocking=True)
-        torch.cuda.current_stream(self.device).synchronize()      # the caller reads the result
+        cur.synchronize()                                         # the caller reads the result
         for f in hs["download"]:
             if f in hs["in"]:
                 hs["in"][f], hs["out"][f] = hs["out"][f], hs["in"][f]

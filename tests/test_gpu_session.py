@@ -215,3 +215,33 @@ def test_checkpoint_restart(built_lib, tmp_path):
     for name, v in want.items():
         assert rel(b.download(name), v) < 1e-13, name
     assert [b.scalar(x) for x in ("age", "dt", "d", "ct")] == pytest.approx(want_scal, rel=1e-13)
+
+
+@pytest.mark.parametrize("fields", ["all", "partial"])
+def test_host_resident_step(built_lib, fields):
+    """Session.step_host (the call bench.py's e2e leg times): state in pinned host memory, copied in and
+    out every step.  With every field uploaded the copy of the late fields overlaps the neighbour search
+    (phase "sort_keys"); with a partial set the plain path runs.  Both must equal step() on the device."""
+    from sphb200 import ics
+    from sphb200.session import Session, STATE_FIELDS
+    st = ics.uniform_box(20000, 12, n_dust=40)
+    st["dt_0"] = O.dt_0 * 1e-6
+    up = tuple(STATE_FIELDS) if fields == "all" else ("points", "velocities", "sizes", "T", "E_internal")
+    down = ("points", "velocities", "total_accel", "sizes", "T", "E_internal", "densities_0", "densities")
+    a = Session(len(st["points"]), st["N_NEIGH"], st["dist"], dt_0=st["dt_0"])
+    a.upload(st); a.startup()
+    hs = a.make_host_state(up, down)
+    assert hs["overlap"] == (fields == "all")
+    ref = O.startup(st)
+    for it in range(3):
+        a.step_host(hs)
+        a.check()
+        ref = O.step(ref)
+        assert np.array_equal(a.download("neighbor"), ref["neighbor"])
+        for f in ("points", "velocities", "total_accel", "sizes", "T", "E_internal", "densities_0"):
+            back = hs["in"][f] if f in hs["in"] else hs["out"][f]                         # what came back to the host
+            assert rel(back.numpy().reshape(ref[f].shape), ref[f]) < RTOL, (it, f)
+            assert rel(a.download(f), ref[f]) < RTOL, (it, f)
+        assert rel(hs["out"]["densities"].numpy(), ref["densities"]) < RTOL
+        for f in ("mass", "mu_array", "gamma_array", "particle_type"):
+            assert np.array_equal(a.download(f), st[f]), f
