@@ -109,7 +109,8 @@ int sphb200_session_download(sphb200_ctx* ctx, const char* field, void* dst, int
  * state fields in the order listed above, column 17 the k-NN trial radius (previous k-th distance);
  * further columns belong to the caller.  download writes rows [0, n_rows); upload needs n_rows == N.
  * Also accepted by upload/download by name: "densities", "visc_pi", "knn_h" (owner-computed values a
- * slab decomposition overwrites for ghost particles) and, download only, "dist_sq".
+ * slab decomposition overwrites for ghost particles) and, download only, "dist_sq" (|x|^2 of the slow
+ * owned particles, +inf for the rest).
  * Extra phases: "kick", "length", "smooth" (the three parts of "integrate"), "rho0"; "sort_keys" = "sort"
  * that carries only points, velocities and particle_type into the new order: a host-resident step uploads
  * the other fields afterwards (uploads land in the current order), overlapping the copy with the search. */
@@ -140,6 +141,11 @@ int sphb200_session_startup(sphb200_ctx* ctx, void* stream);
 /* one pass of the while-body, code_running.py:217-540 (gas/dust only, gravity and chemistry zero; drag as
  * set by sphb200_session_set_drag, off by default) */
 int sphb200_session_step(sphb200_ctx* ctx, void* stream);
+/* device pointer + element count of an internal array a caller-side collective works on in place:
+ * "length_hist": int64 histogram of the percentile's radix select (code_running.py:515-518), valid between
+ * the phases "length_hist" and "length_pick"; a slab decomposition all_reduces (SUM) it there, five times
+ * per step ("length_begin", then 5 x ("length_hist", all_reduce, "length_pick")). */
+int sphb200_session_buffer(sphb200_ctx* ctx, const char* name, void** ptr, int64_t* count);
 /* one phase of the step, for per-kernel timing: "crossing", "dt_clamp", "sort", "knn", "pack",
  * "density", "pi", "force", "integrate" */
 int sphb200_session_phase(sphb200_ctx* ctx, const char* phase, void* stream);

@@ -23,7 +23,6 @@ static const char* kOutName[O_NOUT] = {"densities", "num_densities", "dust_densi
 #define SB_OUT 26            // .. 26 + O_NOUT
 #define SB_NONTRIV 34
 #define SB_DISTSQ 35
-#define SB_DISTSQ_ALT 36
 #define SB_KNNH 37           // k-th neighbour distance of the last search (guess for the next one)
 #define SB_KNNH_ALT 38
 #define SB_POS 39            // caller index -> sorted position (inverse of id), built on demand
@@ -172,24 +171,135 @@ integrate_kernel(int n, const double* __restrict__ scal, double kB, double m_h, 
   if (threadIdx.x == 0 && cnt) atomicAdd(nslow, (unsigned long long)cnt);
 }
 
-// ---- A12: global length scale from the 90th percentile              code_running.py:515-524 ----
-// `sorted` holds |x|^2 of slow particles ascending (+inf for the rest); numpy's linear percentile.
-__global__ void length_scale_kernel(const double* __restrict__ sorted, const unsigned long long* nslow, double* scal,
-                                    double n_int) {
-  const unsigned long long ns = *nslow;
-  scal[SC_NSLOW] = (double)ns;
-  if (ns == 0) { scal[SC_MAXDIST] = nan(""); scal[SC_D] = nan(""); return; }
-  const double pos = 0.9 * (double)(ns - 1);
-  const unsigned long long lo = (unsigned long long)floor(pos);
-  const double t = pos - (double)lo;
-  const double a = sorted[lo];
-  const double b = sorted[lo + 1 < ns ? lo + 1 : lo];
-  const double diff = b - a;
-  double v = a + diff * t;                              // numpy _lerp
-  if (t >= 0.5) v = b - diff * (1.0 - t);
-  scal[SC_MAXDIST] = v;
-  const double V_new = v * sqrt(v);                     // max_dist ** 1.5
-  scal[SC_D] = cbrt(V_new / (double)ns / 0.9 * n_int);  // :521
+// ---- A12: exact percentile by radix select (no sort)                  code_running.py:515-518 ----
+// np.percentile(dist_sq[slow], 90) needs two order statistics of |x|^2: ranks lo = floor(0.9 (ns-1)) and
+// lo+1.  Non-negative doubles order like their bit patterns, so both are found by a most-significant-digit
+// radix select: five passes of 13,13,13,13,12 bits, each one histogram over the keys that still match the
+// selected prefix (shared-memory bins, flushed with one global add per non-empty bin) and one single-block
+// pick.  The two ranks share a prefix until they fall into different bins; from then on the second prefix
+// is tracked with direct global adds (its population is ~n/8192 by then).  Excluded particles carry +inf
+// and sort after every finite key.  Between `hist` and `pick` a slab decomposition all_reduces the
+// histogram (2*8192 counts + the slow count), which makes the select exact across ranks in five small
+// collectives; on one GPU the ten kernels run back to back.
+#define SEL_BINS 8192
+#define SEL_HIST (2 * SEL_BINS + 1)                      // [A bins | B bins | slow count]
+#define SEL_PASSES 5
+struct SelectState {
+  unsigned long long prefix[2];                          // selected high bits of the two order statistics
+  unsigned long long rank[2];                            // remaining rank inside the prefix
+  unsigned long long ns;                                 // slow particles (all ranks)
+  double frac;                                           // 0.9 (ns-1) - lo
+  int pass;                                              // next pass, 0 .. SEL_PASSES
+  int split;                                             // the two prefixes differ
+};
+__host__ __device__ __forceinline__ int sel_width(int pass) { return pass < 4 ? 13 : 12; }
+__host__ __device__ __forceinline__ int sel_consumed(int pass) { return 13 * pass; }
+
+__global__ void select_reset_kernel(SelectState* st, long long* hist) {
+  for (int b = threadIdx.x; b < SEL_HIST; b += blockDim.x) hist[b] = 0;
+  if (threadIdx.x == 0) { st->prefix[0] = st->prefix[1] = 0; st->rank[0] = st->rank[1] = 0; st->ns = 0; st->frac = 0; st->pass = 0; st->split = 0; }
+}
+
+__global__ void __launch_bounds__(1024)
+select_hist_kernel(int n, const double* __restrict__ keys, const SelectState* __restrict__ st,
+                   const unsigned long long* __restrict__ nslow_local, long long* __restrict__ hist) {
+  __shared__ unsigned int bins[SEL_BINS];
+  const int pass = st->pass;
+  if (pass >= SEL_PASSES) return;
+  for (int b = threadIdx.x; b < SEL_BINS; b += blockDim.x) bins[b] = 0;
+  __syncthreads();
+  const int cons = sel_consumed(pass), w = sel_width(pass);
+  const unsigned long long pa = st->prefix[0], pb = st->prefix[1];
+  const int split = st->split;
+  const unsigned long long dmask = (1ull << w) - 1ull;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const unsigned long long key = (unsigned long long)__double_as_longlong(keys[i]);
+    const unsigned long long pre = cons ? (key >> (64 - cons)) : 0ull;
+    const unsigned int dig = (unsigned int)((key >> (64 - cons - w)) & dmask);
+    if (pre == pa) atomicAdd(&bins[dig], 1u);
+    else if (split && pre == pb) atomicAdd((unsigned long long*)&hist[SEL_BINS + dig], 1ull);
+  }
+  __syncthreads();
+  for (int b = threadIdx.x; b < SEL_BINS; b += blockDim.x)
+    if (bins[b]) atomicAdd((unsigned long long*)&hist[b], (unsigned long long)bins[b]);
+  if (pass == 0 && blockIdx.x == 0 && threadIdx.x == 0) hist[2 * SEL_BINS] = (long long)*nslow_local;
+}
+
+// one block of 1024 threads; every thread owns 8 consecutive bins
+__device__ int sel_find(const long long* __restrict__ h, unsigned long long rank, unsigned long long* rank_out,
+                        unsigned long long* sh) {
+  const int t = threadIdx.x;
+  unsigned long long loc[8], sum = 0;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) { loc[q] = (unsigned long long)h[t * 8 + q]; sum += loc[q]; }
+  sh[t] = sum;
+  __syncthreads();
+  for (int off = 1; off < 1024; off <<= 1) {              // inclusive scan of the per-thread sums
+    const unsigned long long v = (t >= off) ? sh[t - off] : 0ull;
+    __syncthreads();
+    sh[t] += v;
+    __syncthreads();
+  }
+  const unsigned long long before = sh[t] - sum;
+  __shared__ int found;
+  __shared__ unsigned long long found_rank;
+  if (t == 0) { found = SEL_BINS - 1; found_rank = 0; }
+  __syncthreads();
+  if (rank >= before && rank < before + sum) {
+    unsigned long long c = before;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      if (rank >= c && rank < c + loc[q]) { found = t * 8 + q; found_rank = rank - c; }
+      c += loc[q];
+    }
+  }
+  __syncthreads();
+  *rank_out = found_rank;
+  const int r = found;
+  __syncthreads();
+  return r;
+}
+
+__global__ void __launch_bounds__(1024)
+select_pick_kernel(SelectState* st, long long* __restrict__ hist, double* __restrict__ scal, double n_int) {
+  __shared__ unsigned long long sh[1024];
+  const int pass = st->pass;
+  if (pass >= SEL_PASSES) return;
+  unsigned long long ns = st->ns, rA = st->rank[0], rB = st->rank[1];
+  double frac = st->frac;
+  if (pass == 0) {
+    ns = (unsigned long long)hist[2 * SEL_BINS];
+    const double pos = 0.9 * (double)(ns ? ns - 1 : 0);
+    rA = (unsigned long long)floor(pos);
+    frac = pos - (double)rA;
+    rB = (rA + 1 < ns) ? rA + 1 : rA;
+  }
+  if (ns == 0) {                                           // no slow particle: np.percentile raises; report NaN
+    __syncthreads();
+    if (threadIdx.x == 0) { scal[SC_NSLOW] = 0.0; scal[SC_MAXDIST] = nan(""); scal[SC_D] = nan(""); st->pass = SEL_PASSES; }
+    return;
+  }
+  const int split = st->split, w = sel_width(pass);
+  unsigned long long nrA, nrB;
+  const int dA = sel_find(hist, rA, &nrA, sh);
+  const int dB = sel_find(split ? hist + SEL_BINS : hist, rB, &nrB, sh);
+  const unsigned long long pA = (st->prefix[0] << w) | (unsigned long long)dA;
+  const unsigned long long pB = (st->prefix[1] << w) | (unsigned long long)dB;
+  __syncthreads();
+  for (int b = threadIdx.x; b < SEL_HIST; b += blockDim.x) hist[b] = 0;      // ready for the next pass
+  if (threadIdx.x == 0) {
+    st->prefix[0] = pA; st->prefix[1] = pB; st->rank[0] = nrA; st->rank[1] = nrB;
+    st->ns = ns; st->frac = frac; st->split = (pA != pB); st->pass = pass + 1;
+    if (pass + 1 == SEL_PASSES) {                          // both keys complete: numpy's linear interpolation
+      const double a = __longlong_as_double((long long)pA), b = __longlong_as_double((long long)pB);
+      const double diff = b - a;
+      double v = a + diff * frac;                          // numpy _lerp
+      if (frac >= 0.5) v = b - diff * (1.0 - frac);
+      scal[SC_NSLOW] = (double)ns;
+      scal[SC_MAXDIST] = v;
+      scal[SC_D] = cbrt(v * sqrt(v) / (double)ns / 0.9 * n_int);              // :520-521
+    }
+  }
 }
 
 // ---- A12: smoothing-length update                                    code_running.py:532-540 ----
@@ -466,21 +576,41 @@ static int phase_kick(sphb200_ctx* ctx, cudaStream_t st) {
   return 0;
 }
 
-// A12: global length scale d from the 90th percentile of |x|^2 (single-GPU form; the slab-decomposed
-// driver computes d across ranks and sets the scalar instead)
-static int phase_length(sphb200_ctx* ctx, cudaStream_t st) {
-  Session& s = sess(ctx);
-  const int n = (int)s.n;
-  unsigned long long* nslow = bufp<unsigned long long>(ctx->tmp0) + 1;
-  double* dsq = bufp<double>(ctx->sbuf[SB_DISTSQ]);
-  double* dsq_sorted = bufp<double>(ctx->sbuf[SB_DISTSQ_ALT]);
-  size_t tmp = 0;
-  cub::DeviceRadixSort::SortKeys(nullptr, tmp, dsq, dsq_sorted, n, 0, 64, st);
-  SPH_TRY(devbuf_reserve(ctx->cub_tmp, tmp));
-  CUDA_TRY(cub::DeviceRadixSort::SortKeys(ctx->cub_tmp.p, tmp, dsq, dsq_sorted, n, 0, 64, st));
-  length_scale_kernel<<<1, 1, 0, st>>>(dsq_sorted, nslow, bufp<double>(ctx->scal), s.sc.n_int);
-  ctx->launches += 1 + 9;
+// A12: global length scale d from the 90th percentile of |x|^2: radix select, see select_*_kernel.
+#define SB_SEL 44            // [SEL_HIST int64 histogram | SelectState]
+static long long* sel_hist(sphb200_ctx* ctx) { return bufp<long long>(ctx->sbuf[SB_SEL]); }
+static SelectState* sel_state(sphb200_ctx* ctx) { return reinterpret_cast<SelectState*>(sel_hist(ctx) + SEL_HIST + 7); }
+
+static int phase_length_begin(sphb200_ctx* ctx, cudaStream_t st) {
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_SEL], (SEL_HIST + 8) * sizeof(long long) + sizeof(SelectState)));
+  select_reset_kernel<<<1, 1024, 0, st>>>(sel_state(ctx), sel_hist(ctx));
+  ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+static int phase_length_hist(sphb200_ctx* ctx, cudaStream_t st) {
+  Session& s = sess(ctx);
+  if (ctx->sbuf[SB_SEL].bytes == 0) SPH_FAIL("session: length_hist before length_begin");
+  const unsigned long long* nslow = bufp<unsigned long long>(ctx->tmp0) + 1;
+  select_hist_kernel<<<148, 1024, 0, st>>>((int)s.n, bufp<double>(ctx->sbuf[SB_DISTSQ]), sel_state(ctx), nslow, sel_hist(ctx));
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+static int phase_length_pick(sphb200_ctx* ctx, cudaStream_t st) {
+  Session& s = sess(ctx);
+  if (ctx->sbuf[SB_SEL].bytes == 0) SPH_FAIL("session: length_pick before length_begin");
+  select_pick_kernel<<<1, 1024, 0, st>>>(sel_state(ctx), sel_hist(ctx), bufp<double>(ctx->scal), s.sc.n_int);
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+static int phase_length(sphb200_ctx* ctx, cudaStream_t st) {
+  SPH_TRY(phase_length_begin(ctx, st));
+  for (int p = 0; p < SEL_PASSES; ++p) {
+    SPH_TRY(phase_length_hist(ctx, st));
+    SPH_TRY(phase_length_pick(ctx, st));
+  }
   return 0;
 }
 
@@ -541,7 +671,6 @@ int sphb200_session_create(sphb200_ctx* ctx, int64_t n, int k, double dist) {
   for (int o = 0; o < O_NOUT; ++o) SPH_TRY(devbuf_reserve(ctx->sbuf[SB_OUT + o], (size_t)n * kOutWidth[o] * sizeof(double)));
   SPH_TRY(devbuf_reserve(ctx->sbuf[SB_NONTRIV], n * sizeof(int32_t)));
   SPH_TRY(devbuf_reserve(ctx->sbuf[SB_DISTSQ], n * sizeof(double)));
-  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_DISTSQ_ALT], n * sizeof(double)));
   SPH_TRY(devbuf_reserve(ctx->sbuf[SB_KNNH], n * sizeof(double)));
   SPH_TRY(devbuf_reserve(ctx->sbuf[SB_KNNH_ALT], n * sizeof(double)));
   CUDA_TRY(cudaMemset(ctx->sbuf[SB_KNNH].p, 0, n * sizeof(double)));
@@ -573,7 +702,6 @@ int sphb200_session_resize(sphb200_ctx* ctx, int64_t n, int64_t n_owned, void* s
   for (int o = 0; o < O_NOUT; ++o) SPH_TRY(devbuf_reserve(ctx->sbuf[SB_OUT + o], (size_t)n * kOutWidth[o] * sizeof(double)));
   SPH_TRY(devbuf_reserve(ctx->sbuf[SB_NONTRIV], n * sizeof(int32_t)));
   SPH_TRY(devbuf_reserve(ctx->sbuf[SB_DISTSQ], n * sizeof(double)));
-  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_DISTSQ_ALT], n * sizeof(double)));
   SPH_TRY(devbuf_reserve(ctx->sbuf[SB_KNNH], n * sizeof(double)));
   SPH_TRY(devbuf_reserve(ctx->sbuf[SB_KNNH_ALT], n * sizeof(double)));
   iota_kernel<<<ceil_div(n, 256), 256, 0, st>>>((int)n, bufp<uint32_t>(ctx->sbuf[SB_ID]));
@@ -677,10 +805,6 @@ int sphb200_session_download(sphb200_ctx* ctx, const char* name, void* dst, int6
   } else if (!strcmp(name, "scalars")) {               // raw device scalars: [6] ct, [7] dt, [8] d, [9] age, [10] max_dist, [11] n_slow
     if (count < 0 || count > SC_COUNT) SPH_FAIL("session_download: scalars holds %d values", SC_COUNT);
     CUDA_TRY(cudaMemcpyAsync(dst, ctx->scal.p, (size_t)count * sizeof(double), cudaMemcpyDeviceToDevice, st));
-    return 0;
-  } else if (!strcmp(name, "dist_sq_sorted")) {        // ascending |x|^2 of the slow (owned) particles, raw
-    if (count < 0 || count > s.n) SPH_FAIL("session_download: dist_sq_sorted holds at most %lld values", (long long)s.n);
-    CUDA_TRY(cudaMemcpyAsync(dst, ctx->sbuf[SB_DISTSQ_ALT].p, (size_t)count * sizeof(double), cudaMemcpyDeviceToDevice, st));
     return 0;
   } else if (!strcmp(name, "num_nontrivial")) {
     if (count != s.n) SPH_FAIL("session_download: num_nontrivial needs %lld values", (long long)s.n);
@@ -811,7 +935,6 @@ int sphb200_session_append_rows(sphb200_ctx* ctx, const double* rows, int64_t n_
   for (int o = 0; o < O_NOUT; ++o) SPH_TRY(devbuf_reserve(ctx->sbuf[SB_OUT + o], (size_t)n1 * kOutWidth[o] * sizeof(double)));
   SPH_TRY(devbuf_reserve(ctx->sbuf[SB_NONTRIV], n1 * sizeof(int32_t)));
   SPH_TRY(devbuf_reserve(ctx->sbuf[SB_DISTSQ], n1 * sizeof(double)));
-  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_DISTSQ_ALT], n1 * sizeof(double)));
   RowArgs a;
   for (int f = 0; f < F_NFIELDS; ++f) a.f[f] = fld(ctx, f) + (size_t)n0 * kFieldWidth[f];
   a.knnh = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]) + n0;
@@ -901,6 +1024,21 @@ int sphb200_session_set_drag(sphb200_ctx* ctx, const void* f_un, int n_species, 
   return 0;
 }
 
+// Device pointer of an internal array a caller-side collective works on in place:
+// "length_hist" = the radix-select histogram (int64, 2*8192 + 1 values) between the phases "length_hist"
+// and "length_pick" (a slab decomposition all_reduces it there).
+int sphb200_session_buffer(sphb200_ctx* ctx, const char* name, void** ptr, int64_t* count) {
+  if (!ctx || !name || !ptr || !count) SPH_FAIL("session_buffer: null argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!strcmp(name, "length_hist")) {
+    SPH_TRY(devbuf_reserve(ctx->sbuf[SB_SEL], (SEL_HIST + 8) * sizeof(long long) + sizeof(SelectState)));
+    *ptr = sel_hist(ctx);
+    *count = SEL_HIST;
+    return 0;
+  }
+  SPH_FAIL("session_buffer: unknown buffer '%s'", name);
+}
+
 int sphb200_session_step(sphb200_ctx* ctx, void* stream) {
   if (!ctx) SPH_FAIL("null context");
   CUDA_TRY(cudaSetDevice(ctx->device));
@@ -934,6 +1072,9 @@ int sphb200_session_phase(sphb200_ctx* ctx, const char* phase, void* stream) {
   if (!strcmp(phase, "integrate")) return phase_integrate(ctx, st);
   if (!strcmp(phase, "kick")) return phase_kick(ctx, st);
   if (!strcmp(phase, "length")) return phase_length(ctx, st);
+  if (!strcmp(phase, "length_begin")) return phase_length_begin(ctx, st);
+  if (!strcmp(phase, "length_hist")) return phase_length_hist(ctx, st);
+  if (!strcmp(phase, "length_pick")) return phase_length_pick(ctx, st);
   if (!strcmp(phase, "smooth")) return phase_smooth(ctx, st);
   if (!strcmp(phase, "rho0")) {               // densities_0 <- densities (end of start-up, code_running.py:183)
     Session& s = sess(ctx);

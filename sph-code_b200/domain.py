@@ -273,7 +273,7 @@ class DistributedSession(object):
         self.w = None
         self.halo_redo = 0
         self.hmax = 0.0
-        self._pct_overflow = None
+        self._hist = None
         nt = torch.tensor([float(self.n_own)], dtype=torch.float64, device=self.device)
         dist.all_reduce(nt, op=dist.ReduceOp.SUM, group=group)
         self.n_total = int(nt.item())
@@ -346,6 +346,11 @@ class DistributedSession(object):
         self._ghost_idx = torch.arange(self.n_own, self.n_own + self._n_ghost, dtype=torch.int64, device=self.device)
         self.sess = s
         self.w = w
+
+    def _length_hist(self):
+        if self._hist is None:
+            self._hist = self.sess.buffer_tensor("length_hist")
+        return self._hist
 
     def _owned_rows(self):
         """Current owned rows (state columns + trial radius + gid) out of the session."""
@@ -421,12 +426,12 @@ class DistributedSession(object):
             s.phase("force")
         elif name == "integrate":
             s.phase("kick")
-            s.phase("length")                                      # local sort: owned slow particles' |x|^2, then +inf
-            r = percentile_on_device(s.download_raw("dist_sq_sorted", s.n), 90.0, self.group, cap=self._cap_hint)
-            v, ns = lerp_percentile(r[0], r[1], r[2], r[3], 90.0), r[2]        # code_running.py:515-518
-            d = torch.pow(torch.pow(v, 1.5) / ns / 0.9 * self.C.N_INT_PER_PARTICLE, 1. / 3.)   # :520-521
-            s.upload_raw("scalar:d", d.reshape(1).contiguous())    # stays on the device: no host sync in this phase
-            self._pct_overflow = torch.maximum(self._pct_overflow, r[4]) if self._pct_overflow is not None else r[4]
+            s.phase("length_begin")                                # exact global percentile: radix select whose
+            hist = self._length_hist()                             # histograms are summed over the ranks
+            for _ in range(5):                                     # (code_running.py:515-521; d stays on the device)
+                s.phase("length_hist")
+                dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=self.group)
+                s.phase("length_pick")
             s.phase("smooth")
         else:
             raise ValueError("unknown phase %r" % name)
@@ -444,8 +449,6 @@ class DistributedSession(object):
 
     def check(self):
         self.sess.check()
-        if self._pct_overflow is not None and float(self._pct_overflow.item()) != 0.0:
-            raise RuntimeError("distributed percentile: a rank's window overflowed (too many equal |x|^2 values)")
 
     def launches(self):
         return self.sess.launches()               # the context's counter is cumulative across sessions

@@ -100,6 +100,16 @@ class Session(object):
         _lib.check(self.lib.sphb200_session_upload(self.ctx.handle, name.encode(), ctypes.c_void_p(t.data_ptr()),
                                                    int(t.numel()), self._stream()))
 
+    def buffer_tensor(self, name):
+        """Zero-copy int64 tensor over an internal device array ("length_hist")."""
+        ptr = ctypes.c_void_p(0); cnt = ctypes.c_int64(0)
+        _lib.check(self.lib.sphb200_session_buffer(self.ctx.handle, name.encode(), ctypes.byref(ptr), ctypes.byref(cnt)))
+
+        class _Raw(object):
+            __cuda_array_interface__ = {"shape": (int(cnt.value),), "typestr": "<i8", "data": (int(ptr.value), False),
+                                        "version": 2, "strides": None}
+        return torch.as_tensor(_Raw(), device=self.device)
+
     def gather(self, name, idx):
         """Field `name` at caller indices idx (int64 CUDA tensor) -> (len(idx), width) float64 tensor."""
         w = STATE_FIELDS.get(name) or RESULT_FIELDS.get(name) or AUX_FIELDS[name]

@@ -38,6 +38,9 @@ def main():
             torch.cuda.synchronize()
         if rank == 0:
             print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=70))
+            ka = prof.key_averages()
+            busy = sum(getattr(e, "self_device_time_total", 0) for e in ka)
+            print("GPU busy (sum of kernel + memcpy time) per step: %.3f ms" % (busy / 5 / 1e3))
     dist.destroy_process_group()
 
 
