@@ -93,6 +93,10 @@ struct sphb200_ctx {
   int knn_fast = 1;                // 1: cell-tiled fast path (knn_cell.cu), 0: general kernel only
   double knn_margin = 0.02;        // trial radius = previous k-th distance * (1 + margin)
   GridSpec grid;
+  // slab decomposition: rows whose caller index (skip_id[i]) is >= skip_from are ghosts; their owners
+  // compute their sums, so the k-NN and the list-driven passes skip them as targets (nullptr: none)
+  const uint32_t* skip_id = nullptr;
+  int skip_from = 0;
   int64_t launches = 0;            // kernels launched through this context (for bench "gpu_launches")
 };
 

@@ -83,10 +83,11 @@ template <int G>
 __global__ void __launch_bounds__(HY_THREADS)
 density_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __restrict__ r0,
                const double4* __restrict__ r1, double* __restrict__ rho, double* __restrict__ dust,
-               double* __restrict__ num) {
+               double* __restrict__ num, const uint32_t* __restrict__ skip_id, int skip_from) {
   cg::thread_block_tile<G> tile = cg::tiled_partition<G>(cg::this_thread_block());
   const int i = blockIdx.x * (HY_THREADS / G) + tile.meta_group_rank();
   if (i >= n) return;
+  if (skip_id && (int)skip_id[i] >= skip_from) return;     // ghost: its owner computes it
   const int lane = tile.thread_rank();
   const int32_t* row = list + (int64_t)i * k;
   const int js = row[0];
@@ -116,7 +117,7 @@ density_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __
 int launch_density(sphb200_ctx* ctx, int n, int k, const int32_t* list, double* rho, double* dust, double* num,
                    cudaStream_t st) {
   density_kernel<HY_G><<<ceil_div(n, HY_THREADS / HY_G), HY_THREADS, 0, st>>>(
-      n, k, list, bufp<double4>(ctx->r0), bufp<double4>(ctx->r1), rho, dust, num);
+      n, k, list, bufp<double4>(ctx->r0), bufp<double4>(ctx->r1), rho, dust, num, ctx->skip_id, ctx->skip_from);
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;
@@ -129,10 +130,11 @@ template <int G>
 __global__ void __launch_bounds__(HY_THREADS)
 pi_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __restrict__ r0, const double4* __restrict__ r1,
           const double4* __restrict__ r2, const double* __restrict__ rho, const double* __restrict__ coefA,
-          double* __restrict__ Pi, rec2* __restrict__ r3) {
+          double* __restrict__ Pi, rec2* __restrict__ r3, const uint32_t* __restrict__ skip_id, int skip_from) {
   cg::thread_block_tile<G> tile = cg::tiled_partition<G>(cg::this_thread_block());
   const int i = blockIdx.x * (HY_THREADS / G) + tile.meta_group_rank();
   if (i >= n) return;
+  if (skip_id && (int)skip_id[i] >= skip_from) return;     // ghost: Pi and r3 arrive from its owner
   const int lane = tile.thread_rank();
   const int32_t* row = list + (int64_t)i * k;
   const int js = row[0];
@@ -167,17 +169,22 @@ pi_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __restr
   }
 }
 
-// r3[i].b = 6 c6_i m_i Pi_i [gas_i] from the current Pi array (after ghosts' Pi were overwritten)
+// r3[i] = {6 c6_i A_i, 6 c6_i m_i Pi_i [gas_i]} from the current Pi array (after the ghosts' Pi were
+// overwritten with their owners' values; the pi pass itself skips ghost rows)
 __global__ void __launch_bounds__(256)
-repack_pi_kernel(int n, const double4* __restrict__ r1, const double* __restrict__ Pi, rec2* __restrict__ r3) {
+repack_pi_kernel(int n, const double4* __restrict__ r1, const double* __restrict__ coefA, const double* __restrict__ Pi,
+                 rec2* __restrict__ r3) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const double4 w = r1[i];
-  r3[i].b = (6.0 * w.x) * (w.y * Pi[i]);
+  const double K = 6.0 * w.x;
+  rec2 o; o.a = K * coefA[i]; o.b = K * (w.y * Pi[i]);
+  r3[i] = o;
 }
 
 int launch_repack_pi(sphb200_ctx* ctx, int n, cudaStream_t st) {
-  repack_pi_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, bufp<double4>(ctx->r1), bufp<double>(ctx->pi_), bufp<rec2>(ctx->r3));
+  repack_pi_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, bufp<double4>(ctx->r1), bufp<double>(ctx->aux), bufp<double>(ctx->pi_),
+                                                     bufp<rec2>(ctx->r3));
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;
@@ -187,7 +194,7 @@ int launch_pi(sphb200_ctx* ctx, int n, int k, const int32_t* list, const double*
   SPH_TRY(devbuf_reserve(ctx->pi_, (size_t)(n + 1) * sizeof(double)));
   pi_kernel<HY_G><<<ceil_div(n, HY_THREADS / HY_G), HY_THREADS, 0, st>>>(
       n, k, list, bufp<double4>(ctx->r0), bufp<double4>(ctx->r1), bufp<double4>(ctx->r2), rho, bufp<double>(ctx->aux),
-      bufp<double>(ctx->pi_), bufp<rec2>(ctx->r3));
+      bufp<double>(ctx->pi_), bufp<rec2>(ctx->r3), ctx->skip_id, ctx->skip_from);
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;
@@ -204,10 +211,17 @@ __global__ void __launch_bounds__(HY_THREADS)
 force_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __restrict__ r0,
              const double4* __restrict__ r2, const rec2* __restrict__ r3, const double* __restrict__ rho,
              const double* __restrict__ mass, double* __restrict__ hydro_accel, double* __restrict__ visc_accel,
-             double* __restrict__ visc_heat) {
+             double* __restrict__ visc_heat, const uint32_t* __restrict__ skip_id, int skip_from) {
   cg::thread_block_tile<G> tile = cg::tiled_partition<G>(cg::this_thread_block());
   const int i = blockIdx.x * (HY_THREADS / G) + tile.meta_group_rank();
   if (i >= n) return;
+  if (skip_id && (int)skip_id[i] >= skip_from) {            // ghost: not advanced here; keep its outputs defined
+    if (tile.thread_rank() == 0) {
+      for (int c = 0; c < 3; ++c) { hydro_accel[3 * (int64_t)i + c] = 0.0; visc_accel[3 * (int64_t)i + c] = 0.0; }
+      visc_heat[i] = 0.0;
+    }
+    return;
+  }
   const int lane = tile.thread_rank();
   const int32_t* row = list + (int64_t)i * k;
   const int js = row[0];
@@ -252,7 +266,7 @@ int launch_force(sphb200_ctx* ctx, int n, int k, const int32_t* list, const doub
                  double* hydro_accel, double* visc_accel, double* visc_heat, cudaStream_t st) {
   force_kernel<HY_G><<<ceil_div(n, HY_THREADS / HY_G), HY_THREADS, 0, st>>>(
       n, k, list, bufp<double4>(ctx->r0), bufp<double4>(ctx->r2), bufp<rec2>(ctx->r3), rho, mass, hydro_accel, visc_accel,
-      visc_heat);
+      visc_heat, ctx->skip_id, ctx->skip_from);
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;

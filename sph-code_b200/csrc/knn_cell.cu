@@ -74,6 +74,8 @@ struct KnnCellArgs {
   int* flags;
   int* worklist;             // unresolved targets
   int* nwork;
+  const uint32_t* skip_id;   // slab decomposition: targets with skip_id[i] >= skip_from are ghosts (their owner
+  int skip_from;             // searches for them); nullptr = every particle is a target
 };
 
 // Shared-memory tile of one chunk of the cell block's candidates: one base address, fixed offsets
@@ -281,6 +283,13 @@ __device__ __forceinline__ KnnTarget knn_target_init(const KnnCellArgs& a, const
       atomicAdd(&a.flags[FL_KNN_NONFINITE], 1);
     }
   }
+  if (t.active && a.skip_id && (int)a.skip_id[i] >= a.skip_from) {            // ghost: an empty, well-defined row
+    t.active = false;
+    if (own) {
+      for (int s = 0; s < a.k; ++s) { a.list[(int64_t)i * a.k + s] = a.n; if (a.dists) a.dists[(int64_t)i * a.k + s] = 0.0; }
+      a.nontriv[i] = 0; a.h_out[i] = a.h_guess ? a.h_guess[i] : 0.0;
+    }
+  }
   if (t.active) {
     if (!b.whole) {
       // distance to the nearest face of the cell block that is not a face of the whole grid
@@ -472,6 +481,7 @@ int launch_knn_cell(sphb200_ctx* ctx, int n, int k, double dist, const double* h
   a.flags = bufp<int>(ctx->flags);
   a.worklist = bufp<int>(ctx->worklist);
   a.nwork = nwork;
+  a.skip_id = ctx->skip_id; a.skip_from = ctx->skip_from;
   if (dists) knn_cell_kernel<true><<<ctx->grid.ncells, KC_WARPS * 32, 0, st>>>(a);
   else knn_cell_kernel<false><<<ctx->grid.ncells, KC_WARPS * 32, 0, st>>>(a);
   ctx->launches += 1;

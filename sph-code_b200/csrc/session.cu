@@ -507,6 +507,7 @@ static int phase_sort(sphb200_ctx* ctx, cudaStream_t st, unsigned mask = ~0u) {
   s.knnh_cur ^= 1;
   s.has_list = 0;
   s.pos_valid = 0;
+  if (ctx->skip_id) ctx->skip_id = bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]);     // the ghost mask follows the new order
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -644,6 +645,19 @@ static double* aux_field(sphb200_ctx* ctx, const char* name, bool for_upload) {
   if (!for_upload && !strcmp(name, "dist_sq")) return bufp<double>(ctx->sbuf[SB_DISTSQ]);
   return nullptr;
 }
+
+// While a session call runs, the launchers skip the ghosts of a slab decomposition as targets; the
+// function-level API (api.cu) never sees the pointer.  Evaluated per launch: the sort flips id_cur.
+struct SkipGhosts {
+  sphb200_ctx* ctx;
+  explicit SkipGhosts(sphb200_ctx* c) : ctx(c) { refresh(); }
+  void refresh() {
+    Session& s = sess(ctx);
+    ctx->skip_id = (s.n_owned >= 0 && s.n_owned < s.n) ? bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]) : nullptr;
+    ctx->skip_from = (int)s.n_owned;
+  }
+  ~SkipGhosts() { ctx->skip_id = nullptr; }
+};
 
 extern "C" {
 
@@ -1043,6 +1057,7 @@ int sphb200_session_step(sphb200_ctx* ctx, void* stream) {
   if (!ctx) SPH_FAIL("null context");
   CUDA_TRY(cudaSetDevice(ctx->device));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  SkipGhosts skip(ctx);
   SPH_TRY(phase_crossing(ctx, st));
   SPH_TRY(phase_dt_clamp(ctx, st));
   SPH_TRY(phase_sort(ctx, st));
@@ -1060,6 +1075,7 @@ int sphb200_session_phase(sphb200_ctx* ctx, const char* phase, void* stream) {
   if (!ctx || !phase) SPH_FAIL("null argument");
   CUDA_TRY(cudaSetDevice(ctx->device));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  SkipGhosts skip(ctx);
   if (!strcmp(phase, "crossing")) return phase_crossing(ctx, st);
   if (!strcmp(phase, "dt_clamp")) return phase_dt_clamp(ctx, st);
   if (!strcmp(phase, "sort")) return phase_sort(ctx, st);

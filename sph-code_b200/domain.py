@@ -58,6 +58,7 @@ class SlabExchange(object):
         self.bounds = [float(b) for b in bounds]                  # world + 1 ascending; ends may be +-inf
         assert len(self.bounds) == self.world + 1
         self.lo, self.hi = self.bounds[self.rank], self.bounds[self.rank + 1]
+        self._inner = None
         self.send_idx = None          # per destination rank: indices of owned rows sent as ghosts
         self.recv_counts = None
         self.w = None
@@ -83,8 +84,9 @@ class SlabExchange(object):
         return recv, recv_counts
 
     def owner_of(self, x):
-        inner = torch.tensor(self.bounds[1:-1], dtype=x.dtype, device=x.device)
-        return torch.bucketize(x, inner, right=True)              # x == bound belongs to the upper slab
+        if self._inner is None or self._inner.device != x.device or self._inner.dtype != x.dtype:
+            self._inner = torch.tensor(self.bounds[1:-1], dtype=x.dtype, device=x.device)   # once: a host->device copy
+        return torch.bucketize(x, self._inner, right=True)        # x == bound belongs to the upper slab
 
     # -- the three exchanges --------------------------------------------------------------------
     def migrate(self, rows):
