@@ -30,6 +30,15 @@
 #define KC_CHP 640         // padded candidates staged per chunk (multiple of 32)
 #define KC_WARPS 4
 #define KC_MAX_ATTEMPT 24
+#ifndef KC_UNROLL
+#define KC_UNROLL 4
+#endif
+#define KC_PRAGMA_(x) _Pragma(#x)
+#define KC_PRAGMA(x) KC_PRAGMA_(x)
+#define KC_UNROLL_SCAN KC_PRAGMA(unroll KC_UNROLL)
+#ifndef KC_MIN_CTAS
+#define KC_MIN_CTAS 8          // resident CTAs per SM the register budget is set for (64 registers, 26.7 KB)
+#endif
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -159,7 +168,7 @@ __device__ __forceinline__ int knn_scan_chunk(const KnnTile& t, int c_n, double 
                                               int count, double* keybuf, int32_t* idxbuf, int lane) {
   const unsigned lt = (1u << lane) - 1u;
   const double* T = t.T + lane;
-#pragma unroll 2
+  KC_UNROLL_SCAN
   for (int c0 = 0; c0 < c_n; c0 += 32) {
     const double dx = T[c0] - px, dy = T[c0 + KC_CHP] - py, dz = T[c0 + 2 * KC_CHP] - pz;
     const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
@@ -233,13 +242,24 @@ __device__ __forceinline__ double knn_emit(const KnnCellArgs& a, int i, int coun
     for (int s = nsel + lane; s < k; s += 32) { a.list[row + s] = a.n; a.dists[row + s] = 0.0; }
     warp_max_pair(km, im);
   } else {
-    // session layout: drop the (count - k) largest, keep the rest unordered with self in column 0
+    // session layout: drop the (count - k) largest, keep the rest unordered with self in column 0.
+    // The float keys (rounded up, so monotone in the exact key) are formed once; while the float maximum
+    // is unique its owner just clears its entry: one REDUX, two ballots and no shuffle per removal.
     double k0 = (lane < count) ? keybuf[lane] : -1.0, k1 = (lane + 32 < count) ? keybuf[lane + 32] : -1.0;
     int i0 = (lane < count) ? idxbuf[lane] : -1, i1 = (lane + 32 < count) ? idxbuf[lane + 32] : -1;
+    unsigned f0 = (k0 >= 0.0) ? __float_as_uint(__double2float_ru(k0)) + 1u : 0u;
+    unsigned f1 = (k1 >= 0.0) ? __float_as_uint(__double2float_ru(k1)) + 1u : 0u;
     for (int r = count; r > nsel; --r) {
-      knn_max_entry(k0, i0, k1, i1, km, im);
-      if (i0 == im && k0 == km) { k0 = -1.0; i0 = -1; }
-      else if (i1 == im && k1 == km) { k1 = -1.0; i1 = -1; }
+      const unsigned m = __reduce_max_sync(0xffffffffu, max(f0, f1));
+      const unsigned b0 = __ballot_sync(0xffffffffu, f0 == m), b1 = __ballot_sync(0xffffffffu, f1 == m);
+      if (__popc(b0) + __popc(b1) == 1) {
+        if (f0 == m) { f0 = 0u; k0 = -1.0; i0 = -1; }
+        if (f1 == m) { f1 = 0u; k1 = -1.0; i1 = -1; }
+      } else {                                               // equal float keys: exact (key, index) maximum
+        knn_max_entry(k0, i0, k1, i1, km, im);
+        if (i0 == im && k0 == km) { f0 = 0u; k0 = -1.0; i0 = -1; }
+        else if (i1 == im && k1 == km) { f1 = 0u; k1 = -1.0; i1 = -1; }
+      }
     }
     knn_max_entry(k0, i0, k1, i1, km, im);
     const unsigned lt = (1u << lane) - 1u;
@@ -337,7 +357,7 @@ __device__ __forceinline__ int knn_radius_update(const KnnCellArgs& a, bool whol
 #define KC_SMEM (KC_OFF_BAR + 16)
 
 template <bool SORTED>
-__global__ void __launch_bounds__(KC_WARPS * 32, 6) knn_cell_kernel(KnnCellArgs a) {
+__global__ void __launch_bounds__(KC_WARPS * 32, KC_MIN_CTAS) knn_cell_kernel(KnnCellArgs a) {
   __shared__ __align__(128) unsigned char smem[KC_SMEM];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cell = blockIdx.x;
