@@ -110,9 +110,20 @@ static void choose_grid(const double* bb, int64_t n, double occ, double edge_hin
   }
   double Lmax = fmax(L[0], fmax(L[1], L[2]));
   if (!(Lmax > 0.0)) Lmax = 1.0;
-  for (int a = 0; a < 3; ++a) if (L[a] < 1e-6 * Lmax) L[a] = 1e-6 * Lmax;   // degenerate (planar) inputs
+  // Degenerate inputs (particles on a plane or a line): a collapsed direction gets one layer of cells and
+  // the occupancy is set over the directions that do extend, otherwise the cells come out far too small.
+  double measure = 1.0;
+  int dims = 0;
+  for (int a = 0; a < 3; ++a) {
+    if (L[a] < 1e-6 * Lmax) L[a] = 0.0;
+    else { measure *= L[a]; ++dims; }
+  }
   double c = edge_hint;
-  if (!(c > 0.0)) c = cbrt(L[0] * L[1] * L[2] * occ / (double)(n > 0 ? n : 1));
+  if (!(c > 0.0)) {
+    const double per_cell = measure * occ / (double)(n > 0 ? n : 1);
+    c = (dims == 3) ? cbrt(per_cell) : (dims == 2) ? sqrt(per_cell) : (dims == 1) ? per_cell : 1.0;
+  }
+  if (!(c > 0.0)) c = Lmax;
   const double max_cells = fmin(4.0 * (double)n + 4096.0, 1.0e9);
   for (;;) {
     double nx = floor(L[0] / c) + 1, ny = floor(L[1] / c) + 1, nz = floor(L[2] / c) + 1;

@@ -126,8 +126,55 @@ knn_kernel(const double4* __restrict__ r0, const uint32_t* __restrict__ keys, co
     ++m; widened = 1;                       // block too small: widen, re-estimate
     R2try = -1.0;
   }
+  if (!done) {
+    // The radius search did not settle: more candidates share one distance than the buffer holds
+    // (coincident or lattice points), so no radius separates k of them.  Select by successive minima of
+    // (d^2, index) over the block instead: exact for ties, O(k x candidates) and only ever used here.
+    const int x0 = max(cx - m, 0), x1 = min(cx + m, g.nx - 1);
+    const int y0 = max(cy - m, 0), y1 = min(cy + m, g.ny - 1);
+    const int z0 = max(cz - m, 0), z1 = min(cz + m, g.nz - 1);
+    const bool whole = (x0 == 0 && y0 == 0 && z0 == 0 && x1 == g.nx - 1 && y1 == g.ny - 1 && z1 == g.nz - 1);
+    const double rsafe = (double)m * g.c * (1.0 - 1e-8);
+    const double R2lim = whole ? dist2 : fmin(dist2, rsafe * rsafe);
+    const int ysp = y1 - y0 + 1;
+    const int nrows = ysp * (z1 - z0 + 1);
+    const int64_t row = (int64_t)i * k;
+    unsigned long long last_k = 0ull; int last_j = -1;
+    int nsel = 0;
+    for (; nsel < k; ++nsel) {
+      unsigned long long best_k = ~0ull; int best_j = 0x7fffffff;
+      for (int r = 0; r < nrows; ++r) {
+        const int base = ((z0 + r / ysp) * g.ny + (y0 + r % ysp)) * g.nx;
+        const int s = (int)cell_start[base + x0], e = (int)cell_start[base + x1 + 1];
+        for (int j = s + lane; j < e; j += G) {
+          const double4 q = r0[j];
+          const double dx = q.x - p.x, dy = q.y - p.y, dz = q.z - p.z;
+          const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+          if (!(d2 < R2lim)) continue;
+          const unsigned long long kk = (unsigned long long)__double_as_longlong(d2);
+          const bool after = (last_j < 0) || kk > last_k || (kk == last_k && j > last_j);
+          if (after && (kk < best_k || (kk == best_k && j < best_j))) { best_k = kk; best_j = j; }
+        }
+      }
+      const unsigned long long mk = cg::reduce(tile, best_k, cg::less<unsigned long long>());
+      const int mj = cg::reduce(tile, (best_k == mk) ? best_j : 0x7fffffff, cg::less<int>());
+      if (mj == 0x7fffffff) break;                          // nothing left inside the covered radius
+      last_k = mk; last_j = mj;
+      if (lane == 0) { list[row + nsel] = mj; if (dists) dists[row + nsel] = sqrt(__longlong_as_double((long long)mk)); }
+    }
+    const bool exact = (nsel == k) || whole || R2lim >= dist2;   // else the block did not reach the k-th neighbour
+    for (int s = nsel + lane; s < k; s += G) { list[row + s] = n; if (dists) dists[row + s] = 0.0; }
+    if (lane == 0) {
+      nontriv[i] = nsel;
+      h_out[i] = nsel > 0 ? sqrt(__longlong_as_double((long long)last_k)) : 0.0;
+      if (!exact) atomicAdd(&flags[FL_KNN_OVERFLOW], 1);
+      if (rescans > 0) atomicAdd(&flags[FL_KNN_RESCAN], rescans);
+      atomicAdd(&flags[FL_KNN_WIDEN], 1);
+    }
+    tile.sync();
+    continue;
+  }
   if (lane == 0) {
-    if (!done) atomicAdd(&flags[FL_KNN_OVERFLOW], 1);
     if (rescans > 0) atomicAdd(&flags[FL_KNN_RESCAN], rescans);
     if (widened) atomicAdd(&flags[FL_KNN_WIDEN], 1);
   }

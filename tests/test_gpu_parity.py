@@ -175,3 +175,42 @@ def test_loop_generation_ragged(nsc):
         w = O._weigh2(np.sum(x ** 2, axis=1), st["mass"][row], d) * (st["particle_type"][row] == 0)
         want[i] = np.sum(w[w > 0])
     assert rel(got, want) < RTOL
+
+
+@pytest.mark.parametrize("k", [1, 2, 50, 56, 57, 100])
+def test_neighbors_other_k(nsc, k):
+    """BASELINE config 2 mentions '~50 neighbours': k = 50 is the labelled variant; 56 is the widest row
+    the cell-tiled kernel takes, 57 and 100 go to the general kernel; 1 and 2 are the degenerate ends."""
+    st = _state(30000, 21)
+    gi, _, gd, gn, gs = nsc.neighbors(st["points"], st["dist"] * 1.5, k)
+    if k == 1:      # cKDTree squeezes the k axis away and nsc:546 raises AxisError; the brute force keeps (N,1)
+        oi, _, od, on, os_ = O.neighbors_bruteforce(st["points"], st["dist"] * 1.5, k)
+    else:
+        oi, _, od, on, os_ = O.neighbors(st["points"], st["dist"] * 1.5, k)
+    assert gi.shape == (30000, k)
+    assert np.array_equal(gi, oi) and np.array_equal(gd, od)
+    assert np.array_equal(gn, on) and np.array_equal(gs, os_)
+
+
+def test_neighbors_degenerate_inputs(nsc):
+    """one particle; particles on a line (a grid that is one cell thick in two directions); all particles
+    on one point."""
+    p1 = np.array([[1.0, 2.0, 3.0]])
+    gi, _, gd, gn, gs = nsc.neighbors(p1, 10.0, 4)
+    assert gi.tolist() == [[0, 1, 1, 1]] and gd.tolist() == [[0.0, 0.0, 0.0, 0.0]] and gn.tolist() == [1] and gs.tolist() == [0.0]
+    rs = np.random.RandomState(3)
+    line = np.zeros((5000, 3)); line[:, 0] = rs.rand(5000) * 1e17
+    gi, _, gd, gn, gs = nsc.neighbors(line, np.inf, 40)
+    oi, _, od, on, os_ = O.neighbors(line, np.inf, 40)
+    assert np.array_equal(gi, oi) and np.array_equal(gd, od) and np.array_equal(gs, os_)
+    same = np.ones((300, 3)) * 7.0                 # every distance ties: any 40 distinct indices are a right answer
+    gi, _, gd, gn, gs = nsc.neighbors(same, 1.0, 40)
+    assert np.all(gd == 0.0) and np.all(gn == 40) and np.all(gs == 0.0)
+    assert gi.min() >= 0 and gi.max() < 300 and all(len(set(r)) == 40 for r in gi.tolist())
+
+
+def test_empty_input_is_an_error(nsc):
+    """cKDTree.query on zero points returns empty arrays; the C ABI refuses N = 0 instead (documented)."""
+    from sphb200._lib import Sphb200Error
+    with pytest.raises((Sphb200Error, ValueError, IndexError)):
+        nsc.neighbors(np.zeros((0, 3)), 1.0, 4)
