@@ -195,7 +195,8 @@ def workload_name(args):
 # ------------------------------------------------------------------------------------------------
 UPLOAD_FIELDS = ("points", "velocities", "total_accel", "mass", "sizes", "T", "E_internal", "mu_array",
                  "gamma_array", "particle_type", "densities_0")
-DOWNLOAD_FIELDS = ("points", "velocities", "total_accel", "sizes", "T", "E_internal", "densities_0", "densities")
+# what a step changes (densities_0 is the step's density, code_running.py:540): 104 B/particle back to the host
+DOWNLOAD_FIELDS = ("points", "velocities", "total_accel", "sizes", "T", "E_internal", "densities_0")
 
 
 def run_ours(args):

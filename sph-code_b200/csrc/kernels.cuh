@@ -9,8 +9,9 @@ int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint
 int knn_cap_for(int k);
 int launch_knn(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, int32_t* list, double* dists,
                double* h_out, int32_t* nontriv, cudaStream_t st);
-int launch_knn_worklist(sphb200_ctx* ctx, int n, int k, double dist, const int* worklist, const int* nwork, int32_t* list,
-                        double* dists, double* h_out, int32_t* nontriv, cudaStream_t st);
+int launch_knn_worklist(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, double guess_factor,
+                        const int* worklist, const int* nwork, int32_t* list, double* dists, double* h_out, int32_t* nontriv,
+                        cudaStream_t st);
 // knn_cell.cu (fast path: one warp per cell, one lane per target, candidates staged by bulk copies)
 int knn_cell_max_k();
 int launch_knn_cell(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, double margin, int32_t* list,

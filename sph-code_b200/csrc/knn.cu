@@ -29,7 +29,7 @@ namespace cg = cooperative_groups;
 template <int G>
 __global__ void __launch_bounds__(KNN_THREADS)
 knn_kernel(const double4* __restrict__ r0, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ cell_start,
-           GridSpec g, int n, int k, double dist2, int cap, const double* __restrict__ h_guess,
+           GridSpec g, int n, int k, double dist2, int cap, const double* __restrict__ h_guess, double guess_factor,
            int32_t* __restrict__ list, double* __restrict__ dists, double* __restrict__ h_out,
            int32_t* __restrict__ nontriv, int* __restrict__ flags, const int* __restrict__ worklist,
            const int* __restrict__ nwork) {
@@ -58,7 +58,7 @@ knn_kernel(const double4* __restrict__ r0, const uint32_t* __restrict__ keys, co
   }
   int m = 1;
   double R2try = -1.0;
-  if (h_guess) { double hg = h_guess[i]; if (hg > 0.0) { R2try = hg * hg; m = (int)(hg * g.inv_c) + 1; } }
+  if (h_guess) { double hg = h_guess[i] * guess_factor; if (hg > 0.0) { R2try = hg * hg; m = (int)(hg * g.inv_c) + 1; } }
   int count = 0;
   bool done = false;
   int iter = 0, rescans = -1, widened = 0;
@@ -87,26 +87,44 @@ knn_kernel(const double4* __restrict__ r0, const uint32_t* __restrict__ keys, co
       R2try = R2lim;
     }
     // ---- scan the block ----
+    // The targets that reach this kernel are few (one warp each, nearly empty GPU), so the scan is bound by
+    // load latency: the row bounds of up to G rows are fetched by the lanes at once, and two candidate
+    // batches are in flight per trip.
     ++rescans;
     count = 0;
-    for (int r = 0; r < nrows; ++r) {
-      const int base = ((z0 + r / ysp) * g.ny + (y0 + r % ysp)) * g.nx;
-      const int s = (int)cell_start[base + x0], e = (int)cell_start[base + x1 + 1];
-      for (int jb = s; jb < e; jb += G) {
-        const int j = jb + lane;
-        bool ok = false;
-        double d2 = 0.0;
-        if (j < e) {
-          const double4 q = r0[j];
-          const double dx = q.x - p.x, dy = q.y - p.y, dz = q.z - p.z;
-          d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
-          ok = d2 < R2try;
-        }
-        const unsigned b = tile.ballot(ok);
-        if (b) {
-          const int pos = count + __popc(b & ((1u << lane) - 1u));
-          if (ok && pos < cap) { keybuf[pos] = (unsigned long long)__double_as_longlong(d2); idxbuf[pos] = j; }
-          count += __popc(b);
+    for (int rb = 0; rb < nrows; rb += G) {
+      int my_s = 0, my_e = 0;
+      if (rb + lane < nrows) {
+        const int r = rb + lane;
+        const int base = ((z0 + r / ysp) * g.ny + (y0 + r % ysp)) * g.nx;
+        my_s = (int)cell_start[base + x0]; my_e = (int)cell_start[base + x1 + 1];
+      }
+      const int rn = min(G, nrows - rb);
+      for (int r = 0; r < rn; ++r) {
+        const int s = tile.shfl(my_s, r), e = tile.shfl(my_e, r);
+        for (int jb = s; jb < e; jb += 2 * G) {
+          const int ja = jb + lane, jc = jb + G + lane;
+          double4 qa = make_double4(0, 0, 0, 0), qc = make_double4(0, 0, 0, 0);
+          if (ja < e) qa = r0[ja];
+          if (jc < e) qc = r0[jc];
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            const int j = half ? jc : ja;
+            const double4 q = half ? qc : qa;
+            bool ok = false;
+            double d2 = 0.0;
+            if (j < e) {
+              const double dx = q.x - p.x, dy = q.y - p.y, dz = q.z - p.z;
+              d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+              ok = d2 < R2try;
+            }
+            const unsigned b = tile.ballot(ok);
+            if (b) {
+              const int pos = count + __popc(b & ((1u << lane) - 1u));
+              if (ok && pos < cap) { keybuf[pos] = (unsigned long long)__double_as_longlong(d2); idxbuf[pos] = j; }
+              count += __popc(b);
+            }
+          }
         }
       }
     }
@@ -215,7 +233,7 @@ int knn_cap_for(int k) {
   return cap;
 }
 
-static int launch_knn_impl(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, int32_t* list, double* dists,
+static int launch_knn_impl(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, double guess_factor, int32_t* list, double* dists,
                            double* h_out, int32_t* nontriv, const int* worklist, const int* nwork, cudaStream_t st) {
   if (k < 1) SPH_FAIL("knn: k must be >= 1");
   const int cap = knn_cap_for(k);
@@ -234,7 +252,7 @@ static int launch_knn_impl(sphb200_ctx* ctx, int n, int k, double dist, const do
   do {                                                                                                         \
     if (smem > 48 * 1024)                                                                                      \
       CUDA_TRY(cudaFuncSetAttribute(knn_kernel<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));  \
-    knn_kernel<GG><<<blocks, KNN_THREADS, smem, st>>>(r0, keys, cs, ctx->grid, n, k, dist2, cap, h_guess, list, \
+    knn_kernel<GG><<<blocks, KNN_THREADS, smem, st>>>(r0, keys, cs, ctx->grid, n, k, dist2, cap, h_guess, guess_factor, list, \
                                                       dists, h_out, nontriv, flags, worklist, nwork);          \
   } while (0)
   if (G == 32) KNN_LAUNCH(32);
@@ -249,12 +267,15 @@ static int launch_knn_impl(sphb200_ctx* ctx, int n, int k, double dist, const do
 
 int launch_knn(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, int32_t* list, double* dists,
                double* h_out, int32_t* nontriv, cudaStream_t st) {
-  return launch_knn_impl(ctx, n, k, dist, h_guess, list, dists, h_out, nontriv, nullptr, nullptr, st);
+  return launch_knn_impl(ctx, n, k, dist, h_guess, 1.0, list, dists, h_out, nontriv, nullptr, nullptr, st);
 }
 
-int launch_knn_worklist(sphb200_ctx* ctx, int n, int k, double dist, const int* worklist, const int* nwork, int32_t* list,
-                        double* dists, double* h_out, int32_t* nontriv, cudaStream_t st) {
-  return launch_knn_impl(ctx, n, k, dist, nullptr, list, dists, h_out, nontriv, worklist, nwork, st);
+// h_guess (may be nullptr): previous k-th distances; the first trial radius is guess * guess_factor, which
+// sizes the block and normally settles the target in one scan
+int launch_knn_worklist(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, double guess_factor,
+                        const int* worklist, const int* nwork, int32_t* list, double* dists, double* h_out, int32_t* nontriv,
+                        cudaStream_t st) {
+  return launch_knn_impl(ctx, n, k, dist, h_guess, guess_factor, list, dists, h_out, nontriv, worklist, nwork, st);
 }
 
 // Sorted-space rows -> the reference's return layout (original particle order, int64 indices,

@@ -507,6 +507,6 @@ int launch_knn_cell(sphb200_ctx* ctx, int n, int k, double dist, const double* h
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   // unresolved targets: general warp-per-target kernel over the work list (grid-stride, count on device)
-  SPH_TRY(launch_knn_worklist(ctx, n, k, dist, bufp<int>(ctx->worklist), nwork, list, dists, h_out, nontriv, st));
+  SPH_TRY(launch_knn_worklist(ctx, n, k, dist, h_guess, 1.0 + margin, bufp<int>(ctx->worklist), nwork, list, dists, h_out, nontriv, st));
   return 0;
 }

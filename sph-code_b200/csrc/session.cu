@@ -225,44 +225,52 @@ select_hist_kernel(int n, const double* __restrict__ keys, const SelectState* __
   if (pass == 0 && blockIdx.x == 0 && threadIdx.x == 0) hist[2 * SEL_BINS] = (long long)*nslow_local;
 }
 
-// one block of 1024 threads; every thread owns 8 consecutive bins
-__device__ int sel_find(const long long* __restrict__ h, unsigned long long rank, unsigned long long* rank_out,
-                        unsigned long long* sh) {
-  const int t = threadIdx.x;
+// One block of 1024 threads, every thread owns 8 consecutive bins of `h`: finds the bins holding the ranks
+// r0 and r1 (both looked up in the same histogram) and the ranks inside those bins.  Block scan = warp
+// shuffles + one pass over the 32 warp totals.
+__device__ void sel_find2(const long long* __restrict__ h, unsigned long long r0, unsigned long long r1, int* dig,
+                          unsigned long long* rank_in, unsigned long long* warp_tot) {
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   unsigned long long loc[8], sum = 0;
 #pragma unroll
   for (int q = 0; q < 8; ++q) { loc[q] = (unsigned long long)h[t * 8 + q]; sum += loc[q]; }
-  sh[t] = sum;
-  __syncthreads();
-  for (int off = 1; off < 1024; off <<= 1) {              // inclusive scan of the per-thread sums
-    const unsigned long long v = (t >= off) ? sh[t - off] : 0ull;
-    __syncthreads();
-    sh[t] += v;
-    __syncthreads();
-  }
-  const unsigned long long before = sh[t] - sum;
-  __shared__ int found;
-  __shared__ unsigned long long found_rank;
-  if (t == 0) { found = SEL_BINS - 1; found_rank = 0; }
-  __syncthreads();
-  if (rank >= before && rank < before + sum) {
-    unsigned long long c = before;
+  unsigned long long inc = sum;
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
-      if (rank >= c && rank < c + loc[q]) { found = t * 8 + q; found_rank = rank - c; }
-      c += loc[q];
+  for (int d = 1; d < 32; d <<= 1) {
+    const unsigned long long v = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane >= d) inc += v;
+  }
+  if (lane == 31) warp_tot[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    unsigned long long w = warp_tot[lane];
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const unsigned long long v = __shfl_up_sync(0xffffffffu, w, d);
+      if (lane >= d) w += v;
+    }
+    warp_tot[lane] = w;                                     // inclusive totals of the warps
+  }
+  __syncthreads();
+  const unsigned long long before = (warp ? warp_tot[warp - 1] : 0ull) + inc - sum;
+#pragma unroll
+  for (int which = 0; which < 2; ++which) {
+    const unsigned long long rank = which ? r1 : r0;
+    if (rank >= before && rank < before + sum) {
+      unsigned long long c = before;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        if (rank >= c && rank < c + loc[q]) { dig[which] = t * 8 + q; rank_in[which] = rank - c; }
+        c += loc[q];
+      }
     }
   }
   __syncthreads();
-  *rank_out = found_rank;
-  const int r = found;
-  __syncthreads();
-  return r;
 }
 
 __global__ void __launch_bounds__(1024)
 select_pick_kernel(SelectState* st, long long* __restrict__ hist, double* __restrict__ scal, double n_int) {
-  __shared__ unsigned long long sh[1024];
+  __shared__ unsigned long long sh[32];
   const int pass = st->pass;
   if (pass >= SEL_PASSES) return;
   unsigned long long ns = st->ns, rA = st->rank[0], rB = st->rank[1];
@@ -280,9 +288,14 @@ select_pick_kernel(SelectState* st, long long* __restrict__ hist, double* __rest
     return;
   }
   const int split = st->split, w = sel_width(pass);
-  unsigned long long nrA, nrB;
-  const int dA = sel_find(hist, rA, &nrA, sh);
-  const int dB = sel_find(split ? hist + SEL_BINS : hist, rB, &nrB, sh);
+  __shared__ int dig[4];
+  __shared__ unsigned long long rin[4];
+  if (threadIdx.x < 4) { dig[threadIdx.x] = SEL_BINS - 1; rin[threadIdx.x] = 0; }
+  __syncthreads();
+  sel_find2(hist, rA, split ? rA : rB, dig, rin, sh);                 // one histogram serves both ranks until they split
+  if (split) sel_find2(hist + SEL_BINS, rB, rB, dig + 2, rin + 2, sh);
+  const int dA = dig[0], dB = split ? dig[2] : dig[1];
+  const unsigned long long nrA = rin[0], nrB = split ? rin[2] : rin[1];
   const unsigned long long pA = (st->prefix[0] << w) | (unsigned long long)dA;
   const unsigned long long pB = (st->prefix[1] << w) | (unsigned long long)dB;
   __syncthreads();

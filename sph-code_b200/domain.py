@@ -91,15 +91,29 @@ class SlabExchange(object):
     # -- the three exchanges --------------------------------------------------------------------
     def migrate(self, rows):
         """Send every row to the rank whose slab holds its x (column 0); returns the new owned rows.
-        Only the movers are sorted and split; the rows that stay are taken with one mask."""
+        One host sync (send and receive counts together); when nobody moves anywhere near this rank the
+        rows are returned as they are, otherwise only the movers are gathered and split."""
         dest = self.owner_of(rows[:, 0].contiguous())
+        counts = torch.bincount(dest, minlength=self.world)            # stays on the device
+        rc = torch.empty_like(counts)
+        dist.all_to_all_single(rc, counts, group=self.group)
+        both = torch.cat([counts, rc]).tolist()                        # the one sync
+        send_list, recv_list = both[:self.world], both[self.world:]
+        recv_list[self.rank] = 0
+        n_out = sum(send_list) - send_list[self.rank]
+        send_list[self.rank] = 0
+        if n_out == 0 and sum(recv_list) == 0:
+            return rows
         stay = dest == self.rank
-        mv = torch.nonzero(~stay, as_tuple=False).flatten()
-        mdest = dest[mv]
-        order = torch.argsort(mdest, stable=True)
-        counts = torch.bincount(mdest, minlength=self.world)           # stays on the device
-        recv, _ = self._all_to_all_rows(rows[mv[order]], send_counts=counts)
-        return torch.cat([rows[stay], recv], dim=0) if recv.shape[0] else rows[stay]
+        if n_out:
+            mv = torch.nonzero(~stay, as_tuple=False).flatten()
+            send = rows[mv[torch.argsort(dest[mv], stable=True)]].contiguous()
+        else:
+            send = rows[:0].contiguous()
+        recv = torch.empty((sum(recv_list), rows.shape[1]), dtype=rows.dtype, device=rows.device)
+        dist.all_to_all_single(recv, send, output_split_sizes=recv_list, input_split_sizes=send_list, group=self.group)
+        kept = rows[stay] if n_out else rows
+        return torch.cat([kept, recv], dim=0) if recv.shape[0] else kept
 
     def build_halo(self, rows, w):
         """Select, for every other rank, the owned rows within `w` of its slab; exchange them.
