@@ -69,37 +69,48 @@ def test_ten_steps_against_reference_outputs(built_lib):
                 assert rel(s.download(f)[::50], g["step%d_%s" % (it + 1, f)]) < RTOL, (it, f)
 
 
-def test_full_size_properties(built_lib):
-    """BASELINE config 2 size (N = 10^6): size-independent properties of the neighbour search and sums.
-    rows sorted by distance, self first, h = last distance, k-th distance consistent with a brute-force
-    check on a random sample of targets; density positive and equal to a host sum over the returned rows."""
-    import torch
+@pytest.mark.parametrize("config,n,kind,seed", [(2, 1000000, "uniform", 1), (3, 4000000, "clustered", 2),
+                                                (4, 10000000, "uniform", 3)])
+def test_full_size_properties(built_lib, config, n, kind, seed):
+    """BASELINE configs 2-4 at their full sizes (uniform 10^6, clustered 4x10^6, uniform 10^7): size-independent
+    properties of the neighbour search and the sums.  Rows sorted by distance with self first, h = the row's
+    largest distance, rows identical to a brute-force search for a random sample of targets (including the
+    distance cut), density positive and equal to a host sum over the returned rows."""
     from sphb200 import ics
     from sphb200 import navier_stokes_cleaned as nsc
-    n = 1000000
-    st = ics.uniform_box(n, 1)
-    idx, _, dd, nontriv, sizes = nsc.neighbors(st["points"], st["dist"], 40)
-    assert np.array_equal(idx[:, 0], np.arange(n))
-    assert np.all(np.diff(dd, axis=1) >= 0)
-    assert np.array_equal(sizes, dd[:, -1]) and np.all(nontriv == 40)
+    st = ics.uniform_box(n, seed) if kind == "uniform" else ics.clustered_cloud(n, seed)
+    p, dist = st["points"], st["dist"]
+    idx, _, dd, nontriv, sizes = nsc.neighbors(p, dist, 40)
+    assert idx.shape == (n, 40) and np.array_equal(idx[:, 0], np.arange(n))
+    full = nontriv == 40
+    assert full.mean() > 0.9 and nontriv.min() >= 1
+    cols = np.arange(40)[None, :]
+    valid = cols < nontriv[:, None]
+    assert np.all(idx[~valid] == n) and np.all(dd[~valid] == 0.0)           # missing neighbours: index N, distance 0
+    step = np.diff(dd, axis=1)
+    assert np.all(step[valid[:, 1:]] >= 0)                                   # ascending distance inside each row
+    del step
+    assert np.array_equal(sizes, dd.max(axis=1)) and np.all(dd[valid] < dist)
     rs = np.random.RandomState(0)
-    p = st["points"]
     for i in rs.randint(0, n, 40):
         dx = p - p[i]
         d2 = dx[:, 0] * dx[:, 0] + dx[:, 1] * dx[:, 1] + dx[:, 2] * dx[:, 2]
-        part = np.argpartition(d2, 40)[:40]
+        part = np.argpartition(d2, 41)[:41]
         order = part[np.argsort(d2[part], kind="stable")]
-        assert np.array_equal(order, idx[i]), i
-        assert np.array_equal(np.sqrt(d2[order]), dd[i])
+        m = int(nontriv[i])
+        assert np.array_equal(order[:m], idx[i, :m]), i
+        assert np.array_equal(np.sqrt(d2[order[:m]]), dd[i, :m])
+        assert m == 40 or np.sqrt(d2[order[m]]) >= dist                      # the cut, not the search, ended the row
     out = nsc.hydro_update(idx, p, st["mass"], sizes, None, st["particle_type"], st["T"], st["mu_array"],
                            st["gamma_array"], st["velocities"])
     rho = out[3]
     sub = rs.randint(0, n, 2000)
-    hj = sizes[idx[sub]]
+    jj = np.where(valid[sub], idx[sub], 0)
+    hj = sizes[jj]
     W = 315. / (64 * np.pi * hj ** 9) * (hj ** 2 - dd[sub] ** 2) ** 3
-    W[W < 0] = 0
-    assert rel(rho[sub], np.sum(st["mass"][idx[sub]] * W, axis=1)) < RTOL
-    assert np.all(rho > 0) and np.all(np.isfinite(out[0]))
+    W[(W < 0) | ~valid[sub]] = 0
+    assert rel(rho[sub], np.sum(st["mass"][jj] * W, axis=1)) < RTOL
+    assert np.all(rho > 0) and np.all(np.isfinite(out[0])) and np.all(np.isfinite(out[1]))
 
 
 def test_net_impulse_against_reference_outputs(built_lib):
