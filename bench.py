@@ -41,8 +41,8 @@ ALGO_BYTES = {"sort": 216.0, "knn": 32.0, "density": 76.0, "pi": 116.0, "force":
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--n", type=float, default=1e6, help="particles per GPU")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--kind", default="uniform", choices=["uniform", "clustered"])
@@ -304,8 +304,8 @@ def run_ours(args):
     traffic, traffic_src = ncu_traffic(top_kernel)
     roofline = {"kernel": top, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
-                "note": "the k-NN kernel is bound by instruction issue / the fp64 pipe, not HBM (ncu: issue slots 71 % "
-                        "busy, fp64 pipe 24 %, DRAM 2 %; profiles/README.md); its algorithmic traffic is 32 B/particle",
+                "note": "the k-NN kernel is bound by instruction issue / the fp64 pipe, not HBM (ncu: issue slots 74 % "
+                        "busy, fp64 pipe 26 %, DRAM 2 %; profiles/README.md); its algorithmic traffic is 32 B/particle",
                 "algo_bytes_per_particle": ALGO_BYTES.get(top), "avg_launch_ms": phase_ms[top],
                 "density_plus_force_frac": round((ALGO_BYTES["density"] + ALGO_BYTES["force"]) * n_local / 1e9 /
                                                  ((phase_ms.get("density", 0) + phase_ms.get("force", 0)) * 1e-3) / peak, 4)
@@ -323,9 +323,9 @@ def run_ours(args):
         line["e2e"] = e2e
     if world == 1 and not args.no_cpu:
         cn = int(args.cpu_n)
-        v, per = cpu_steps(cn, args.kind, 2, 0, 1)
+        v, per = cpu_steps(cn, args.kind, 5, 0, 1)                     # ~10 s of CPU work at the default N = 1e5
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": 1, "kind": "port", "host_cpus": os.cpu_count(),
-                                "sample": "2 steps of the CPU port (oracle/sph_oracle.py, numpy + scipy cKDTree, "
+                                "sample": "5 steps of the CPU port (oracle/sph_oracle.py, numpy + scipy cKDTree, "
                                           "single-threaded as the reference runs) on N=%d particles of the same box "
                                           "recipe, %.2f s per step" % (cn, per)}
     print(json.dumps(line), flush=True)
