@@ -119,6 +119,15 @@ int sphb200_session_gather(sphb200_ctx* ctx, const char* field, const int64_t* i
 int sphb200_session_scatter(sphb200_ctx* ctx, const char* field, const int64_t* idx, int64_t count, const double* in, void* stream);
 int sphb200_session_download_rows(sphb200_ctx* ctx, double* rows, int64_t n_rows, int ncol, void* stream);
 int sphb200_session_upload_rows(sphb200_ctx* ctx, const double* rows, int64_t n_rows, int ncol, void* stream);
+/* pieces of the same: download with column 18 filled from `tag` (device, caller order: the particle id a slab
+ * decomposition sends along with a row); upload of the rows of the caller indices [first, first + n_rows) */
+int sphb200_session_download_rows_tagged(sphb200_ctx* ctx, double* rows, int64_t n_rows, int ncol, const double* tag,
+                                         void* stream);
+int sphb200_session_upload_rows_at(sphb200_ctx* ctx, const double* rows, int64_t first, int64_t n_rows, int ncol, void* stream);
+/* slab decomposition, after the search: writes [1 if some owned particle's ball (x, h) leaves [lo, hi) along x,
+ * largest h of the owned particles] into the float64 buffer "cover" (sphb200_session_buffer), to be
+ * all_reduced (MAX) in place */
+int sphb200_session_cover_check(sphb200_ctx* ctx, double lo, double hi, void* stream);
 /* SURVEY row F4, variable-N state (code_running.py:361-381 grows every array when a supernova injects
  * particles): append n_new rows (same layout) as caller indices N .. N+n_new-1, keeping the existing state
  * and scalars.  Run the phases "sort" and "knn" afterwards (the driver's nsc.neighbors call at :386); the
@@ -142,6 +151,7 @@ int sphb200_session_startup(sphb200_ctx* ctx, void* stream);
  * set by sphb200_session_set_drag, off by default) */
 int sphb200_session_step(sphb200_ctx* ctx, void* stream);
 /* device pointer + element count of an internal array a caller-side collective works on in place:
+ * "cover": float64 [bad, hmax] of sphb200_session_cover_check;
  * "length_hist": int64 histogram of the percentile's radix select (code_running.py:515-518), valid between
  * the phases "length_hist" and "length_pick"; a slab decomposition all_reduces (SUM) it there, five times
  * per step ("length_begin", then 5 x ("length_hist", all_reduce, "length_pick")). */

@@ -33,6 +33,9 @@ SIGNATURES = {
     "sphb200_session_create": [c_ptr, c_i64, c_int, c_dbl],
     "sphb200_session_resize": [c_ptr, c_i64, c_i64, c_ptr],
     "sphb200_session_append_rows": [c_ptr, c_ptr, c_i64, c_int, c_ptr],
+    "sphb200_session_download_rows_tagged": [c_ptr, c_ptr, c_i64, c_int, c_ptr, c_ptr],
+    "sphb200_session_upload_rows_at": [c_ptr, c_ptr, c_i64, c_i64, c_int, c_ptr],
+    "sphb200_session_cover_check": [c_ptr, c_dbl, c_dbl, c_ptr],
     "sphb200_session_buffer": [c_ptr, ctypes.c_char_p, c_ptr, c_ptr],
     "sphb200_session_set_drag": [c_ptr, c_ptr, c_int, c_ptr, c_ptr, c_ptr],
     "sphb200_session_upload": [c_ptr, ctypes.c_char_p, c_ptr, c_i64, c_ptr],

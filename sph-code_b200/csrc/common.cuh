@@ -120,6 +120,8 @@ enum Scal {
   SC_AGE = 9,
   SC_MAXDIST = 10,    // 90th percentile of |x|^2 among slow particles
   SC_NSLOW = 11,
+  SC_COVER_BAD = 12,  // slab decomposition: 1 if some owned particle's k-th neighbour ball leaves the covered region
+  SC_COVER_HMAX = 13, // largest smoothing length among the owned particles
   SC_COUNT = 32
 };
 

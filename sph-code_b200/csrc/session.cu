@@ -426,7 +426,7 @@ scatter_at_kernel(int64_t count, int w, int n, const int64_t* __restrict__ cidx,
 // Whole particle rows (AoS, `ncol` doubles per particle: the eleven state fields in kFieldName order,
 // then the k-NN trial radius) <-> the session's sorted struct of arrays, in one pass.  The slab
 // decomposition moves particles between ranks as such rows (domain.py).
-struct RowArgs { double* f[F_NFIELDS]; double* knnh; };
+struct RowArgs { double* f[F_NFIELDS]; double* knnh; const double* tag; };   // tag: optional caller-order column 18
 #define ROW_STATE_COLS 18
 
 // One warp per 32 sorted particles: the 18 values of each particle are read field by field (coalesced)
@@ -452,24 +452,29 @@ rows_out_kernel(int n, int64_t n_rows, int ncol, const uint32_t* __restrict__ id
   __syncwarp();
   for (int r = 0; r < 32; ++r) {
     const int64_t cr = __shfl_sync(0xffffffffu, c, r);
-    if (cr >= 0 && cr < n_rows && lane < ROW_STATE_COLS) dst[cr * ncol + lane] = tile[warp][r][lane];
+    if (cr >= 0 && cr < n_rows) {
+      if (lane < ROW_STATE_COLS) dst[cr * ncol + lane] = tile[warp][r][lane];
+      else if (lane == ROW_STATE_COLS && a.tag) dst[cr * ncol + ROW_STATE_COLS] = a.tag[cr];
+    }
   }
 }
 
 __global__ void __launch_bounds__(256)
-rows_in_kernel(int n, int ncol, const uint32_t* __restrict__ id, const double* __restrict__ src, RowArgs a) {
+rows_in_kernel(int n, int ncol, const uint32_t* __restrict__ id, const double* __restrict__ src, RowArgs a,
+               int64_t first = 0, int64_t n_rows = -1) {
   __shared__ double tile[8][32][ROW_STATE_COLS + 1];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int base = (blockIdx.x * 8 + warp) * 32;
   if (base >= n) return;
   const int i = base + lane;
-  const int64_t c = (i < n) ? (id ? (int64_t)id[i] : (int64_t)i) : -1;       // id == nullptr: row r -> slot r
+  int64_t c = (i < n) ? (id ? (int64_t)id[i] : (int64_t)i) : -1;             // id == nullptr: row r -> slot r
+  if (n_rows >= 0) c = (c >= first && c < first + n_rows) ? c - first : -1;  // only the caller indices [first, first + n_rows)
   for (int r = 0; r < 32; ++r) {
     const int64_t cr = __shfl_sync(0xffffffffu, c, r);
     if (cr >= 0 && lane < ROW_STATE_COLS) tile[warp][r][lane] = src[cr * ncol + lane];
   }
   __syncwarp();
-  if (i < n) {
+  if (i < n && c >= 0) {
     int col = 0;
 #pragma unroll
     for (int f = 0; f < 3; ++f)
@@ -891,7 +896,18 @@ int sphb200_session_scatter(sphb200_ctx* ctx, const char* field, const int64_t* 
 }
 
 // rows: device pointer, (n_rows, ncol) doubles, caller order; ncol >= 18 (extra columns are the caller's)
+static int download_rows_impl(sphb200_ctx* ctx, double* rows, int64_t n_rows, int ncol, const double* tag, void* stream);
 int sphb200_session_download_rows(sphb200_ctx* ctx, double* rows, int64_t n_rows, int ncol, void* stream) {
+  return download_rows_impl(ctx, rows, n_rows, ncol, nullptr, stream);
+}
+// same, and column 18 of every row is filled from `tag` (device, caller order, >= n_rows doubles): the id a
+// slab decomposition sends along with a row
+int sphb200_session_download_rows_tagged(sphb200_ctx* ctx, double* rows, int64_t n_rows, int ncol, const double* tag,
+                                         void* stream) {
+  if (!tag || ncol < ROW_STATE_COLS + 1) SPH_FAIL("session_download_rows_tagged: needs a tag array and ncol >= 19");
+  return download_rows_impl(ctx, rows, n_rows, ncol, tag, stream);
+}
+static int download_rows_impl(sphb200_ctx* ctx, double* rows, int64_t n_rows, int ncol, const double* tag, void* stream) {
   if (!ctx || !rows) SPH_FAIL("session_download_rows: null argument");
   CUDA_TRY(cudaSetDevice(ctx->device));
   Session& s = sess(ctx);
@@ -900,25 +916,37 @@ int sphb200_session_download_rows(sphb200_ctx* ctx, double* rows, int64_t n_rows
   RowArgs a;
   for (int f = 0; f < F_NFIELDS; ++f) a.f[f] = fld(ctx, f);
   a.knnh = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]);
+  a.tag = tag;
   rows_out_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, n_rows, ncol, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]), a, rows);
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
 
-int sphb200_session_upload_rows(sphb200_ctx* ctx, const double* rows, int64_t n_rows, int ncol, void* stream) {
-  if (!ctx || !rows) SPH_FAIL("session_upload_rows: null argument");
+// rows for the caller indices [first, first + n_rows)
+int sphb200_session_upload_rows_at(sphb200_ctx* ctx, const double* rows, int64_t first, int64_t n_rows, int ncol, void* stream) {
+  if (!ctx || (!rows && n_rows > 0)) SPH_FAIL("session_upload_rows: null argument");
   CUDA_TRY(cudaSetDevice(ctx->device));
   Session& s = sess(ctx);
-  if (ncol < ROW_STATE_COLS || n_rows != s.n) SPH_FAIL("session_upload_rows: needs (%lld, >=18) rows, got (%lld, %d)", (long long)s.n, (long long)n_rows, ncol);
+  if (ncol < ROW_STATE_COLS || first < 0 || n_rows < 0 || first + n_rows > s.n)
+    SPH_FAIL("session_upload_rows: rows [%lld, %lld) x %d do not fit %lld particles x >= 18 columns", (long long)first,
+             (long long)(first + n_rows), ncol, (long long)s.n);
+  if (n_rows == 0) return 0;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   RowArgs a;
   for (int f = 0; f < F_NFIELDS; ++f) a.f[f] = fld(ctx, f);
   a.knnh = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]);
-  rows_in_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, ncol, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]), rows, a);
+  a.tag = nullptr;
+  rows_in_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, ncol, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]), rows, a, first, n_rows);
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;
+}
+
+int sphb200_session_upload_rows(sphb200_ctx* ctx, const double* rows, int64_t n_rows, int ncol, void* stream) {
+  if (!ctx) SPH_FAIL("null context");
+  if (n_rows != sess(ctx).n) SPH_FAIL("session_upload_rows: needs all %lld rows, got %lld", (long long)sess(ctx).n, (long long)n_rows);
+  return sphb200_session_upload_rows_at(ctx, rows, 0, n_rows, ncol, stream);
 }
 
 // grow a buffer to `bytes`, keeping its first `keep` bytes (devbuf_reserve alone discards the content)
@@ -965,6 +993,7 @@ int sphb200_session_append_rows(sphb200_ctx* ctx, const double* rows, int64_t n_
   RowArgs a;
   for (int f = 0; f < F_NFIELDS; ++f) a.f[f] = fld(ctx, f) + (size_t)n0 * kFieldWidth[f];
   a.knnh = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]) + n0;
+  a.tag = nullptr;
   rows_in_kernel<<<ceil_div(n_new, 256), 256, 0, st>>>((int)n_new, ncol, nullptr, rows, a);
   iota_kernel<<<ceil_div(n_new, 256), 256, 0, st>>>((int)n_new, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]) + n0, (uint32_t)n0);
   ctx->launches += 2;
@@ -1051,6 +1080,45 @@ int sphb200_session_set_drag(sphb200_ctx* ctx, const void* f_un, int n_species, 
   return 0;
 }
 
+// Slab decomposition, after the search: does every owned particle's ball (x, h) stay inside [lo, hi) along x
+// (the region this rank's owned + ghost particles cover), and what is the largest h?  Both land in device
+// scalars (buffer "cover": [bad, hmax]) so the ranks can all_reduce(MAX) them in place.
+__global__ void __launch_bounds__(256)
+cover_check_kernel(int n, const double* __restrict__ pos, const double* __restrict__ h, const uint32_t* __restrict__ id,
+                   int n_owned, double lo, double hi, double* __restrict__ scal) {
+  __shared__ unsigned long long s_bad, s_h;
+  if (threadIdx.x == 0) { s_bad = 0ull; s_h = 0ull; }
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && (int)id[i] < n_owned) {
+    const double x = pos[3 * (int64_t)i], hh = h[i];
+    const bool ok = ((x - hh) >= lo) && ((x + hh) < hi);
+    if (!ok) atomicMax(&s_bad, (unsigned long long)__double_as_longlong(1.0));
+    if (hh > 0.0) atomicMax(&s_h, (unsigned long long)__double_as_longlong(hh));
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (s_bad) atomicMax(reinterpret_cast<unsigned long long*>(scal + SC_COVER_BAD), s_bad);
+    if (s_h) atomicMax(reinterpret_cast<unsigned long long*>(scal + SC_COVER_HMAX), s_h);
+  }
+}
+
+int sphb200_session_cover_check(sphb200_ctx* ctx, double lo, double hi, void* stream) {
+  if (!ctx) SPH_FAIL("null context");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  Session& s = sess(ctx);
+  if (s.k <= 0) SPH_FAIL("session_cover_check: no session");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  double* scal = bufp<double>(ctx->scal);
+  CUDA_TRY(cudaMemsetAsync(scal + SC_COVER_BAD, 0, 2 * sizeof(double), st));
+  const int n_owned = s.n_owned >= 0 ? (int)s.n_owned : (int)s.n;
+  cover_check_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, fld(ctx, F_POS), fld(ctx, F_H),
+                                                         bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]), n_owned, lo, hi, scal);
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
 // Device pointer of an internal array a caller-side collective works on in place:
 // "length_hist" = the radix-select histogram (int64, 2*8192 + 1 values) between the phases "length_hist"
 // and "length_pick" (a slab decomposition all_reduces it there).
@@ -1061,6 +1129,11 @@ int sphb200_session_buffer(sphb200_ctx* ctx, const char* name, void** ptr, int64
     SPH_TRY(devbuf_reserve(ctx->sbuf[SB_SEL], (SEL_HIST + 8) * sizeof(long long) + sizeof(SelectState)));
     *ptr = sel_hist(ctx);
     *count = SEL_HIST;
+    return 0;
+  }
+  if (!strcmp(name, "cover")) {               // float64 [bad, hmax] written by sphb200_session_cover_check
+    *ptr = bufp<double>(ctx->scal) + SC_COVER_BAD;
+    *count = 2;
     return 0;
   }
   SPH_FAIL("session_buffer: unknown buffer '%s'", name);

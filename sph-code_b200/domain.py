@@ -290,6 +290,7 @@ class DistributedSession(object):
         self.halo_redo = 0
         self.hmax = 0.0
         self._hist = None
+        self._cover = None
         nt = torch.tensor([float(self.n_own)], dtype=torch.float64, device=self.device)
         dist.all_reduce(nt, op=dist.ReduceOp.SUM, group=group)
         self.n_total = int(nt.item())
@@ -344,18 +345,19 @@ class DistributedSession(object):
     def _open_session(self, rows, w):
         """Ghost exchange for halo width w, then a session over owned + ghost rows."""
         ghosts = self.ex.build_halo(rows, w)
-        local = torch.cat([rows, ghosts], dim=0).contiguous()
         self.rows = rows
         self.n_own = int(rows.shape[0])
+        n_loc = self.n_own + int(ghosts.shape[0])
         if self.sess is None:
-            s = self._Session(int(local.shape[0]), self.k, self.dist_cut, device=self.device.index, dt_0=self.dt_0)
+            s = self._Session(n_loc, self.k, self.dist_cut, device=self.device.index, dt_0=self.dt_0)
             for name, v in (("age", 0.0), ("d", self.d), ("dt", self.dt_0), ("ct", 0.0), ("n_owned", self.n_own)):
                 s.set_scalar(name, v)
         else:
             s = self.sess
-            s.resize(int(local.shape[0]), self.n_own)                  # keeps the device scalars: no host traffic
-        s.upload_rows(local)
-        self.gid = local[:, 18].contiguous()
+            s.resize(n_loc, self.n_own)                            # keeps the device scalars: no host traffic
+        s.upload_rows_at(rows, 0)                                  # two pieces: no concatenated copy of the state
+        s.upload_rows_at(ghosts.contiguous(), self.n_own)
+        self.gid = torch.cat([rows[:, 18], ghosts[:, 18]])
         self._send_cat = torch.cat(self.ex.send_idx)
         self._send_counts = [int(i.numel()) for i in self.ex.send_idx]
         self._n_ghost = int(ghosts.shape[0])
@@ -370,9 +372,7 @@ class DistributedSession(object):
 
     def _owned_rows(self):
         """Current owned rows (state columns + trial radius + gid) out of the session."""
-        rows = self.sess.download_rows(self.n_own, NCOL)
-        rows[:, 18] = self.gid[:self.n_own]
-        return rows
+        return self.sess.download_rows_tagged(self.n_own, NCOL, self.gid)
 
     def _initial_halo_width(self, rows):
         """1.6 x the k-th-neighbour distance expected at the mean number density of the global box."""
@@ -391,12 +391,13 @@ class DistributedSession(object):
         while True:
             self.sess.phase("sort")
             self.sess.phase("knn")
-            h = self.sess.download_tensor("sizes")[:self.n_own]
-            x = self.sess.download_tensor("points")[:self.n_own, 0]
-            chk = torch.stack([(~self.ex.covered(x, h)).any().to(torch.float64),
-                               h.max() if self.n_own else torch.zeros((), dtype=torch.float64, device=self.device)])
-            dist.all_reduce(chk, op=dist.ReduceOp.MAX, group=self.group)            # one collective, one host sync
-            bad, self.hmax = chk.tolist()
+            lo = self.ex.lo - self.ex.w if self.ex.rank > 0 else float("-inf")
+            hi = self.ex.hi + self.ex.w if self.ex.rank < self.ex.world - 1 else float("inf")
+            self.sess.cover_check(lo, hi)                          # [ball leaves the covered region, largest h] on the device
+            if self._cover is None:
+                self._cover = self.sess.buffer_tensor("cover")
+            dist.all_reduce(self._cover, op=dist.ReduceOp.MAX, group=self.group)    # one collective, one host sync
+            bad, self.hmax = self._cover.tolist()
             if bad == 0:
                 break
             self.halo_redo += 1
@@ -485,9 +486,7 @@ class DistributedSession(object):
         """One step of a host-resident slab: the owned rows are uploaded from pinned memory into the
         session, the step runs (with its exchanges), the new owned rows come back to pinned memory."""
         rows = hs["buf"][:hs["n"]].to(self.device, non_blocking=True)
-        full = self.sess.download_rows(self.sess.n, NCOL)          # ghosts keep their rows (refreshed in the step)
-        full[:self.n_own] = rows
-        self.sess.upload_rows(full)
+        self.sess.upload_rows_at(rows, 0)                          # ghosts keep their rows (refreshed in the step)
         self.step()
         out = self._owned_rows()
         if out.shape[0] > hs["buf"].shape[0]:

@@ -101,14 +101,30 @@ class Session(object):
                                                    int(t.numel()), self._stream()))
 
     def buffer_tensor(self, name):
-        """Zero-copy int64 tensor over an internal device array ("length_hist")."""
+        """Zero-copy tensor over an internal device array: "length_hist" (int64), "cover" (float64)."""
         ptr = ctypes.c_void_p(0); cnt = ctypes.c_int64(0)
         _lib.check(self.lib.sphb200_session_buffer(self.ctx.handle, name.encode(), ctypes.byref(ptr), ctypes.byref(cnt)))
 
         class _Raw(object):
-            __cuda_array_interface__ = {"shape": (int(cnt.value),), "typestr": "<i8", "data": (int(ptr.value), False),
-                                        "version": 2, "strides": None}
+            __cuda_array_interface__ = {"shape": (int(cnt.value),), "typestr": "<f8" if name == "cover" else "<i8",
+                                        "data": (int(ptr.value), False), "version": 2, "strides": None}
         return torch.as_tensor(_Raw(), device=self.device)
+
+    def cover_check(self, lo, hi):
+        _lib.check(self.lib.sphb200_session_cover_check(self.ctx.handle, float(lo), float(hi), self._stream()))
+
+    def download_rows_tagged(self, n_rows, ncol, tag):
+        """download_rows with column 18 taken from `tag` (float64 CUDA tensor, caller order)."""
+        rows = torch.empty((int(n_rows), int(ncol)), dtype=torch.float64, device=self.device)
+        _lib.check(self.lib.sphb200_session_download_rows_tagged(self.ctx.handle, ctypes.c_void_p(rows.data_ptr()), int(n_rows),
+                                                                 int(ncol), ctypes.c_void_p(tag.data_ptr()), self._stream()))
+        return rows
+
+    def upload_rows_at(self, rows, first):
+        if rows.dtype != torch.float64 or not rows.is_cuda or not rows.is_contiguous():
+            raise ValueError("upload_rows_at needs a contiguous float64 CUDA tensor")
+        _lib.check(self.lib.sphb200_session_upload_rows_at(self.ctx.handle, ctypes.c_void_p(rows.data_ptr()), int(first),
+                                                           int(rows.shape[0]), int(rows.shape[1]), self._stream()))
 
     def gather(self, name, idx):
         """Field `name` at caller indices idx (int64 CUDA tensor) -> (len(idx), width) float64 tensor."""
