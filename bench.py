@@ -73,6 +73,23 @@ def ncu_traffic(kernel_substr):
     return None, None
 
 
+def ncu_value(kernel_substr, metric):
+    """One metric of one kernel from the committed ncu `--set full` summary; None when absent."""
+    import glob
+    import re
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_full_step.txt")), reverse=True):
+        try:
+            txt = open(path).read()
+        except OSError:
+            continue
+        for block in txt.split("== ")[1:]:
+            if kernel_substr in block.split("\n", 1)[0]:
+                m = re.search(re.escape(metric) + r"\s+(?:\S+\s+)?([0-9.]+)\s*$", block, re.M)
+                if m:
+                    return float(m.group(1)), os.path.basename(path)
+    return None, None
+
+
 def peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -310,6 +327,18 @@ def run_ours(args):
                 "density_plus_force_frac": round((ALGO_BYTES["density"] + ALGO_BYTES["force"]) * n_local / 1e9 /
                                                  ((phase_ms.get("density", 0) + phase_ms.get("force", 0)) * 1e-3) / peak, 4)
                 if (phase_ms.get("density", 0) + phase_ms.get("force", 0)) > 0 else None}
+    # the bound that does bind this kernel ("report both fractions and say which binds"):
+    # warp instructions per launch from the committed ncu capture / the live launch time, against the SM's
+    # issue rate (4 warp instructions per clock and SM at the sampled SM clock)
+    inst, inst_src = ncu_value(top_kernel, "smsp__inst_executed.sum")
+    if inst is not None and clocks and clocks.get("sm_mhz"):
+        # the capture is of one N = 1e6 launch: scale to this run's particles per GPU
+        inst_launch = inst * n_local / 1.0e6
+        issue_peak = 148 * 4 * float(clocks["sm_mhz"]) * 1e6
+        roofline["issue"] = {"bound": "instruction issue", "achieved": inst_launch / (phase_ms[top] * 1e-3) / 1e9,
+                             "peak": issue_peak / 1e9, "unit": "G warp-instr/s", "frac": inst_launch / (phase_ms[top] * 1e-3) / issue_peak,
+                             "warp_instr_per_particle": inst / 1.0e6, "source": inst_src,
+                             "what": "instructions of %s only; the phase time also holds the work-list kernel" % top_kernel}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": args.warmup,
             "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
