@@ -230,7 +230,11 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        # a stuck collective must fail loudly and soon (stack of every thread on stderr), not hang the run
+        import datetime
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ.get("BENCH_WATCHDOG_S", "540")), exit=True)
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
     if rank == 0:
         ge.build()
     if world > 1:

@@ -91,19 +91,20 @@ class SlabExchange(object):
     # -- the three exchanges --------------------------------------------------------------------
     def migrate(self, rows):
         """Send every row to the rank whose slab holds its x (column 0); returns the new owned rows.
-        One host sync (send and receive counts together); when nobody moves anywhere near this rank the
-        rows are returned as they are, otherwise only the movers are gathered and split."""
+        One host sync (the whole count table); when no particle of any rank moves the rows are returned
+        as they are (a decision every rank takes identically), otherwise only the movers are gathered."""
         dest = self.owner_of(rows[:, 0].contiguous())
         counts = torch.bincount(dest, minlength=self.world)            # stays on the device
-        rc = torch.empty_like(counts)
-        dist.all_to_all_single(rc, counts, group=self.group)
-        both = torch.cat([counts, rc]).tolist()                        # the one sync
-        send_list, recv_list = both[:self.world], both[self.world:]
-        recv_list[self.rank] = 0
-        n_out = sum(send_list) - send_list[self.rank]
+        table = torch.empty(self.world * self.world, dtype=counts.dtype, device=counts.device)
+        dist.all_gather_into_tensor(table, counts, group=self.group)   # every rank sees who sends what to whom,
+        table = table.view(self.world, self.world).tolist()            # so all of them take the same branch (one sync)
+        send_list = list(table[self.rank])
+        recv_list = [table[r][self.rank] for r in range(self.world)]
         send_list[self.rank] = 0
-        if n_out == 0 and sum(recv_list) == 0:
-            return rows
+        recv_list[self.rank] = 0
+        n_out = sum(send_list)
+        if sum(table[a][b] for a in range(self.world) for b in range(self.world) if a != b) == 0:
+            return rows                                                # nobody moves anywhere: no second collective
         stay = dest == self.rank
         if n_out:
             mv = torch.nonzero(~stay, as_tuple=False).flatten()
@@ -388,6 +389,7 @@ class DistributedSession(object):
     def _search(self):
         """sort + k-NN on owned + ghosts; widen the halo and redo until every owned particle's k-th
         neighbour provably lies inside the covered region; then fetch the ghosts' owner-computed h."""
+        redo = 0
         while True:
             self.sess.phase("sort")
             self.sess.phase("knn")
@@ -400,6 +402,11 @@ class DistributedSession(object):
             bad, self.hmax = self._cover.tolist()
             if bad == 0:
                 break
+            redo += 1
+            if redo > 8 or not math.isfinite(self.hmax):
+                self.sess.check()
+                raise RuntimeError("slab search: halo width %.3e still does not cover the k-th neighbours after %d "
+                                   "doublings (largest h %.3e): non-finite positions?" % (self.w, redo, self.hmax))
             self.halo_redo += 1
             self._open_session(self.rows, 2.0 * self.w)
         self._refresh_ghosts("sizes")
