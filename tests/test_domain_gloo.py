@@ -1,4 +1,4 @@
-"""CPU, world_size 2 over gloo: the slab decomposition's host logic (sphb200.domain) — migration, ghost
+"""CPU, world_size 2 (and 3, 8 for the exchange protocol) over gloo: the slab decomposition's host logic (sphb200.domain) — migration, ghost
 selection and refresh, the distributed percentile — and the whole exchange protocol with the CPU oracle
 standing in for the CUDA passes: owned particles must get exactly the single-process neighbour rows
 and densities ("results must be identical to the 1-GPU run for owned particles")."""
@@ -22,15 +22,17 @@ def _free_port():
     return p
 
 
-def _run(fn, *args):
+def _run(fn, *args, world=WORLD):
     port = _free_port()
-    mp.spawn(_entry, args=(fn, port, args), nprocs=WORLD, join=True)
+    mp.spawn(_entry, args=(fn, port, world, args), nprocs=world, join=True)
 
 
-def _entry(rank, fn, port, args):
+def _entry(rank, fn, port, world, args):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
-    dist.init_process_group("gloo", rank=rank, world_size=WORLD)
+    os.environ["OMP_NUM_THREADS"] = "1"
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         fn(rank, *args)
     finally:
@@ -38,22 +40,33 @@ def _entry(rank, fn, port, args):
 
 
 # ------------------------------------------------------------------------------------------------
-def _w_exchange(rank):
+def _w_exchange(rank, w=0.31):
     from sphb200.domain import SlabExchange, NCOL
+    world = dist.get_world_size()
     rs = np.random.RandomState(0)
     n = 5000
     rows = np.zeros((n, NCOL))
     rows[:, :3] = rs.rand(n, 3) * [4.0, 1.0, 1.0]
     rows[:, 18] = np.arange(n)
     rows[:, 10] = 2.0 * np.arange(n)                       # a field to refresh later
-    bounds = [-np.inf, 1.7, np.inf]
-    start = rows[rs.permutation(n)[rank::WORLD]]           # ownership unrelated to position
+    bounds = [-np.inf, 1.7, np.inf] if world == 2 else [-np.inf] + list(np.linspace(0, 4, world + 1)[1:-1]) + [np.inf]
+    start = rows[rs.permutation(n)[rank::world]]           # ownership unrelated to position
     ex = SlabExchange(bounds)
     own = ex.migrate(torch.from_numpy(start))
     x = rows[:, 0]
     mine = (x >= bounds[rank]) & (x < bounds[rank + 1])
     assert sorted(own[:, 18].numpy().astype(int)) == sorted(np.nonzero(mine)[0])
-    w = 0.31
+    again = ex.migrate(own)                                # nobody moves: every rank must take the same shortcut
+    assert again.shape == own.shape and torch.equal(again, own)
+    if rank == 0 and own.shape[0]:                         # one particle of one rank moves: the others have no traffic
+        own = own.clone(); own[0, 0] = bounds[1] + 1e-3
+    own2 = ex.migrate(own)
+    moved_t = torch.tensor([int(own[0, 18]) if rank == 0 else -1]); dist.broadcast(moved_t, 0)
+    moved = int(moved_t)
+    x = x.copy(); x[moved] = bounds[1] + 1e-3
+    mine = (x >= bounds[rank]) & (x < bounds[rank + 1])
+    assert sorted(own2[:, 18].numpy().astype(int)) == sorted(np.nonzero(mine)[0])
+    own = own2
     ghosts = ex.build_halo(own, w)
     want = (~mine) & (x >= bounds[rank] - w) & (x < bounds[rank + 1] + w)
     assert sorted(ghosts[:, 18].numpy().astype(int)) == sorted(np.nonzero(want)[0])
@@ -66,14 +79,23 @@ def _w_exchange(rank):
     # coverage test: a ball reaching past the halo is flagged
     h = torch.full((own.shape[0],), 0.3, dtype=torch.float64)
     ok = ex.covered(own[:, 0], h)
-    if rank == 0:
-        assert torch.equal(ok, own[:, 0] + 0.3 < 1.7 + w)
-    else:
-        assert torch.equal(ok, own[:, 0] - 0.3 >= 1.7 - w)
+    want_ok = torch.ones_like(ok)
+    if rank > 0:
+        want_ok &= own[:, 0] - 0.3 >= bounds[rank] - w
+    if rank < world - 1:
+        want_ok &= own[:, 0] + 0.3 < bounds[rank + 1] + w
+    assert torch.equal(ok, want_ok)
 
 
 def test_migrate_halo_refresh():
     _run(_w_exchange)
+
+
+@pytest.mark.parametrize("world,w", [(3, 0.31), (8, 0.31), (8, 0.7)])
+def test_migrate_halo_refresh_more_ranks(world, w):
+    """more slabs than the GPU tests can afford: middle ranks with two neighbours, ranks that exchange nothing
+    with most others, and (w = 0.7 > slab width 0.5) halos that reach across two slabs."""
+    _run(_w_exchange, w, world=world)
 
 
 def _w_percentile(rank):
@@ -106,10 +128,11 @@ def _w_protocol(rank):
     g_out = O.hydro_update(g_idx, st["points"], st["mass"], g_h, None, st["particle_type"], st["T"], st["mu_array"],
                            st["gamma_array"], st["velocities"], species=False)
     rows = rows_from_state(st)
-    bounds = equal_count_bounds(rows[:, 0], WORLD)
+    world = dist.get_world_size()
+    bounds = equal_count_bounds(rows[:, 0], world)
     ex = SlabExchange(bounds)
-    own = ex.migrate(torch.from_numpy(rows[rank::WORLD].copy()))
-    assert abs(own.shape[0] - 2000) <= 1
+    own = ex.migrate(torch.from_numpy(rows[rank::world].copy()))
+    assert abs(own.shape[0] - 4000 // world) <= 1
     w = 1.25 * float(g_h.max())
     ghosts = ex.build_halo(own, w)
     local = torch.cat([own, ghosts]).numpy()
@@ -136,3 +159,7 @@ def _w_protocol(rank):
 
 def test_exchange_protocol_reproduces_single_process_results():
     _run(_w_protocol)
+
+
+def test_exchange_protocol_three_ranks():
+    _run(_w_protocol, world=3)
