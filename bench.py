@@ -233,7 +233,7 @@ def run_ours(args):
         # a stuck collective must fail loudly and soon (stack of every thread on stderr), not hang the run
         import datetime
         import faulthandler
-        faulthandler.dump_traceback_later(int(os.environ.get("BENCH_WATCHDOG_S", "540")), exit=True)
+        faulthandler.dump_traceback_later(int(os.environ.get("BENCH_WATCHDOG_S", "420")), exit=True)
         dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
     if rank == 0:
         ge.build()
