@@ -156,6 +156,9 @@ def equal_count_bounds(x, world):
     return [-np.inf] + inner + [np.inf]
 
 
+# The three functions below are the torch-level form of the distributed percentile (any backend, so they
+# run over gloo in the CPU tests and serve host-side callers).  The slab driver itself no longer uses
+# them: its percentile is the radix select inside libsphb200 with the histogram all_reduced in place.
 def distributed_order_statistic(sorted_local, k, group=None):
     """Exact k-th smallest (0-based) of the union of every rank's `sorted_local` (ascending float64,
     values >= 0, no NaN).  Radix select on the IEEE bit patterns (monotone for non-negative doubles):
