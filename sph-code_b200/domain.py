@@ -22,6 +22,7 @@ reference's formulas need from the other side of a slab face:
 libsphb200 (include/sphb200.h: sphb200_session_*) between the exchanges.
 """
 import math
+import os
 
 import numpy as np
 import torch
@@ -46,6 +47,9 @@ def rows_from_state(state, gid=None):
             rows[:, a:b] = np.asarray(state[name], dtype=np.float64).reshape(n, b - a)
     rows[:, 18] = np.arange(n) if gid is None else gid
     return rows
+
+
+_NCCL_INPLACE = os.environ.get("SPHB200_NCCL_INPLACE", "0") == "1"
 
 
 class SlabExchange(object):
@@ -295,6 +299,7 @@ class DistributedSession(object):
         self.hmax = 0.0
         self._hist = None
         self._cover = None
+        self._stage = {}
         nt = torch.tensor([float(self.n_own)], dtype=torch.float64, device=self.device)
         dist.all_reduce(nt, op=dist.ReduceOp.SUM, group=group)
         self.n_total = int(nt.item())
@@ -374,6 +379,21 @@ class DistributedSession(object):
             self._hist = self.sess.buffer_tensor("length_hist")
         return self._hist
 
+    def _reduce_buffer(self, view, op):
+        """all_reduce a library-owned device buffer (`view`: zero-copy tensor over it).  By default the
+        collective runs on a torch-allocated staging tensor (two small device copies around it), so that
+        NCCL only ever sees memory of torch's allocator; SPHB200_NCCL_INPLACE=1 reduces the buffer in place."""
+        if _NCCL_INPLACE:
+            dist.all_reduce(view, op=op, group=self.group)
+            return view
+        stage = self._stage.get(view.data_ptr())
+        if stage is None:
+            stage = self._stage[view.data_ptr()] = torch.empty_like(view)
+        stage.copy_(view)
+        dist.all_reduce(stage, op=op, group=self.group)
+        view.copy_(stage)
+        return stage
+
     def _owned_rows(self):
         """Current owned rows (state columns + trial radius + gid) out of the session."""
         return self.sess.download_rows_tagged(self.n_own, NCOL, self.gid)
@@ -401,8 +421,7 @@ class DistributedSession(object):
             self.sess.cover_check(lo, hi)                          # [ball leaves the covered region, largest h] on the device
             if self._cover is None:
                 self._cover = self.sess.buffer_tensor("cover")
-            dist.all_reduce(self._cover, op=dist.ReduceOp.MAX, group=self.group)    # one collective, one host sync
-            bad, self.hmax = self._cover.tolist()
+            bad, self.hmax = self._reduce_buffer(self._cover, dist.ReduceOp.MAX).tolist()   # one collective, one host sync
             if bad == 0:
                 break
             redo += 1
@@ -457,7 +476,7 @@ class DistributedSession(object):
             hist = self._length_hist()                             # histograms are summed over the ranks
             for _ in range(5):                                     # (code_running.py:515-521; d stays on the device)
                 s.phase("length_hist")
-                dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=self.group)
+                self._reduce_buffer(hist, dist.ReduceOp.SUM)
                 s.phase("length_pick")
             s.phase("smooth")
         else:
