@@ -38,6 +38,10 @@ int sphb200_set_option(sphb200_ctx* ctx, const char* name, double value);
  * synchronises the stream and resets it */
 int sphb200_get_counter(sphb200_ctx* ctx, const char* name, int64_t* value_host, void* stream);
 
+/* measurement aid (bench.py roofline): DFMA thread-instructions per second of a register-resident chain on
+ * this GPU, timed with CUDA events (synchronises) */
+int sphb200_fp64_peak(sphb200_ctx* ctx, double* dfma_per_second_host, void* stream);
+
 /* ---- A1: neighbors(points, dist, N_NEIGH)            navier_stokes_cleaned.py:541-552 ---------
  * points (N,3).  Outputs: idx (N,k) int64 ascending distance, self first, missing = N;
  * dists (N,k) (missing = 0); nontriv (N) int64; new_sizes (N) = row max of dists.
@@ -100,6 +104,10 @@ int sphb200_net_impulse(sphb200_ctx* ctx, int64_t n, int k, const int64_t* neigh
  * ((N,k) int64 rows in the caller's indices, N = missing): the list a checkpoint saved, so that the next
  * step's crossing time (code_running.py:222) sees the same rows as the uninterrupted run. */
 int sphb200_session_create(sphb200_ctx* ctx, int64_t n, int k, double dist);
+/* A context holds at most one session: create fails while one is live.  The function-level calls above
+ * (A1-A9, F1) share the context's scratch buffers with it and are refused on a context with a live
+ * session - give them a context of their own.  destroy ends the session (sphb200_destroy does it too). */
+int sphb200_session_destroy(sphb200_ctx* ctx);
 /* same run, new particle set of n particles (the first n_owned are owned, the rest ghosts; -1 = all owned):
  * keeps k, dist, run parameters and device scalars; fill the arrays with sphb200_session_upload_rows */
 int sphb200_session_resize(sphb200_ctx* ctx, int64_t n, int64_t n_owned, void* stream);
@@ -150,6 +158,11 @@ int sphb200_session_startup(sphb200_ctx* ctx, void* stream);
 /* one pass of the while-body, code_running.py:217-540 (gas/dust only, gravity and chemistry zero; drag as
  * set by sphb200_session_set_drag, off by default) */
 int sphb200_session_step(sphb200_ctx* ctx, void* stream);
+/* Synthetic motion for the measured workloads and the moving-particle parity tests (the reference has no
+ * counterpart: its own step cannot displace particles by a sizeable fraction of h and stay finite, DESIGN.md
+ * section 2): points[i] += amplitude * u(id_i, seed), u uniform in [-1,1)^3, a pure function of the particle's
+ * caller index and the seed (host mirror: sph-code_b200/ics.py perturbation()).  Ghosts are left alone. */
+int sphb200_session_perturb(sphb200_ctx* ctx, double amplitude, uint64_t seed, void* stream);
 /* device pointer + element count of an internal array a caller-side collective works on in place:
  * "cover": float64 [bad, hmax] of sphb200_session_cover_check;
  * "length_hist": int64 histogram of the percentile's radix select (code_running.py:515-518), valid between

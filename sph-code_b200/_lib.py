@@ -23,6 +23,7 @@ SIGNATURES = {
     "sphb200_set_constants": [c_ptr, c_dbl, c_dbl, c_dbl, c_dbl],
     "sphb200_set_option": [c_ptr, ctypes.c_char_p, c_dbl],
     "sphb200_get_counter": [c_ptr, ctypes.c_char_p, ctypes.POINTER(c_i64), c_ptr],
+    "sphb200_fp64_peak": [c_ptr, ctypes.POINTER(c_dbl), c_ptr],
     "sphb200_neighbors": [c_ptr, c_ptr, c_i64, c_int, c_dbl, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
     "sphb200_hydro_update": [c_ptr, c_i64, c_int] + [c_ptr] * 5 + [c_int] + [c_ptr] * 5 + [c_ptr] * 7 + [c_ptr],
     "sphb200_crossing_time": [c_ptr, c_i64, c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_dbl, ctypes.POINTER(c_dbl), c_ptr],
@@ -31,6 +32,7 @@ SIGNATURES = {
     "sphb200_artificial_viscosity": [c_ptr, c_i64, c_int] + [c_ptr] * 10 + [c_dbl, c_ptr, c_ptr, c_ptr],
     "sphb200_net_impulse": [c_ptr, c_i64, c_int] + [c_ptr] * 7 + [c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
     "sphb200_session_create": [c_ptr, c_i64, c_int, c_dbl],
+    "sphb200_session_destroy": [c_ptr],
     "sphb200_session_resize": [c_ptr, c_i64, c_i64, c_ptr],
     "sphb200_session_append_rows": [c_ptr, c_ptr, c_i64, c_int, c_ptr],
     "sphb200_session_download_rows_tagged": [c_ptr, c_ptr, c_i64, c_int, c_ptr, c_ptr],
@@ -46,6 +48,7 @@ SIGNATURES = {
     "sphb200_session_upload_rows": [c_ptr, c_ptr, c_i64, c_int, c_ptr],
     "sphb200_session_startup": [c_ptr, c_ptr],
     "sphb200_session_step": [c_ptr, c_ptr],
+    "sphb200_session_perturb": [c_ptr, c_dbl, ctypes.c_uint64, c_ptr],
     "sphb200_session_scalar": [c_ptr, ctypes.c_char_p, ctypes.POINTER(c_dbl), c_ptr],
     "sphb200_session_set_scalar": [c_ptr, ctypes.c_char_p, c_dbl],
     "sphb200_session_phase": [c_ptr, ctypes.c_char_p, c_ptr],

@@ -8,6 +8,13 @@ thread_local char g_sphb200_err[SPHB200_MAX_ERR] = {0};
 
 static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
+// The function-level calls use the context's scratch buffers (neighbour list, records, cell list) that a live
+// session also owns: interleaving them would silently corrupt the run, so it is refused.
+static int check_no_session(sphb200_ctx* ctx, const char* who) {
+  if (ctx && ctx->session) SPH_FAIL("%s: this context holds a live session; call the function-level API on another context", who);
+  return 0;
+}
+
 static int check_nk(int64_t n, int k) {
   if (n <= 0) SPH_FAIL("empty particle set (N=%lld)", (long long)n);
   if (n >= (int64_t)0x7fffffff) SPH_FAIL("N=%lld exceeds 2^31-1 particles per GPU", (long long)n);
@@ -32,12 +39,14 @@ int sphb200_create(sphb200_ctx** out, int device) {
   sphb200_ctx* ctx = new (std::nothrow) sphb200_ctx();
   if (!ctx) SPH_FAIL("sphb200_create: out of host memory");
   ctx->device = device;
-  if (devbuf_reserve(ctx->flags, FL_COUNT * sizeof(int)) || devbuf_reserve(ctx->scal, SC_COUNT * sizeof(double))) {
+  if (devbuf_reserve(ctx->flags, FL_COUNT * sizeof(int)) || devbuf_reserve(ctx->scal, SC_COUNT * sizeof(double)) ||
+      cudaMemset(ctx->flags.p, 0, FL_COUNT * sizeof(int)) != cudaSuccess ||
+      cudaMemset(ctx->scal.p, 0, SC_COUNT * sizeof(double)) != cudaSuccess) {
+    if (!g_sphb200_err[0]) snprintf(g_sphb200_err, SPHB200_MAX_ERR, "sphb200_create: clearing the device scalars failed");
+    devbuf_free(ctx->flags); devbuf_free(ctx->scal);
     delete ctx;
     return 1;
   }
-  CUDA_TRY(cudaMemset(ctx->flags.p, 0, FL_COUNT * sizeof(int)));
-  CUDA_TRY(cudaMemset(ctx->scal.p, 0, SC_COUNT * sizeof(double)));
   *out = ctx;
   return 0;
 }
@@ -45,6 +54,7 @@ int sphb200_create(sphb200_ctx** out, int device) {
 int sphb200_destroy(sphb200_ctx* ctx) {
   if (!ctx) return 0;
   cudaSetDevice(ctx->device);
+  session_free(ctx);
   DevBuf* all[] = {&ctx->r0, &ctx->r1, &ctx->r2, &ctx->r3, &ctx->rho, &ctx->pi_, &ctx->aux, &ctx->list, &ctx->keys,
                    &ctx->keys_alt, &ctx->perm, &ctx->perm_alt, &ctx->cell_start, &ctx->cub_tmp, &ctx->scal, &ctx->flags, &ctx->worklist, &ctx->soa,
                    &ctx->tmp0, &ctx->tmp1, &ctx->tmp2, &ctx->tmp3};
@@ -108,10 +118,53 @@ int sphb200_get_counter(sphb200_ctx* ctx, const char* name, int64_t* value_host,
   SPH_FAIL("unknown counter '%s'", name);
 }
 
+// ---- fp64 pipe rate (roofline denominator of the pair passes) ---------------------------------------
+__global__ void __launch_bounds__(512) fp64_chain_kernel(int iters, double seed, double* out) {
+  double a0 = seed + threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+  const double m = 1.0000001, c = 1e-9;
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+      a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+    }
+  }
+  const double r = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+  if (r == 12345.678) out[0] = r;                  // never true: keeps the chain alive
+}
+
+int sphb200_fp64_peak(sphb200_ctx* ctx, double* dfma_per_second_host, void* stream) {
+  if (!ctx || !dfma_per_second_host) SPH_FAIL("sphb200_fp64_peak: null argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  cudaStream_t st = as_stream(stream);
+  cudaEvent_t e0, e1;
+  CUDA_TRY(cudaEventCreate(&e0));
+  CUDA_TRY(cudaEventCreate(&e1));
+  const int blocks = 148 * 4, threads = 512, iters = 2048;
+  double* out = bufp<double>(ctx->scal) + SC_COUNT - 1;
+  fp64_chain_kernel<<<blocks, threads, 0, st>>>(64, 1.0, out);             // warm-up
+  float best = 1e30f;
+  for (int rep = 0; rep < 3; ++rep) {
+    CUDA_TRY(cudaEventRecord(e0, st));
+    fp64_chain_kernel<<<blocks, threads, 0, st>>>(iters, 1.0, out);
+    CUDA_TRY(cudaEventRecord(e1, st));
+    CUDA_TRY(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+    if (ms < best) best = ms;
+  }
+  ctx->launches += 4;
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  CUDA_TRY(cudaGetLastError());
+  *dfma_per_second_host = (double)blocks * threads * iters * 64.0 / ((double)best * 1e-3);
+  return 0;
+}
+
 // ---- A1 ----------------------------------------------------------------------------------------
 int sphb200_neighbors(sphb200_ctx* ctx, const double* points, int64_t n, int k, double dist, int64_t* idx,
                       double* dists, int64_t* nontriv, double* new_sizes, void* stream) {
   if (!ctx || !points || !idx || !dists || !nontriv || !new_sizes) SPH_FAIL("sphb200_neighbors: null argument");
+  SPH_TRY(check_no_session(ctx, "sphb200_neighbors"));
   SPH_TRY(check_nk(n, k));
   CUDA_TRY(cudaSetDevice(ctx->device));
   cudaStream_t st = as_stream(stream);
@@ -146,6 +199,7 @@ int sphb200_hydro_update(sphb200_ctx* ctx, int64_t n, int k, const int64_t* neig
   if (!ctx || !neighbor || !points || !mass || !sizes || !particle_type || !T || !mu_array || !gamma_array ||
       !velocities || !hydro_accel || !visc_accel || !visc_heat || !density || !num_density || !dust_density)
     SPH_FAIL("sphb200_hydro_update: null argument");
+  SPH_TRY(check_no_session(ctx, "sphb200_hydro_update"));
   SPH_TRY(check_nk(n, k));
   CUDA_TRY(cudaSetDevice(ctx->device));
   cudaStream_t st = as_stream(stream);
@@ -166,6 +220,7 @@ int sphb200_crossing_time(sphb200_ctx* ctx, int64_t n, int k, const int64_t* nei
                           const double* sizes, const double* particle_type, double dt_0, double* result_host,
                           void* stream) {
   if (!ctx || !neighbor || !velocities || !sizes || !particle_type || !result_host) SPH_FAIL("sphb200_crossing_time: null argument");
+  SPH_TRY(check_no_session(ctx, "sphb200_crossing_time"));
   SPH_TRY(check_nk(n, k));
   CUDA_TRY(cudaSetDevice(ctx->device));
   cudaStream_t st = as_stream(stream);
@@ -185,6 +240,7 @@ int sphb200_loop_density(sphb200_ctx* ctx, int mode, int64_t n, int k, const int
   if (mode < 0 || mode > 2) SPH_FAIL("sphb200_loop_density: mode %d", mode);
   if ((mode == 0 && !particle_type) || (mode == 1 && (!particle_type || !sizes)) || (mode == 2 && !mu_array))
     SPH_FAIL("sphb200_loop_density: missing array for mode %d", mode);
+  SPH_TRY(check_no_session(ctx, "sphb200_loop_density"));
   SPH_TRY(check_nk(n, k));
   CUDA_TRY(cudaSetDevice(ctx->device));
   cudaStream_t st = as_stream(stream);
@@ -199,6 +255,7 @@ int sphb200_del_pressure(sphb200_ctx* ctx, int64_t n, int k, const int64_t* neig
                          const double* gamma_array, double d, double* grad_pressure, void* stream) {
   if (!ctx || !neighbor || !points || !mass || !particle_type || !E_internal || !gamma_array || !grad_pressure)
     SPH_FAIL("sphb200_del_pressure: null argument");
+  SPH_TRY(check_no_session(ctx, "sphb200_del_pressure"));
   SPH_TRY(check_nk(n, k));
   CUDA_TRY(cudaSetDevice(ctx->device));
   cudaStream_t st = as_stream(stream);
@@ -217,6 +274,7 @@ int sphb200_artificial_viscosity(sphb200_ctx* ctx, int64_t n, int k, const int64
       !mu_array || !visc_accel || !visc_heat)
     SPH_FAIL("sphb200_artificial_viscosity: null argument");
   (void)sizes;   // accepted and unused, as in the reference (nsc:788)
+  SPH_TRY(check_no_session(ctx, "sphb200_artificial_viscosity"));
   SPH_TRY(check_nk(n, k));
   CUDA_TRY(cudaSetDevice(ctx->device));
   cudaStream_t st = as_stream(stream);
@@ -237,6 +295,7 @@ int sphb200_net_impulse(sphb200_ctx* ctx, int64_t n, int k, const int64_t* neigh
     SPH_FAIL("sphb200_net_impulse: null argument");
   if (n_species <= 0 || n_species > SPHB200_MAX_SPECIES)
     SPH_FAIL("sphb200_net_impulse: n_species=%d outside 1..%d", n_species, SPHB200_MAX_SPECIES);
+  SPH_TRY(check_no_session(ctx, "sphb200_net_impulse"));
   SPH_TRY(check_nk(n, k));
   CUDA_TRY(cudaSetDevice(ctx->device));
   cudaStream_t st = as_stream(stream);

@@ -98,6 +98,7 @@ struct sphb200_ctx {
   const uint32_t* skip_id = nullptr;
   int skip_from = 0;
   int64_t launches = 0;            // kernels launched through this context (for bench "gpu_launches")
+  void* session = nullptr;         // the device-resident run this context holds (session.cu), or nullptr
 };
 
 int devbuf_reserve(DevBuf& b, size_t bytes);

@@ -5,6 +5,9 @@
 // cells.cu
 int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint, cudaStream_t st);
 
+// session.cu
+void session_free(sphb200_ctx* ctx);
+
 // knn.cu
 int knn_cap_for(int k);
 int launch_knn(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, int32_t* list, double* dists,

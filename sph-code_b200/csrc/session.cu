@@ -8,6 +8,7 @@
 #include <cub/cub.cuh>
 #include <float.h>
 #include <math.h>
+#include <new>
 
 enum Field { F_POS = 0, F_VEL, F_ACC, F_MASS, F_H, F_T, F_E, F_MU, F_GAMMA, F_TYPE, F_RHO0, F_NFIELDS };
 static const int kFieldWidth[F_NFIELDS] = {3, 3, 3, 1, 1, 1, 1, 1, 1, 1, 1};
@@ -51,9 +52,13 @@ struct Session {
   int64_t n_owned = -1;      // slab decomposition: caller indices >= n_owned are ghosts (-1: none)
   SessionScalars sc;
 };
-static Session g_sess[16];   // one per device
-
-static Session& sess(sphb200_ctx* ctx) { return g_sess[ctx->device & 15]; }
+// The session belongs to its context (ctx->session): two contexts on one GPU are two independent runs.
+static Session g_no_session;   // k == 0: what the entry points see before sphb200_session_create
+static Session& sess(sphb200_ctx* ctx) { return ctx->session ? *static_cast<Session*>(ctx->session) : g_no_session; }
+void session_free(sphb200_ctx* ctx) {
+  delete static_cast<Session*>(ctx->session);
+  ctx->session = nullptr;
+}
 static double* fld(sphb200_ctx* ctx, int f, int alt = 0) {
   Session& s = sess(ctx);
   return bufp<double>(ctx->sbuf[2 * f + (s.cur[f] ^ alt)]);
@@ -485,6 +490,30 @@ rows_in_kernel(int n, int ncol, const uint32_t* __restrict__ id, const double* _
   }
 }
 
+// ---- synthetic motion (bench.py / tests): x += amplitude * u(id, seed), u uniform in [-1,1)^3 ----
+// The reference's own step cannot move particles by a sizeable fraction of h and stay finite (DESIGN.md
+// "Stability of the reference step"), so the measured workloads displace every owned particle between
+// steps instead.  The displacement is a pure function of (particle id, seed): identical for any domain
+// decomposition and reproducible on the host (ics.perturbation).  Separately rounded product and sum, so
+// the host mirror is bit-identical.
+__host__ __device__ __forceinline__ double perturb_unit(unsigned long long g, int c, unsigned long long seed) {
+  unsigned long long z = (g * 3ull + (unsigned long long)c + 1ull) * 0x9E3779B97F4A7C15ull + seed * 0xBF58476D1CE4E5B9ull;
+  z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ull;
+  z ^= z >> 27; z *= 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  return (double)(z >> 11) * (1.0 / 4503599627370496.0) - 1.0;      // (z >> 11) 2^-52 - 1, exact
+}
+__global__ void __launch_bounds__(256)
+perturb_kernel(int n, const uint32_t* __restrict__ id, int n_owned, double amp, unsigned long long seed, double* __restrict__ pos) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t g = id[i];
+  if (n_owned >= 0 && (int)g >= n_owned) return;                     // ghosts follow their owners
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+    pos[3 * (int64_t)i + c] = __dadd_rn(pos[3 * (int64_t)i + c], __dmul_rn(amp, perturb_unit(g, c, seed)));
+}
+
 // ------------------------------------------------------------------------------------------------
 static int phase_crossing(sphb200_ctx* ctx, cudaStream_t st) {
   Session& s = sess(ctx);
@@ -684,8 +713,11 @@ int sphb200_session_create(sphb200_ctx* ctx, int64_t n, int k, double dist) {
   if (n <= 0 || n >= (int64_t)0x7fffffff) SPH_FAIL("session: bad particle count %lld", (long long)n);
   if (k <= 0) SPH_FAIL("session: bad k=%d", k);
   CUDA_TRY(cudaSetDevice(ctx->device));
+  if (ctx->session) SPH_FAIL("session_create: this context already holds a live session of %lld particles; destroy it "
+                             "(sphb200_session_destroy) or use another context", (long long)sess(ctx).n);
+  ctx->session = new (std::nothrow) Session();
+  if (!ctx->session) SPH_FAIL("session_create: out of host memory");
   Session& s = sess(ctx);
-  s = Session();
   s.n = n; s.k = k; s.dist = dist;
   s.sc.dt_0 = 60. * 60. * 24. * 365. * 250000.;
   s.sc.max_age = 3e7 * 60. * 60. * 24. * 365.;
@@ -712,6 +744,12 @@ int sphb200_session_create(sphb200_ctx* ctx, int64_t n, int k, double dist) {
   return 0;
 }
 
+int sphb200_session_destroy(sphb200_ctx* ctx) {
+  if (!ctx) SPH_FAIL("null context");
+  session_free(ctx);
+  return 0;
+}
+
 // Same run, different particle set: the slab decomposition rebuilds its local set (owned + ghosts)
 // every step.  Keeps k, dist, the run parameters and the device scalars (age, dt, ct, d); the state
 // arrays are to be filled by sphb200_session_upload_rows (nothing is cleared, nothing synchronises).
@@ -719,6 +757,7 @@ int sphb200_session_resize(sphb200_ctx* ctx, int64_t n, int64_t n_owned, void* s
   if (!ctx) SPH_FAIL("null context");
   if (n <= 0 || n >= (int64_t)0x7fffffff) SPH_FAIL("session_resize: bad particle count %lld", (long long)n);
   CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   Session& s = sess(ctx);
   if (s.k <= 0) SPH_FAIL("session_resize: no session to resize");
@@ -776,6 +815,7 @@ list_in_kernel(int n, int k, const uint32_t* __restrict__ id, const uint32_t* __
 int sphb200_session_upload(sphb200_ctx* ctx, const char* name, const void* src, int64_t count, void* stream) {
   if (!ctx || !name || !src) SPH_FAIL("session_upload: null argument");
   CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   Session& s = sess(ctx);
   const int sc = find_scalar(name);
@@ -819,6 +859,7 @@ int sphb200_session_upload(sphb200_ctx* ctx, const char* name, const void* src, 
 int sphb200_session_download(sphb200_ctx* ctx, const char* name, void* dst, int64_t count, void* stream) {
   if (!ctx || !name || !dst) SPH_FAIL("session_download: null argument");
   CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   Session& s = sess(ctx);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const uint32_t* id = bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]);
@@ -886,12 +927,14 @@ static int field_at(sphb200_ctx* ctx, const char* name, const int64_t* idx, int6
 int sphb200_session_gather(sphb200_ctx* ctx, const char* field, const int64_t* idx, int64_t count, double* out, void* stream) {
   if (!ctx || !field || (count > 0 && (!idx || !out))) SPH_FAIL("session_gather: null argument");
   CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   return field_at(ctx, field, idx, count, out, false, reinterpret_cast<cudaStream_t>(stream));
 }
 // field at caller indices idx <- in (count, w)
 int sphb200_session_scatter(sphb200_ctx* ctx, const char* field, const int64_t* idx, int64_t count, const double* in, void* stream) {
   if (!ctx || !field || (count > 0 && (!idx || !in))) SPH_FAIL("session_scatter: null argument");
   CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   return field_at(ctx, field, idx, count, const_cast<double*>(in), true, reinterpret_cast<cudaStream_t>(stream));
 }
 
@@ -910,6 +953,7 @@ int sphb200_session_download_rows_tagged(sphb200_ctx* ctx, double* rows, int64_t
 static int download_rows_impl(sphb200_ctx* ctx, double* rows, int64_t n_rows, int ncol, const double* tag, void* stream) {
   if (!ctx || !rows) SPH_FAIL("session_download_rows: null argument");
   CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   Session& s = sess(ctx);
   if (ncol < ROW_STATE_COLS || n_rows < 0 || n_rows > s.n) SPH_FAIL("session_download_rows: bad shape (%lld, %d)", (long long)n_rows, ncol);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
@@ -927,6 +971,7 @@ static int download_rows_impl(sphb200_ctx* ctx, double* rows, int64_t n_rows, in
 int sphb200_session_upload_rows_at(sphb200_ctx* ctx, const double* rows, int64_t first, int64_t n_rows, int ncol, void* stream) {
   if (!ctx || (!rows && n_rows > 0)) SPH_FAIL("session_upload_rows: null argument");
   CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   Session& s = sess(ctx);
   if (ncol < ROW_STATE_COLS || first < 0 || n_rows < 0 || first + n_rows > s.n)
     SPH_FAIL("session_upload_rows: rows [%lld, %lld) x %d do not fit %lld particles x >= 18 columns", (long long)first,
@@ -945,6 +990,7 @@ int sphb200_session_upload_rows_at(sphb200_ctx* ctx, const double* rows, int64_t
 
 int sphb200_session_upload_rows(sphb200_ctx* ctx, const double* rows, int64_t n_rows, int ncol, void* stream) {
   if (!ctx) SPH_FAIL("null context");
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   if (n_rows != sess(ctx).n) SPH_FAIL("session_upload_rows: needs all %lld rows, got %lld", (long long)sess(ctx).n, (long long)n_rows);
   return sphb200_session_upload_rows_at(ctx, rows, 0, n_rows, ncol, stream);
 }
@@ -970,6 +1016,7 @@ static int devbuf_grow(DevBuf& b, size_t keep, size_t bytes, cudaStream_t st) {
 int sphb200_session_append_rows(sphb200_ctx* ctx, const double* rows, int64_t n_new, int ncol, void* stream) {
   if (!ctx || (!rows && n_new > 0)) SPH_FAIL("session_append_rows: null argument");
   CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   Session& s = sess(ctx);
   if (s.k <= 0) SPH_FAIL("session_append_rows: no session");
   if (n_new < 0 || ncol < ROW_STATE_COLS) SPH_FAIL("session_append_rows: needs (n_new >= 0, ncol >= 18), got (%lld, %d)", (long long)n_new, ncol);
@@ -1006,6 +1053,7 @@ int sphb200_session_append_rows(sphb200_ctx* ctx, const double* rows, int64_t n_
 int sphb200_session_set_scalar(sphb200_ctx* ctx, const char* name, double value) {
   if (!ctx || !name) SPH_FAIL("null argument");
   CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   Session& s = sess(ctx);
   double* scal = bufp<double>(ctx->scal);
   if (!strcmp(name, "dt_0")) s.sc.dt_0 = value;
@@ -1027,6 +1075,7 @@ int sphb200_session_set_scalar(sphb200_ctx* ctx, const char* name, double value)
 int sphb200_session_scalar(sphb200_ctx* ctx, const char* name, double* out, void* stream) {
   if (!ctx || !name || !out) SPH_FAIL("null argument");
   CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   int which = -1;
   if (!strcmp(name, "ct")) which = SC_CT;
@@ -1045,6 +1094,7 @@ int sphb200_session_scalar(sphb200_ctx* ctx, const char* name, double* out, void
 int sphb200_session_startup(sphb200_ctx* ctx, void* stream) {
   if (!ctx) SPH_FAIL("null context");
   CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   Session& s = sess(ctx);
   SPH_TRY(phase_sort(ctx, st));
@@ -1064,6 +1114,7 @@ int sphb200_session_set_drag(sphb200_ctx* ctx, const void* f_un, int n_species, 
                              const double* sigma_effective_host, void* stream) {
   if (!ctx) SPH_FAIL("null context");
   CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   Session& s = sess(ctx);
   if (s.k <= 0) SPH_FAIL("session_set_drag: no session");
   if (!f_un) { s.drag = 0; return 0; }
@@ -1106,6 +1157,7 @@ cover_check_kernel(int n, const double* __restrict__ pos, const double* __restri
 int sphb200_session_cover_check(sphb200_ctx* ctx, double lo, double hi, void* stream) {
   if (!ctx) SPH_FAIL("null context");
   CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   Session& s = sess(ctx);
   if (s.k <= 0) SPH_FAIL("session_cover_check: no session");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
@@ -1125,6 +1177,7 @@ int sphb200_session_cover_check(sphb200_ctx* ctx, double lo, double hi, void* st
 int sphb200_session_buffer(sphb200_ctx* ctx, const char* name, void** ptr, int64_t* count) {
   if (!ctx || !name || !ptr || !count) SPH_FAIL("session_buffer: null argument");
   CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   if (!strcmp(name, "length_hist")) {
     SPH_TRY(devbuf_reserve(ctx->sbuf[SB_SEL], (SEL_HIST + 8) * sizeof(long long) + sizeof(SelectState)));
     *ptr = sel_hist(ctx);
@@ -1139,9 +1192,23 @@ int sphb200_session_buffer(sphb200_ctx* ctx, const char* name, void** ptr, int64
   SPH_FAIL("session_buffer: unknown buffer '%s'", name);
 }
 
+int sphb200_session_perturb(sphb200_ctx* ctx, double amplitude, uint64_t seed, void* stream) {
+  if (!ctx) SPH_FAIL("null context");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
+  Session& s = sess(ctx);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  perturb_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]), (int)s.n_owned,
+                                                     amplitude, (unsigned long long)seed, fld(ctx, F_POS));
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
 int sphb200_session_step(sphb200_ctx* ctx, void* stream) {
   if (!ctx) SPH_FAIL("null context");
   CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   SkipGhosts skip(ctx);
   SPH_TRY(phase_crossing(ctx, st));
@@ -1160,6 +1227,7 @@ int sphb200_session_step(sphb200_ctx* ctx, void* stream) {
 int sphb200_session_phase(sphb200_ctx* ctx, const char* phase, void* stream) {
   if (!ctx || !phase) SPH_FAIL("null argument");
   CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   SkipGhosts skip(ctx);
   if (!strcmp(phase, "crossing")) return phase_crossing(ctx, st);

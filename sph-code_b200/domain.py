@@ -107,6 +107,7 @@ class SlabExchange(object):
         send_list[self.rank] = 0
         recv_list[self.rank] = 0
         n_out = sum(send_list)
+        self.last_migrated = n_out
         if sum(table[a][b] for a in range(self.world) for b in range(self.world) if a != b) == 0:
             return rows                                                # nobody moves anywhere: no second collective
         stay = dest == self.rank
@@ -335,6 +336,19 @@ class DistributedSession(object):
         rows = rows_from_state(st, gid=np.arange(n_per_rank) + rank * n_per_rank)
         return cls(torch.from_numpy(rows), bounds, k, st["dist"], C.dt_0 * dt_scale, device, group=group)
 
+    @classmethod
+    def synthetic(cls, kind, n, seed, k, dt_scale, device, scaling="weak", group=None):
+        """bench.py's workloads.  weak + uniform: `uniform_slabs` (n per rank, every rank draws its own slab);
+        strong (or clustered at sizes one host can draw): every rank draws the same n particles and keeps its
+        equal-count slab."""
+        from . import constants as C, ics
+        if kind == "uniform" and scaling == "weak":
+            return cls.uniform_slabs(int(n), seed, k, dt_scale, device, group=group)
+        world = dist.get_world_size(group)
+        n_total = int(n) * (world if scaling == "weak" else 1)
+        st = ics.uniform_box(n_total, seed) if kind == "uniform" else ics.clustered_cloud(n_total, seed)
+        return cls.from_global_state(st, device, dt_0=C.dt_0 * dt_scale, group=group)
+
     # -- small collectives --------------------------------------------------------------------
     def _allreduce(self, value, op):
         t = torch.tensor([value], dtype=torch.float64, device=self.device)
@@ -455,6 +469,7 @@ class DistributedSession(object):
             s.phase("dt_clamp")
         elif name == "exchange":
             rows = self.ex.migrate(self._owned_rows())
+            self.migrated = getattr(self, "migrated", 0) + int(getattr(self.ex, "last_migrated", 0))
             self._open_session(rows, 1.25 * self.hmax)
         elif name == "sort":
             pass                                                  # part of "knn" here (the search may be redone)
@@ -486,6 +501,75 @@ class DistributedSession(object):
         for ph in self.PHASES:
             self.phase(ph)
 
+    def perturb(self, amplitude, seed):
+        """Session.perturb for slabs: the displacement is a function of the particle's GLOBAL id, so every
+        decomposition moves every particle identically (ics.perturbation is the host mirror)."""
+        g = self.gid[:self.n_own].to(torch.int64)
+        M = (1 << 64) - 1
+
+        def c64(v):                                               # uint64 constant as the int64 with the same bits
+            v &= M
+            return v - (1 << 64) if v >= (1 << 63) else v
+
+        def shr(z, b):                                            # logical shift right on int64 bit patterns
+            return (z >> b) & ((1 << (64 - b)) - 1)
+        cols = []
+        for c in range(3):
+            z = (g * 3 + (c + 1)) * c64(0x9E3779B97F4A7C15) + c64(int(seed) * 0xBF58476D1CE4E5B9)
+            z = z ^ shr(z, 30); z = z * c64(0xBF58476D1CE4E5B9)
+            z = z ^ shr(z, 27); z = z * c64(0x94D049BB133111EB)
+            z = z ^ shr(z, 31)
+            cols.append(shr(z, 11).to(torch.float64) * (1.0 / 4503599627370496.0) - 1.0)
+        disp = torch.stack(cols, dim=1) * float(amplitude)
+        idx = torch.arange(self.n_own, dtype=torch.int64, device=self.device)
+        self.sess.scatter("points", idx, self.sess.gather("points", idx) + disp)
+
+    def counters(self, reset=True):
+        c = self.sess.counters(reset)
+        c["halo_redo"] = self.halo_redo
+        c["migrated"] = getattr(self, "migrated", 0)
+        if reset:
+            self.halo_redo = 0
+            self.migrated = 0
+        return c
+
+    def median_h(self):
+        """Median smoothing length over ALL ranks' owned particles (approximated by the mean of the ranks' medians)."""
+        m = self.sess.download_tensor("sizes")[:self.n_own].median().reshape(1)
+        dist.all_reduce(m, op=dist.ReduceOp.SUM, group=self.group)
+        return float(m.item()) / dist.get_world_size(self.group)
+
+    def fp64_peak(self):
+        return self.sess.fp64_peak()
+
+    def close(self):
+        if self.sess is not None:
+            self.sess.close()
+            self.sess = None
+
+    def gather_neighbor_ids(self):
+        """(N_total, k) neighbour rows as GLOBAL particle ids, ordered by global id, on every rank (tests / verify)."""
+        nb = self.sess.download_tensor("neighbor")[:self.n_own]
+        g_all = torch.cat([self.gid.to(torch.int64), torch.full((1,), -1, dtype=torch.int64, device=self.device)])
+        rows = g_all[nb.clamp(max=self.sess.n)]                    # index n = missing neighbour -> -1
+        gid = self.gid[:self.n_own].to(torch.int64)
+        world = dist.get_world_size(self.group)
+        counts = [None] * world
+        dist.all_gather_object(counts, int(gid.numel()), group=self.group)
+        nmax = max(counts)
+        pad_g = torch.full((nmax,), -1, dtype=torch.int64, device=self.device); pad_g[:gid.numel()] = gid
+        pad_r = torch.full((nmax, rows.shape[1]), -1, dtype=torch.int64, device=self.device); pad_r[:gid.numel()] = rows
+        gs = [torch.empty_like(pad_g) for _ in range(world)]
+        rs = [torch.empty_like(pad_r) for _ in range(world)]
+        dist.all_gather(gs, pad_g, group=self.group)
+        dist.all_gather(rs, pad_r, group=self.group)
+        g = torch.cat([gs[r][:counts[r]] for r in range(world)])
+        v = torch.cat([rs[r][:counts[r]] for r in range(world)])
+        out = torch.empty_like(v)
+        out[g] = v
+        out[out < 0] = self.n_total
+        return out.cpu().numpy()
+
     # -- the Session interface bench.py and the tests use ---------------------------------------
     def phases(self):
         return self.PHASES
@@ -511,11 +595,13 @@ class DistributedSession(object):
         return {"buf": buf, "n": int(rows.shape[0]), "h2d_bytes": int(rows.shape[0]) * NCOL * 8,
                 "d2h_bytes": int(rows.shape[0]) * NCOL * 8}
 
-    def step_host(self, hs):
+    def step_host(self, hs, perturb=None):
         """One step of a host-resident slab: the owned rows are uploaded from pinned memory into the
         session, the step runs (with its exchanges), the new owned rows come back to pinned memory."""
         rows = hs["buf"][:hs["n"]].to(self.device, non_blocking=True)
         self.sess.upload_rows_at(rows, 0)                          # ghosts keep their rows (refreshed in the step)
+        if perturb:
+            self.perturb(*perturb)
         self.step()
         out = self._owned_rows()
         if out.shape[0] > hs["buf"].shape[0]:

@@ -87,3 +87,19 @@ def clustered_cloud(n, seed):
     d = (np.percentile(dist_sq, 90) ** 1.5 / n / 0.9 * C.N_INT_PER_PARTICLE) ** (1. / 3.)
     dist = 2. * r[-1]          # no radius cut: every row holds k real neighbours
     return _finish(points, rs, mass, particle_type, d, dist, dict(side=float(2 * r[-1]), kind="clustered"))
+
+
+def perturbation(ids, amplitude, seed):
+    """Host mirror of sphb200_session_perturb: the (len(ids), 3) displacement amplitude * u(id, seed), u uniform
+    in [-1,1)^3 from a splitmix64 hash of (3 id + component, seed).  Bit-identical to the device kernel."""
+    ids = np.asarray(ids, dtype=np.uint64)
+    out = np.empty((len(ids), 3))
+    with np.errstate(over="ignore"):
+        for c in range(3):
+            z = (ids * np.uint64(3) + np.uint64(c + 1)) * np.uint64(0x9E3779B97F4A7C15) \
+                + np.uint64(seed) * np.uint64(0xBF58476D1CE4E5B9)
+            z ^= z >> np.uint64(30); z *= np.uint64(0xBF58476D1CE4E5B9)
+            z ^= z >> np.uint64(27); z *= np.uint64(0x94D049BB133111EB)
+            z ^= z >> np.uint64(31)
+            out[:, c] = (z >> np.uint64(11)).astype(np.float64) * (1.0 / 4503599627370496.0) - 1.0
+    return amplitude * out

@@ -29,7 +29,12 @@ PHASES = ("crossing", "dt_clamp", "sort", "knn", "pack", "density", "pi", "force
 
 class Session(object):
     def __init__(self, n, k=C.N_NEIGH, dist=np.inf, device=None, dt_0=C.dt_0):
-        self.ctx = _lib.context(device)
+        # a context of its own: the session's scratch buffers (neighbour list, records, cell list) are never
+        # shared with the function-level nsc.* calls (they use the process-wide _lib.context()) nor with
+        # another Session on the same GPU
+        if not torch.cuda.is_available():
+            raise _lib.Sphb200Error("no CUDA device visible: sphb200 runs on a B200 only (no CPU fallback)")
+        self.ctx = _lib.Context(torch.cuda.current_device() if device is None else int(device))
         self.lib = _lib.load()
         self.n = int(n)
         self.k = int(k)
@@ -39,6 +44,12 @@ class Session(object):
         for name, val in (("dt_0", dt_0), ("MAX_AGE", C.MAX_AGE), ("N_INT_PER_PARTICLE", C.N_INT_PER_PARTICLE),
                           ("raise_factor", C.raise_factor), ("AU", C.AU)):
             self.set_scalar(name, val)
+
+    def close(self):
+        """Free the session and its context (device buffers)."""
+        if getattr(self, "ctx", None) is not None:
+            self.ctx.close()
+            self.ctx = None
 
     def resize(self, n, n_owned=-1):
         """Same run, new particle set (slab decomposition): keeps scalars and run parameters."""
@@ -221,6 +232,10 @@ class Session(object):
         """One pass of the while-body (code_running.py:217-540), asynchronous on the current stream."""
         _lib.check(self.lib.sphb200_session_step(self.ctx.handle, self._stream()))
 
+    def perturb(self, amplitude, seed):
+        """points += amplitude * u(id, seed) (synthetic motion between steps; ics.perturbation is the host mirror)."""
+        _lib.check(self.lib.sphb200_session_perturb(self.ctx.handle, float(amplitude), int(seed), self._stream()))
+
     def phase(self, name):
         _lib.check(self.lib.sphb200_session_phase(self.ctx.handle, name.encode(), self._stream()))
 
@@ -232,6 +247,25 @@ class Session(object):
 
     def launches(self):
         return self.ctx.counter("launches")
+
+    def counters(self, reset=True):
+        """Statistics of the neighbour searches since the last read: extra scans (stale trial radius), targets
+        handed to the general kernel (k-th neighbour outside the cell block), length of the last work list."""
+        st = self._stream()
+        return {"knn_rescan": self.ctx.counter("knn_rescan", st), "knn_widen": self.ctx.counter("knn_widen", st),
+                "knn_worklist_last": self.ctx.counter("knn_worklist", st)}
+
+    def median_h(self):
+        """Median smoothing length of the current state (device-side; one host sync)."""
+        return float(self.download_tensor("sizes").median().item())
+
+    def fp64_peak(self):
+        """Measured fp64 rate of this GPU (DFMA thread-instructions per second of a register-resident chain):
+        the denominator of the fp64-pipe fractions bench.py reports."""
+        out = ctypes.c_double(0.0)
+        _lib.check(self.lib.sphb200_fp64_peak(self.ctx.handle, ctypes.byref(out), self._stream()))
+        return {"dfma_per_s": float(out.value), "tflops": 2.0 * float(out.value) / 1e12,
+                "how": "sphb200_fp64_peak: 8 independent DFMA chains per thread, 592 CTAs x 512 threads, CUDA events"}
 
     def phases(self):
         return PHASES
@@ -259,7 +293,7 @@ class Session(object):
         hs["overlap"] = set(HOST_EARLY_FIELDS) <= set(upload_fields) and set(HOST_LATE_FIELDS) <= set(upload_fields)
         return hs
 
-    def step_host(self, hs):
+    def step_host(self, hs, perturb=None):
         """One time step of a host-resident state: every input field is copied from pinned memory, the step
         runs, the advanced fields are copied back to pinned memory and become the next step's inputs.
         The copy of the fields that are first read after the neighbour search (72 of the 136 B/particle)
@@ -270,6 +304,8 @@ class Session(object):
         if not hs.get("overlap"):
             for f in hs["upload"]:
                 self.upload_tensor(f, hs["in"][f].to(self.device, non_blocking=True))
+            if perturb:
+                self.perturb(*perturb)
             self.step()
         else:
             cs = hs["copy_stream"]
@@ -284,6 +320,8 @@ class Session(object):
             cur.wait_event(ev_early)
             for f in hs["early"]:
                 self.upload_tensor(f, hs["stage"][f])
+            if perturb:
+                self.perturb(*perturb)                            # synthetic motion (bench / tests), as before step()
             for ph in ("crossing", "dt_clamp", "sort_keys", "knn"):
                 self.phase(ph)
             cur.wait_event(ev_late)

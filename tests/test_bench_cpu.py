@@ -16,8 +16,31 @@ def test_reference_arm_prints_the_contract_line():
     assert line["impl"] == "reference" and line["metric"] == "SPH particle-steps/sec" and line["unit"] == "particle-steps/s"
     assert line["higher_is_better"] is True and line["value"] > 0 and line["steps"] == 1
     assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["value"] == line["value"]
+    assert line["cpu_baseline"]["sample_particles"] == 3000 and line["warmup"] == 0
     assert line["e2e"] == {"value": line["value"], "unit": line["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
-    assert line["config"]["workload"].startswith("uniform box, N=1000000")
+    # the default workload is BASELINE configs[3] (uniform, N = 10^7, seed 3) with moving particles; the CPU arm
+    # times a bounded sample of it and extrapolates with the N log N law
+    assert line["config"]["workload"].startswith("BASELINE configs[3]: uniform box") and "N=10000000" in line["config"]["workload"]
+    assert line["config"]["particles_total"] == 10000000 and line["config"]["move_h_per_step"] == 0.2
+    ex = line["cpu_baseline"]["extrapolated_to_config"]
+    assert ex["particles"] == 10000000 and 0 < ex["value"] < line["value"]
+
+
+def test_workload_names_follow_baseline_configs():
+    sys.path.insert(0, ROOT)
+    import bench
+    class A(object):
+        n = 1e6; kind = "uniform"; scaling = "weak"; move = 0.2
+    assert bench.workload_name(A).startswith("BASELINE configs[1]") and "seed 1" in bench.workload_name(A)
+    A.n = 1e7
+    assert "configs[3]" in bench.workload_name(A) and "seed 3" in bench.workload_name(A)
+    assert "per GPU x 8 GPUs (weak)" in bench.workload_name(A, 8)
+    A.scaling = "strong"
+    assert "split over 4 GPUs (strong)" in bench.workload_name(A, 4)
+    A.kind = "clustered"; A.n = 1.25e7; A.scaling = "weak"
+    assert "configs[4]" in bench.workload_name(A, 8) and "seed 4" in bench.workload_name(A, 8)
+    A.n = 4e6
+    assert "configs[2]" in bench.workload_name(A) and "seed 2" in bench.workload_name(A)
 
 
 def test_reference_arm_other_ranks_exit_quietly():
