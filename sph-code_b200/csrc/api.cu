@@ -55,9 +55,9 @@ int sphb200_destroy(sphb200_ctx* ctx) {
   if (!ctx) return 0;
   cudaSetDevice(ctx->device);
   session_free(ctx);
-  DevBuf* all[] = {&ctx->r0, &ctx->r1, &ctx->r2, &ctx->r3, &ctx->rho, &ctx->pi_, &ctx->aux, &ctx->list, &ctx->keys,
-                   &ctx->keys_alt, &ctx->perm, &ctx->perm_alt, &ctx->cell_start, &ctx->cub_tmp, &ctx->scal, &ctx->flags, &ctx->worklist, &ctx->soa,
-                   &ctx->tmp0, &ctx->tmp1, &ctx->tmp2, &ctx->tmp3};
+  DevBuf* all[] = {&ctx->r0, &ctx->recD, &ctx->recP, &ctx->recK, &ctx->rho, &ctx->pi_, &ctx->aux, &ctx->list, &ctx->list16,
+                   &ctx->keys, &ctx->keys_alt, &ctx->perm, &ctx->perm_alt, &ctx->cell_start, &ctx->scan_tops, &ctx->grid_dev,
+                   &ctx->scal, &ctx->flags, &ctx->worklist, &ctx->tmp0, &ctx->tmp1, &ctx->tmp2, &ctx->tmp3};
   for (DevBuf* b : all) devbuf_free(*b);
   for (DevBuf& b : ctx->sbuf) devbuf_free(b);
   delete ctx;
@@ -168,16 +168,16 @@ int sphb200_neighbors(sphb200_ctx* ctx, const double* points, int64_t n, int k, 
   SPH_TRY(check_nk(n, k));
   CUDA_TRY(cudaSetDevice(ctx->device));
   cudaStream_t st = as_stream(stream);
-  SPH_TRY(build_cells(ctx, points, n, ctx->cell_edge, st));
+  SPH_TRY(build_cells(ctx, points, n, ctx->cell_edge, nullptr, true, st));
   SPH_TRY(devbuf_reserve(ctx->list, (size_t)n * k * sizeof(int32_t)));
   SPH_TRY(devbuf_reserve(ctx->tmp1, (size_t)n * k * sizeof(double)));
   SPH_TRY(devbuf_reserve(ctx->tmp2, (size_t)n * sizeof(double)));
   SPH_TRY(devbuf_reserve(ctx->tmp3, (size_t)n * sizeof(int32_t)));
-  if (ctx->knn_fast && k <= knn_cell_max_k())
-    SPH_TRY(launch_knn_cell(ctx, (int)n, k, dist, nullptr, 0.0, bufp<int32_t>(ctx->list), bufp<double>(ctx->tmp1),
-                            bufp<double>(ctx->tmp2), bufp<int32_t>(ctx->tmp3), st));
+  if (ctx->knn_fast && k <= knn_group_max_k())
+    SPH_TRY(launch_knn_group(ctx, (int)n, k, dist, 0, 0.0, nullptr, bufp<int32_t>(ctx->list), bufp<double>(ctx->tmp1),
+                             bufp<double>(ctx->tmp2), bufp<int32_t>(ctx->tmp3), st));
   else
-    SPH_TRY(launch_knn(ctx, (int)n, k, dist, nullptr, bufp<int32_t>(ctx->list), bufp<double>(ctx->tmp1),
+    SPH_TRY(launch_knn(ctx, (int)n, k, dist, 0, 1.0, bufp<int32_t>(ctx->list), bufp<double>(ctx->tmp1),
                        bufp<double>(ctx->tmp2), bufp<int32_t>(ctx->tmp3), st));
   SPH_TRY(launch_knn_unsort(ctx, bufp<int32_t>(ctx->list), bufp<double>(ctx->tmp1), bufp<double>(ctx->tmp2),
                             bufp<int32_t>(ctx->tmp3), (int)n, k, idx, dists, nontriv, new_sizes, st));
@@ -207,11 +207,12 @@ int sphb200_hydro_update(sphb200_ctx* ctx, int64_t n, int k, const int64_t* neig
   PackIn in = {points, velocities, mass, sizes, particle_type, T, mu_array, gamma_array};
   SPH_TRY(launch_pack(ctx, (int)n, in, st));
   const int32_t* list = bufp<int32_t>(ctx->list);
-  SPH_TRY(launch_density(ctx, (int)n, k, list, density, dust_density, num_density, st));
+  const RowsRef rows = {nullptr, list, nullptr, nullptr};
+  SPH_TRY(launch_density(ctx, (int)n, k, rows, density, dust_density, num_density, st));
   if (f_un && f_un_neighbor && n_species > 0)
     SPH_TRY(launch_species(ctx, (int)n, k, n_species, list, f_un, f_un_neighbor, st));
-  SPH_TRY(launch_pi(ctx, (int)n, k, list, density, st));
-  SPH_TRY(launch_force(ctx, (int)n, k, list, density, mass, hydro_accel, visc_accel, visc_heat, st));
+  SPH_TRY(launch_pi(ctx, (int)n, k, rows, st));
+  SPH_TRY(launch_force(ctx, (int)n, k, rows, mass, hydro_accel, visc_accel, visc_heat, st));
   return 0;
 }
 
@@ -226,7 +227,8 @@ int sphb200_crossing_time(sphb200_ctx* ctx, int64_t n, int k, const int64_t* nei
   cudaStream_t st = as_stream(stream);
   SPH_TRY(prep_list(ctx, neighbor, n, k, st));
   double* out = bufp<double>(ctx->scal) + SC_CT;
-  SPH_TRY(launch_crossing_time(ctx, (int)n, k, bufp<int32_t>(ctx->list), velocities, sizes, particle_type, dt_0, out, nullptr, (int)n, st));
+  const RowsRef rows = {nullptr, bufp<int32_t>(ctx->list), nullptr, nullptr};
+  SPH_TRY(launch_crossing_time(ctx, (int)n, k, rows, velocities, sizes, particle_type, dt_0, out, nullptr, (uint32_t)n, st));
   CUDA_TRY(cudaMemcpyAsync(result_host, out, sizeof(double), cudaMemcpyDeviceToHost, st));
   CUDA_TRY(cudaStreamSynchronize(st));
   return 0;

@@ -1,88 +1,290 @@
-// Cell-list build: bounding box, cell keys + histogram, radix sort of (key, particle) pairs,
-// cell-start scan, gather of positions into sorted {x,y,z,h^2} records.
+// Cell-list build, entirely on the device (no host synchronisation, fixed launch sizes: graph-capturable):
+//   bounding box -> grid choice (one block) -> cell keys + histogram with in-cell ranks -> exclusive scan
+//   -> counting-sort scatter -> in-cell ordering (deterministic) -> sorted position records.
 // Replaces the cKDTree build of /root/reference/sph/navier_stokes_cleaned.py:542.
 #include "common.cuh"
 #include "kernels.cuh"
-#include <cub/cub.cuh>
+#include "tile.cuh"
 #include <float.h>
 #include <math.h>
 
-// ---- ordered-int encoding so that double min/max can use 64-bit integer atomics ----
-__device__ __forceinline__ long long dbl_to_ordered(double v) {
-  long long b = __double_as_longlong(v);
-  return b >= 0 ? b : (b ^ 0x7fffffffffffffffLL);
-}
-__device__ __forceinline__ double ordered_to_dbl(long long b) {
-  return __longlong_as_double(b >= 0 ? b : (b ^ 0x7fffffffffffffffLL));
-}
+#define BB_BLOCKS (148 * 4)
+#define SCAN_TILE 2048             // elements per block of the scan (256 threads x 8)
 
-__global__ void bbox_init_kernel(long long* bb) {
-  int t = threadIdx.x;
-  if (t < 3) bb[t] = dbl_to_ordered(DBL_MAX);
-  else if (t < 6) bb[t] = dbl_to_ordered(-DBL_MAX);
-}
-
-// points: (N,3) row-major.  Non-finite coordinates are ignored (they land in a border cell).
-__global__ void __launch_bounds__(256) bbox_kernel(const double* __restrict__ pts, int64_t n, long long* bb) {
+// ---- bounding box: per-block partial min/max of the finite coordinates ----
+__global__ void __launch_bounds__(256) bbox_partial_kernel(const double* __restrict__ pts, int64_t n, double* __restrict__ part) {
   double lo[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, hi[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
-      double v = pts[3 * i + a];
+      const double v = pts[3 * i + a];
       if (isfinite(v)) { lo[a] = fmin(lo[a], v); hi[a] = fmax(hi[a], v); }
     }
   }
-  typedef cub::BlockReduce<double, 256> BR;
-  __shared__ typename BR::TempStorage tmp;
+  __shared__ double sh[8][6];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
-    double l = BR(tmp).Reduce(lo[a], cub::Min());
-    __syncthreads();
-    double h = BR(tmp).Reduce(hi[a], cub::Max());
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      atomicMin(&bb[a], dbl_to_ordered(l));
-      atomicMax(&bb[3 + a], dbl_to_ordered(h));
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+      lo[a] = fmin(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], d));
+      hi[a] = fmax(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], d));
     }
+    if (lane == 0) { sh[warp][a] = lo[a]; sh[warp][3 + a] = hi[a]; }
+  }
+  __syncthreads();
+  if (threadIdx.x < 6) {
+    double v = sh[0][threadIdx.x];
+    for (int w = 1; w < 8; ++w) v = (threadIdx.x < 3) ? fmin(v, sh[w][threadIdx.x]) : fmax(v, sh[w][threadIdx.x]);
+    part[blockIdx.x * 6 + threadIdx.x] = v;
   }
 }
 
-__global__ void bbox_decode_kernel(const long long* bb, double* out) {
-  int t = threadIdx.x;
-  if (t < 6) out[t] = ordered_to_dbl(bb[t]);
+// Choose the grid for a bounding box.  `edge_hint` > 0 fixes the cell edge; otherwise the edge is set so
+// that the mean occupancy of the bounding box is `occ` particles per cell.  Degenerate inputs (particles on
+// a plane or a line): a collapsed direction gets one layer of cells and the occupancy is set over the
+// directions that do extend, otherwise the cells come out far too small.
+__device__ void choose_grid(const double* bb, int64_t n, double occ, double edge_hint, int max_cells, GridSpec* g) {
+  double L[3];
+  for (int a = 0; a < 3; ++a) {
+    L[a] = bb[3 + a] - bb[a];
+    if (!(L[a] > 0.0)) L[a] = 0.0;
+  }
+  double Lmax = fmax(L[0], fmax(L[1], L[2]));
+  if (!(Lmax > 0.0)) Lmax = 1.0;
+  double measure = 1.0;
+  int dims = 0;
+  for (int a = 0; a < 3; ++a) {
+    if (L[a] < 1e-6 * Lmax) L[a] = 0.0;
+    else { measure *= L[a]; ++dims; }
+  }
+  double c = edge_hint;
+  if (!(c > 0.0)) {
+    const double per_cell = measure * occ / (double)(n > 0 ? n : 1);
+    c = (dims == 3) ? cbrt(per_cell) : (dims == 2) ? sqrt(per_cell) : (dims == 1) ? per_cell : 1.0;
+  }
+  if (!(c > 0.0)) c = Lmax;
+  for (;;) {
+    const double nx = floor(L[0] / c) + 1, ny = floor(L[1] / c) + 1, nz = floor(L[2] / c) + 1;
+    if (nx * ny * nz <= (double)max_cells && nx < 2.0e6 && ny < 2.0e6 && nz < 2.0e6) {
+      g->nx = (int)nx; g->ny = (int)ny; g->nz = (int)nz;
+      break;
+    }
+    c *= 1.1;
+  }
+  g->c = c;
+  g->inv_c = 1.0 / c;
+  g->ox = bb[0]; g->oy = bb[1]; g->oz = bb[2];
+  g->ncells = g->nx * g->ny * g->nz;
+  g->ngx = (g->nx + 1) / 2; g->ngy = (g->ny + 1) / 2; g->ngz = (g->nz + 1) / 2;
+  g->ngroups = g->ngx * g->ngy * g->ngz;
+  g->n = (int)n;
+}
+
+__global__ void __launch_bounds__(256)
+grid_choose_kernel(const double* __restrict__ part, int nblocks, int64_t n, double occ, double edge_hint, int max_cells,
+                   GridSpec* __restrict__ spec, double* __restrict__ bbox_out) {
+  __shared__ double sh[256][6];
+  double v[6] = {DBL_MAX, DBL_MAX, DBL_MAX, -DBL_MAX, -DBL_MAX, -DBL_MAX};
+  for (int b = threadIdx.x; b < nblocks; b += blockDim.x)
+#pragma unroll
+    for (int a = 0; a < 6; ++a) v[a] = (a < 3) ? fmin(v[a], part[b * 6 + a]) : fmax(v[a], part[b * 6 + a]);
+#pragma unroll
+  for (int a = 0; a < 6; ++a) sh[threadIdx.x][a] = v[a];
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s)
+#pragma unroll
+      for (int a = 0; a < 6; ++a)
+        sh[threadIdx.x][a] = (a < 3) ? fmin(sh[threadIdx.x][a], sh[threadIdx.x + s][a]) : fmax(sh[threadIdx.x][a], sh[threadIdx.x + s][a]);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    double bb[6];
+    bool ok = true;
+    for (int a = 0; a < 6; ++a) bb[a] = sh[0][a];
+    for (int a = 0; a < 3; ++a) if (!(bb[a] <= bb[3 + a])) ok = false;
+    if (!ok) for (int a = 0; a < 6; ++a) bb[a] = 0.0;          // no finite coordinate: one cell, flagged
+    GridSpec g;
+    choose_grid(bb, n, occ, edge_hint, max_cells, &g);
+    g.ok = ok ? 1 : 0;
+    *spec = g;
+    for (int a = 0; a < 6; ++a) bbox_out[a] = bb[a];
+  }
 }
 
 __device__ __forceinline__ int cell_coord(double x, double o, double inv_c, int n) {
-  double f = (x - o) * inv_c;
-  int c = (f >= 0.0) ? ((f < (double)n) ? (int)f : n - 1) : 0;   // NaN -> 0
-  return c;
+  const double f = (x - o) * inv_c;
+  return (f >= 0.0) ? ((f < (double)n) ? (int)f : n - 1) : 0;   // NaN -> 0
 }
 
-__global__ void __launch_bounds__(256) cell_key_kernel(const double* __restrict__ pts, int64_t n, GridSpec g,
-                                                       uint32_t* __restrict__ keys, uint32_t* __restrict__ perm,
-                                                       uint32_t* __restrict__ counts) {
-  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(256) zero_counts_kernel(const GridSpec* __restrict__ spec, uint32_t* __restrict__ counts) {
+  const int m = spec->ncells + 2;
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < m; c += gridDim.x * blockDim.x) counts[c] = 0u;
+}
+
+// key of every particle, its arrival rank inside the cell, per-cell counts
+__global__ void __launch_bounds__(256)
+cell_key_kernel(const double* __restrict__ pts, int64_t n, const GridSpec* __restrict__ spec, uint32_t* __restrict__ keys,
+                uint32_t* __restrict__ rank, uint32_t* __restrict__ counts) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
-  int cx = cell_coord(pts[3 * i + 0], g.ox, g.inv_c, g.nx);
-  int cy = cell_coord(pts[3 * i + 1], g.oy, g.inv_c, g.ny);
-  int cz = cell_coord(pts[3 * i + 2], g.oz, g.inv_c, g.nz);
-  uint32_t key = ((uint32_t)cz * g.ny + cy) * g.nx + cx;
+  const GridSpec g = *spec;
+  const int cx = cell_coord(pts[3 * i + 0], g.ox, g.inv_c, g.nx);
+  const int cy = cell_coord(pts[3 * i + 1], g.oy, g.inv_c, g.ny);
+  const int cz = cell_coord(pts[3 * i + 2], g.oz, g.inv_c, g.nz);
+  const uint32_t key = ((uint32_t)cz * g.ny + cy) * g.nx + cx;
   keys[i] = key;
-  perm[i] = (uint32_t)i;
-  atomicAdd(&counts[key], 1u);
+  rank[i] = atomicAdd(&counts[key], 1u);
 }
 
-// sorted position records {x,y,z,0} (entry n is left to the caller) and the same coordinates as
-// three arrays (the k-NN tiles are staged from these)
-__global__ void __launch_bounds__(256) gather_pos_kernel(const double* __restrict__ pts, const uint32_t* __restrict__ perm,
-                                                         int64_t n, double4* __restrict__ r0, double* __restrict__ xs,
-                                                         double* __restrict__ ys, double* __restrict__ zs) {
-  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+// ---- exclusive scan of counts[0 .. ncells] in place (three small kernels, fixed launch sizes) ----
+__global__ void __launch_bounds__(256)
+scan_tiles_kernel(const GridSpec* __restrict__ spec, uint32_t* __restrict__ a, uint32_t* __restrict__ tops) {
+  const int m = spec->ncells + 1;
+  const int base = blockIdx.x * SCAN_TILE;
+  if (base >= m) return;
+  __shared__ uint32_t wsum[8];
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  uint32_t v[8], sum = 0;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    const int idx = base + t * 8 + q;
+    v[q] = (idx < m) ? a[idx] : 0u;
+    sum += v[q];
+  }
+  uint32_t inc = sum;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane >= d) inc += o;
+  }
+  if (lane == 31) wsum[warp] = inc;
+  __syncthreads();
+  uint32_t before = inc - sum;
+  for (int w = 0; w < warp; ++w) before += wsum[w];
+  if (t == 255) tops[blockIdx.x] = before + sum;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    const int idx = base + t * 8 + q;
+    if (idx < m) a[idx] = before;
+    before += v[q];
+  }
+}
+__global__ void __launch_bounds__(1024) scan_tops_kernel(const GridSpec* __restrict__ spec, uint32_t* __restrict__ tops) {
+  const int ntiles = (spec->ncells + 1 + SCAN_TILE - 1) / SCAN_TILE;
+  __shared__ uint32_t wsum[32];
+  __shared__ uint32_t carry_s;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  if (t == 0) carry_s = 0u;
+  __syncthreads();
+  for (int base = 0; base < ntiles; base += 1024) {
+    const int idx = base + t;
+    const uint32_t v = (idx < ntiles) ? tops[idx] : 0u;
+    uint32_t inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= d) inc += o;
+    }
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+      uint32_t w = wsum[lane];
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xffffffffu, w, d);
+        if (lane >= d) w += o;
+      }
+      wsum[lane] = w;                                        // inclusive totals of the warps
+    }
+    __syncthreads();
+    const uint32_t carry = carry_s;
+    const uint32_t excl = carry + (warp ? wsum[warp - 1] : 0u) + inc - v;
+    if (idx < ntiles) tops[idx] = excl;
+    __syncthreads();
+    if (t == 1023) carry_s = excl + v;
+    __syncthreads();
+  }
+}
+__global__ void __launch_bounds__(256)
+scan_add_kernel(const GridSpec* __restrict__ spec, uint32_t* __restrict__ a, const uint32_t* __restrict__ tops) {
+  const int m = spec->ncells + 1;
+  const int base = blockIdx.x * SCAN_TILE;
+  if (base >= m) return;
+  const uint32_t add = tops[blockIdx.x];
+  for (int q = threadIdx.x; q < SCAN_TILE; q += 256) {
+    const int idx = base + q;
+    if (idx < m) a[idx] += add;
+  }
+}
+// the guard slot cell_start[ncells + 1] = n (rows are read one cell past their end)
+__global__ void scan_guard_kernel(const GridSpec* __restrict__ spec, uint32_t* __restrict__ a) {
+  const int m = spec->ncells + 1;
+  a[m] = a[m - 1];
+}
+
+// counting-sort scatter: sorted slot of particle i = cell_start[key] + rank
+__global__ void __launch_bounds__(256)
+scatter_kernel(int64_t n, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ rank,
+               const uint32_t* __restrict__ cell_start, uint32_t* __restrict__ perm, uint32_t* __restrict__ keys_sorted) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
-  int64_t p = perm[i];
-  const double x = pts[3 * p], y = pts[3 * p + 1], z = pts[3 * p + 2];
-  r0[i] = make_double4(x, y, z, 0.0);
-  xs[i] = x; ys[i] = y; zs[i] = z;
+  const uint32_t key = keys[i];
+  const uint32_t dst = cell_start[key] + rank[i];
+  perm[dst] = (uint32_t)i;
+  keys_sorted[dst] = key;
+}
+
+// The arrival ranks come from atomics, so the order inside a cell differs from run to run.  One warp per cell
+// puts the cell's entries into ascending source index (bitonic network over the lanes for <= 32 entries, a
+// rank sort through `tmp` for up to 256; larger cells keep their arrival order): same sort order, same
+// summation order, same tie-breaks every run.
+__global__ void __launch_bounds__(256)
+cell_order_kernel(const GridSpec* __restrict__ spec, const uint32_t* __restrict__ cell_start, uint32_t* __restrict__ perm,
+                  uint32_t* __restrict__ tmp) {
+  const int ncells = spec->ncells;
+  const int lane = threadIdx.x & 31;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  for (int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; c < ncells; c += nwarps) {
+    const int b = (int)cell_start[c], e = (int)cell_start[c + 1];
+    const int m = e - b;
+    if (m <= 1) continue;
+    if (m <= 32) {
+      uint32_t v = (lane < m) ? perm[b + lane] : 0xffffffffu;
+#pragma unroll
+      for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+          const uint32_t o = __shfl_xor_sync(0xffffffffu, v, j);
+          const bool up = (lane & k) == 0, lower = (lane & j) == 0;
+          v = (lower == up) ? min(v, o) : max(v, o);
+        }
+      }
+      if (lane < m) perm[b + lane] = v;
+    } else if (m <= 256) {
+      for (int s = lane; s < m; s += 32) {
+        const uint32_t v = perm[b + s];
+        int r = 0;
+        for (int f = 0; f < m; ++f) r += perm[b + f] < v;
+        tmp[b + r] = v;
+      }
+      __syncwarp();
+      for (int s = lane; s < m; s += 32) perm[b + s] = tmp[b + s];
+    }
+    __syncwarp();
+  }
+}
+
+// sorted position records {x, y, z, guess}: guess = the previous k-th neighbour distance of the particle (trial
+// radius of the next search; 0 = none).  Entry n is left to the caller.
+__global__ void __launch_bounds__(256)
+gather_pos_kernel(const double* __restrict__ pts, const uint32_t* __restrict__ perm, const double* __restrict__ guess,
+                  int64_t n, double4* __restrict__ r0) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int64_t p = perm[i];
+  r0[i] = make_double4(pts[3 * p], pts[3 * p + 1], pts[3 * p + 2], guess ? guess[p] : 0.0);
 }
 
 int devbuf_reserve(DevBuf& b, size_t bytes) {
@@ -100,97 +302,53 @@ void devbuf_free(DevBuf& b) {
   b.bytes = 0;
 }
 
-// Choose the grid for a bounding box.  `edge_hint` > 0 fixes the cell edge; otherwise the edge is
-// set so that the mean occupancy of the bounding box is `occ` particles per cell.
-static void choose_grid(const double* bb, int64_t n, double occ, double edge_hint, GridSpec* g) {
-  double L[3];
-  for (int a = 0; a < 3; ++a) {
-    L[a] = bb[3 + a] - bb[a];
-    if (!(L[a] > 0.0)) L[a] = 0.0;
-  }
-  double Lmax = fmax(L[0], fmax(L[1], L[2]));
-  if (!(Lmax > 0.0)) Lmax = 1.0;
-  // Degenerate inputs (particles on a plane or a line): a collapsed direction gets one layer of cells and
-  // the occupancy is set over the directions that do extend, otherwise the cells come out far too small.
-  double measure = 1.0;
-  int dims = 0;
-  for (int a = 0; a < 3; ++a) {
-    if (L[a] < 1e-6 * Lmax) L[a] = 0.0;
-    else { measure *= L[a]; ++dims; }
-  }
-  double c = edge_hint;
-  if (!(c > 0.0)) {
-    const double per_cell = measure * occ / (double)(n > 0 ? n : 1);
-    c = (dims == 3) ? cbrt(per_cell) : (dims == 2) ? sqrt(per_cell) : (dims == 1) ? per_cell : 1.0;
-  }
-  if (!(c > 0.0)) c = Lmax;
-  const double max_cells = fmin(4.0 * (double)n + 4096.0, 1.0e9);
-  for (;;) {
-    double nx = floor(L[0] / c) + 1, ny = floor(L[1] / c) + 1, nz = floor(L[2] / c) + 1;
-    if (nx * ny * nz <= max_cells && nx < 2.0e6 && ny < 2.0e6 && nz < 2.0e6) {
-      g->nx = (int)nx; g->ny = (int)ny; g->nz = (int)nz;
-      break;
-    }
-    c *= 1.1;
-  }
-  g->c = c;
-  g->inv_c = 1.0 / c;
-  g->ox = bb[0]; g->oy = bb[1]; g->oz = bb[2];
-  g->ncells = g->nx * g->ny * g->nz;
-}
-
-// Build the cell list for `pts` (device, (N,3) f64).  On return ctx->keys holds sorted keys,
-// ctx->perm the sorted->original permutation, ctx->cell_start the (ncells+1) exclusive scan and
-// ctx->r0 the sorted {x,y,z,0} records.
-int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint, cudaStream_t st) {
+// Build the cell list for `pts` (device, (N,3) f64).  On return (stream order) ctx->grid_dev holds the grid,
+// ctx->keys the sorted cell keys, ctx->perm the sorted->source permutation, ctx->cell_start the
+// (ncells + 2) exclusive scan and ctx->r0 the sorted {x,y,z,guess} records.  Nothing synchronises unless
+// `sync_host` asks for the host copy ctx->grid (function-level API).
+int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint, const double* guess, bool sync_host,
+                cudaStream_t st) {
   if (n <= 0) SPH_FAIL("build_cells: empty particle set");
   if (n >= (int64_t)0x7fffffff) SPH_FAIL("build_cells: N=%lld exceeds the 2^31-1 particle limit per GPU", (long long)n);
+  const int64_t max_cells64 = 2 * n + 4096;
+  const int max_cells = (int)(max_cells64 < 1000000000 ? max_cells64 : 1000000000);
+  ctx->max_cells = max_cells;
+  const int scan_blocks = ceil_div((int64_t)max_cells + 2, SCAN_TILE);
   SPH_TRY(devbuf_reserve(ctx->scal, SC_COUNT * sizeof(double)));
-  SPH_TRY(devbuf_reserve(ctx->tmp0, 64));
-  long long* bb_ord = bufp<long long>(ctx->tmp0);
-  double* scal = bufp<double>(ctx->scal);
-  bbox_init_kernel<<<1, 32, 0, st>>>(bb_ord);
-  int blocks = ceil_div(n, 256); if (blocks > 148 * 8) blocks = 148 * 8;
-  bbox_kernel<<<blocks, 256, 0, st>>>(pts, n, bb_ord);
-  bbox_decode_kernel<<<1, 32, 0, st>>>(bb_ord, scal + SC_BBOX);
-  ctx->launches += 3;
-  double bb[6];
-  CUDA_TRY(cudaMemcpyAsync(bb, scal + SC_BBOX, sizeof(bb), cudaMemcpyDeviceToHost, st));
-  CUDA_TRY(cudaStreamSynchronize(st));
-  for (int a = 0; a < 3; ++a)
-    if (!(bb[a] <= bb[3 + a])) SPH_FAIL("build_cells: no finite coordinates");
-  choose_grid(bb, n, ctx->cell_occ, edge_hint, &ctx->grid);
-  const GridSpec g = ctx->grid;
-
+  SPH_TRY(devbuf_reserve(ctx->tmp0, 64 + BB_BLOCKS * 6 * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->grid_dev, sizeof(GridSpec)));
   SPH_TRY(devbuf_reserve(ctx->keys, n * sizeof(uint32_t)));
   SPH_TRY(devbuf_reserve(ctx->keys_alt, n * sizeof(uint32_t)));
   SPH_TRY(devbuf_reserve(ctx->perm, n * sizeof(uint32_t)));
   SPH_TRY(devbuf_reserve(ctx->perm_alt, n * sizeof(uint32_t)));
-  SPH_TRY(devbuf_reserve(ctx->cell_start, ((size_t)g.ncells + 2) * sizeof(uint32_t)));
+  SPH_TRY(devbuf_reserve(ctx->cell_start, ((size_t)max_cells + 4) * sizeof(uint32_t)));
+  SPH_TRY(devbuf_reserve(ctx->scan_tops, ((size_t)scan_blocks + 1) * sizeof(uint32_t)));
   SPH_TRY(devbuf_reserve(ctx->r0, (size_t)(n + 1) * sizeof(double4)));
+  double* part = reinterpret_cast<double*>(bufp<char>(ctx->tmp0) + 64);
+  double* scal = bufp<double>(ctx->scal);
+  GridSpec* spec = bufp<GridSpec>(ctx->grid_dev);
   uint32_t* cs = bufp<uint32_t>(ctx->cell_start);
-  CUDA_TRY(cudaMemsetAsync(cs, 0, ((size_t)g.ncells + 2) * sizeof(uint32_t), st));
-  cell_key_kernel<<<ceil_div(n, 256), 256, 0, st>>>(pts, n, g, bufp<uint32_t>(ctx->keys_alt), bufp<uint32_t>(ctx->perm_alt), cs);
-  ctx->launches += 1;
-
-  int bits = 1;
-  while ((1ll << bits) < (long long)g.ncells) ++bits;
-  size_t tmp_sort = 0, tmp_scan = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, tmp_sort, bufp<uint32_t>(ctx->keys_alt), bufp<uint32_t>(ctx->keys),
-                                  bufp<uint32_t>(ctx->perm_alt), bufp<uint32_t>(ctx->perm), (int)n, 0, bits, st);
-  cub::DeviceScan::ExclusiveSum(nullptr, tmp_scan, cs, cs, g.ncells + 1, st);
-  size_t tmp_bytes = tmp_sort > tmp_scan ? tmp_sort : tmp_scan;
-  SPH_TRY(devbuf_reserve(ctx->cub_tmp, tmp_bytes));
-  CUDA_TRY(cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tmp_sort, bufp<uint32_t>(ctx->keys_alt), bufp<uint32_t>(ctx->keys),
-                                           bufp<uint32_t>(ctx->perm_alt), bufp<uint32_t>(ctx->perm), (int)n, 0, bits, st));
-  CUDA_TRY(cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tmp_scan, cs, cs, g.ncells + 1, st));
-  ctx->launches += 6;   // radix sort (histogram + onesweep passes) + scan, approximate
-  const size_t ns = soa_stride(n);
-  SPH_TRY(devbuf_reserve(ctx->soa, 3 * ns * sizeof(double)));
-  double* xs = bufp<double>(ctx->soa);
-  gather_pos_kernel<<<ceil_div(n, 256), 256, 0, st>>>(pts, bufp<uint32_t>(ctx->perm), n, bufp<double4>(ctx->r0), xs, xs + ns,
-                                                      xs + 2 * ns);
-  ctx->launches += 1;
+  uint32_t* keys_src = bufp<uint32_t>(ctx->keys_alt);
+  uint32_t* rank = bufp<uint32_t>(ctx->perm_alt);
+  int bb_blocks = ceil_div(n, 256); if (bb_blocks > BB_BLOCKS) bb_blocks = BB_BLOCKS;
+  const int nblk = ceil_div(n, 256);
+  bbox_partial_kernel<<<bb_blocks, 256, 0, st>>>(pts, n, part);
+  grid_choose_kernel<<<1, 256, 0, st>>>(part, bb_blocks, n, ctx->cell_occ, edge_hint, max_cells, spec, scal + SC_BBOX);
+  zero_counts_kernel<<<148 * 4, 256, 0, st>>>(spec, cs);
+  cell_key_kernel<<<nblk, 256, 0, st>>>(pts, n, spec, keys_src, rank, cs);
+  scan_tiles_kernel<<<scan_blocks, 256, 0, st>>>(spec, cs, bufp<uint32_t>(ctx->scan_tops));
+  scan_tops_kernel<<<1, 1024, 0, st>>>(spec, bufp<uint32_t>(ctx->scan_tops));
+  scan_add_kernel<<<scan_blocks, 256, 0, st>>>(spec, cs, bufp<uint32_t>(ctx->scan_tops));
+  scan_guard_kernel<<<1, 1, 0, st>>>(spec, cs);
+  scatter_kernel<<<nblk, 256, 0, st>>>(n, keys_src, rank, cs, bufp<uint32_t>(ctx->perm), bufp<uint32_t>(ctx->keys));
+  cell_order_kernel<<<148 * 4, 256, 0, st>>>(spec, cs, bufp<uint32_t>(ctx->perm), rank);
+  gather_pos_kernel<<<nblk, 256, 0, st>>>(pts, bufp<uint32_t>(ctx->perm), guess, n, bufp<double4>(ctx->r0));
+  ctx->launches += 11;
   CUDA_TRY(cudaGetLastError());
+  if (sync_host) {
+    CUDA_TRY(cudaMemcpyAsync(&ctx->grid, spec, sizeof(GridSpec), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    if (!ctx->grid.ok) SPH_FAIL("build_cells: no finite coordinates");
+  }
   return 0;
 }

@@ -61,6 +61,10 @@ struct GridSpec {
   double c;            // cell edge
   int nx, ny, nz;
   int ncells;
+  int ngx, ngy, ngz;   // groups of 2x2x2 cells (tile.cuh)
+  int ngroups;
+  int n;               // particles the grid was built for
+  int ok;              // 0: no finite coordinate (every particle lands in cell 0)
 };
 
 // A growable device buffer owned by the context.
@@ -77,12 +81,15 @@ struct sphb200_ctx {
   double m_h = 1.0008 * 1.66053906892e-27;
   double m_0 = 31.622776601683793 * 1.989e30;
   // --- scratch / session state (sorted particle order unless noted) ---
-  DevBuf r0, r1, r2, r3;           // packed records, N+1 entries (entry N = the reference's dummy particle)
+  DevBuf r0;                       // sorted position records {x,y,z,guess}, N+1 entries
   DevBuf rho, pi_, aux;            // per-particle doubles
   DevBuf list;                     // (N,k) int32 neighbour list in the index space of the records
-  DevBuf keys, keys_alt, perm, perm_alt, cell_start, cub_tmp;
+  DevBuf keys, keys_alt, perm, perm_alt, cell_start, scan_tops;
+  DevBuf grid_dev;                 // GridSpec chosen on the device by the last build_cells (the hot path never
+                                   // copies it back: every cell-tiled kernel reads it from here)
+  DevBuf list16;                   // (N,k) uint16 neighbour rows as tile offsets (tile.cuh); session path
+  DevBuf recD, recP, recK;         // per-pass records in sorted order: 48 B density, 80 B Pi/force, 8 B Pi coefficient
   DevBuf worklist;                 // k-NN targets left to the general kernel
-  DevBuf soa;                      // sorted coordinates as three arrays xs|ys|zs of soa_stride(n) doubles
   DevBuf scal;                     // device scalars (doubles), see enum Scal
   DevBuf flags;                    // device ints: error / statistics counters
   DevBuf tmp0, tmp1, tmp2, tmp3;   // generic scratch
@@ -92,11 +99,13 @@ struct sphb200_ctx {
   int knn_group = 32;              // lanes per target in the general k-NN kernel
   int knn_fast = 1;                // 1: cell-tiled fast path (knn_cell.cu), 0: general kernel only
   double knn_margin = 0.02;        // trial radius = previous k-th distance * (1 + margin)
-  GridSpec grid;
+  GridSpec grid;                   // host copy; valid only after build_cells(..., sync_host = true)
+  int max_cells = 0;               // capacity of cell_start the device-side grid choice may use
+  int list_is_global = 0;          // 1: ctx->list holds int32 rows for EVERY particle (function API / restored checkpoint)
   // slab decomposition: rows whose caller index (skip_id[i]) is >= skip_from are ghosts; their owners
   // compute their sums, so the k-NN and the list-driven passes skip them as targets (nullptr: none)
   const uint32_t* skip_id = nullptr;
-  int skip_from = 0;
+  uint32_t skip_from = 0;
   int64_t launches = 0;            // kernels launched through this context (for bench "gpu_launches")
   void* session = nullptr;         // the device-resident run this context holds (session.cu), or nullptr
 };
@@ -134,5 +143,7 @@ enum Flag {
   FL_BAD_INDEX = 3,      // neighbour index outside [0, N)
   FL_KNN_NONFINITE = 4,  // k-NN: targets with NaN/inf coordinates
   FL_KNN_NWORK = 5,      // k-NN: length of the work list of the last search
+  FL_GROUP_NEXT = 6,     // dynamic group counter of the persistent cell-tiled kernels (reset by each launch)
+  FL_KNN_CROWDED = 7,    // k-NN: groups whose tile exceeds the shared-memory capacity (all targets to the work list)
   FL_COUNT = 16
 };

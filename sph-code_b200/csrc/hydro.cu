@@ -1,36 +1,58 @@
-// Vectorised-generation hydro passes over a stored neighbour list:
-//   pack      -> per-particle records (see common.cuh)             nsc:559-573, 587-592 per-particle factors
-//   density   -> rho, rho_dust, n                                  nsc:588-590, 605-607
-//   pi        -> per-particle artificial-viscosity Pi_i            nsc:639-649 (axis repaired)
-//   force     -> hydro_accel, visc_accel, visc_heat                nsc:591-592, 615-619, 651-654
-//   species   -> f_un_neighbor                                     nsc:624-626
-//   crossing  -> min_i h_i / max_j |v_j - v_i|                     nsc:776-786
-// G lanes share one target particle: each lane takes neighbours s = lane, lane+G, ... of the row,
-// accumulates privately in fp64 and the G partial sums are combined with warp shuffles.  No atomics;
-// each particle's sums are produced by exactly one group (gather formulation).
-// "self" follows the reference: positions/velocities of column 0 of the row (nsc:580-581), while
-// h_i, rho_i, m_i, Pi_i are taken at the row index.
+// Vectorised-generation hydro passes (nsc:556-671) and the crossing time (nsc:776-786).
+//
+//   pack      -> per-particle records                                  nsc:559-573, 587-592 per-particle factors
+//   density   -> rho, rho_dust, n                                      nsc:588-590, 605-607
+//   pi        -> per-particle artificial-viscosity Pi_i                nsc:639-649 (axis repaired)
+//   force     -> hydro_accel, visc_accel, visc_heat                    nsc:591-592, 615-619, 651-654
+//   crossing  -> min_i h_i / max_j |v_j - v_i|                         nsc:776-786
+//   species   -> f_un_neighbor                                         nsc:624-626
+//   drag      -> dust-gas drag inside the step                         nsc:719-742
+//
+// Every pair pass exists in two forms that share one per-pair function:
+//   * TILE form (the session's hot path): one CTA per half-group of cells (tile.cuh), persistent.  The records of
+//     the three z-layers the half-group needs are staged into shared memory with one bulk asynchronous copy per
+//     row (cp.async.bulk -> UBLKCP, mbarrier completion); a neighbour is a uint16 offset into that tile, so every
+//     neighbour read is a shared-memory read and every record leaves HBM/L2 once per tile instead of once per pair.
+//     8 lanes share one target, accumulate privately in fp64 and combine with shuffles: gather formulation, no
+//     atomics.  Record sizes are odd multiples of 16 B (48, 80) so that random 16-byte reads spread over all
+//     eight 16-byte bank groups.
+//   * LIST form: int32 rows in global memory (the function-level API, whose caller supplies arbitrary rows, and
+//     the rows of targets whose k-th neighbour lies outside their tile).
+// "self" follows the reference: positions/velocities of column 0 of the row (nsc:580-581), while h_i, rho_i,
+// m_i, Pi_i are taken at the row index.
 #include "common.cuh"
 #include "kernels.cuh"
-#include <cooperative_groups.h>
-#include <cooperative_groups/reduce.h>
+#include "tile.cuh"
 #include <float.h>
-namespace cg = cooperative_groups;
 
-#define HY_THREADS 128
-#define HY_G 8
-
+#define HY_THREADS 256
+#define HY_G 8                 // lanes per target
 
 // ---------------------------------------------------------------------------------------------
+// Records (sorted order in the session, caller order in the function-level API)
+//   RecD (48 B) = {x, y | z, h2s | wA, wB}      h2s = h^2, sign bit set for dust;  wA = c6 m [gas or dust];
+//                                               wB = c6 m [gas]/(amu mu);  c6 = 315/(64 pi h^9)          (density)
+//   RecP (80 B) = {x, y | z, h2 | vx, vy | vz, AK | cs, rho}
+//                                               AK = 6 c6 m k T [gas]/(mu amu); cs = sqrt(gamma k T [gas]/(mu amu));
+//                                               rho is filled by the density pass                        (Pi, force)
+//   recK (8 B)  = PK = 6 c6 m Pi [gas], filled by the Pi pass                                            (force)
+//   aux  (8 B)  = 6 c6 m [gas] (PK = aux * Pi)
+// ---------------------------------------------------------------------------------------------
+struct __align__(16) RecD { double x, y, z, h2s, wA, wB; };
+struct __align__(16) RecP { double x, y, z, h2, vx, vy, vz, AK, cs, rho; };
+
+__device__ __forceinline__ double2 ld2(const double* p) { return *reinterpret_cast<const double2*>(p); }
+
 __global__ void __launch_bounds__(256)
-pack_kernel(int n, PackIn in, PhysConst pc, double4* __restrict__ r0, double4* __restrict__ r1, double4* __restrict__ r2,
-            double* __restrict__ coefA) {
+pack_kernel(int n, PackIn in, PhysConst pc, const double4* __restrict__ r0, RecD* __restrict__ rd, RecP* __restrict__ rp,
+            double* __restrict__ aux, double* __restrict__ recK) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const double h = in.h[i];
   const double h2 = h * h;
-  if (in.points) r0[i] = make_double4(in.points[3 * i], in.points[3 * i + 1], in.points[3 * i + 2], h2);
-  else { double4 q = r0[i]; q.w = h2; r0[i] = q; }
+  double x, y, z;
+  if (in.points) { x = in.points[3 * (int64_t)i]; y = in.points[3 * (int64_t)i + 1]; z = in.points[3 * (int64_t)i + 2]; }
+  else { const double4 q = r0[i]; x = q.x; y = q.y; z = q.z; }
   const double h4 = h2 * h2;
   const double c6 = 315.0 / (64.0 * 3.141592653589793 * (h4 * h4 * h));
   const double t = in.ptype[i];
@@ -38,21 +60,33 @@ pack_kernel(int n, PackIn in, PhysConst pc, double4* __restrict__ r0, double4* _
   const double gas = (t == 0.0) ? 1.0 : 0.0;
   const double mg = m * gas;
   const double mn = mg / pc.amu / in.mu[i];
-  r1[i] = make_double4(c6, mg, mn, (t == 2.0) ? m : 0.0);
+  const double md = (t == 2.0) ? m : 0.0;
+  RecD d;
+  d.x = x; d.y = y; d.z = z;
+  d.h2s = (t == 2.0) ? -h2 : h2;
+  d.wA = c6 * (mg + md);
+  d.wB = c6 * mn;
+  rd[i] = d;
   const double kT = pc.kB * in.T[i];
-  const double cs = sqrt(in.gamma[i] * kT / (in.mu[i] * pc.amu) * gas);
-  r2[i] = make_double4(in.vel[3 * i], in.vel[3 * i + 1], in.vel[3 * i + 2], cs);
-  coefA[i] = m / in.mu[i] / pc.amu * kT * gas;          // A_i of nsc:615
+  RecP p;
+  p.x = x; p.y = y; p.z = z; p.h2 = h2;
+  p.vx = in.vel[3 * (int64_t)i]; p.vy = in.vel[3 * (int64_t)i + 1]; p.vz = in.vel[3 * (int64_t)i + 2];
+  p.AK = (6.0 * c6) * (m / in.mu[i] / pc.amu * kT * gas);            // 6 c6 A_i, A_i of nsc:615
+  p.cs = sqrt(in.gamma[i] * kT / (in.mu[i] * pc.amu) * gas);
+  p.rho = 0.0;
+  rp[i] = p;
+  aux[i] = (6.0 * c6) * mg;
+  recK[i] = 0.0;
 }
 
 int launch_pack(sphb200_ctx* ctx, int n, const PackIn& in, cudaStream_t st) {
-  SPH_TRY(devbuf_reserve(ctx->r0, (size_t)(n + 1) * sizeof(double4)));
-  SPH_TRY(devbuf_reserve(ctx->r1, (size_t)(n + 1) * sizeof(double4)));
-  SPH_TRY(devbuf_reserve(ctx->r2, (size_t)(n + 1) * sizeof(double4)));
-  SPH_TRY(devbuf_reserve(ctx->r3, (size_t)(n + 1) * sizeof(rec2)));
-  SPH_TRY(devbuf_reserve(ctx->aux, (size_t)(n + 1) * sizeof(double)));
-  pack_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, in, ctx->phys, bufp<double4>(ctx->r0), bufp<double4>(ctx->r1),
-                                                bufp<double4>(ctx->r2), bufp<double>(ctx->aux));
+  SPH_TRY(devbuf_reserve(ctx->recD, (size_t)(n + 2) * sizeof(RecD)));
+  SPH_TRY(devbuf_reserve(ctx->recP, (size_t)(n + 2) * sizeof(RecP)));
+  SPH_TRY(devbuf_reserve(ctx->recK, (size_t)(n + 2) * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->aux, (size_t)(n + 2) * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->pi_, (size_t)(n + 2) * sizeof(double)));
+  pack_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, in, ctx->phys, bufp<double4>(ctx->r0), bufp<RecD>(ctx->recD),
+                                                bufp<RecP>(ctx->recP), bufp<double>(ctx->aux), bufp<double>(ctx->recK));
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;
@@ -79,296 +113,467 @@ int launch_convert_list(sphb200_ctx* ctx, const int64_t* nb, int n, int k, int32
 }
 
 // ---------------------------------------------------------------------------------------------
-template <int G>
-__global__ void __launch_bounds__(HY_THREADS)
-density_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __restrict__ r0,
-               const double4* __restrict__ r1, double* __restrict__ rho, double* __restrict__ dust,
-               double* __restrict__ num, const uint32_t* __restrict__ skip_id, int skip_from) {
-  cg::thread_block_tile<G> tile = cg::tiled_partition<G>(cg::this_thread_block());
-  const int i = blockIdx.x * (HY_THREADS / G) + tile.meta_group_rank();
-  if (i >= n) return;
-  if (skip_id && (int)skip_id[i] >= skip_from) return;     // ghost: its owner computes it
-  const int lane = tile.thread_rank();
-  const int32_t* row = list + (int64_t)i * k;
-  const int js = row[0];
-  double4 ps = make_double4(0, 0, 0, 0);
-  if (js >= 0) ps = r0[js];
-  double a_rho = 0.0, a_dust = 0.0, a_num = 0.0;
-  for (int s = lane; s < k; s += G) {
-    const int j = row[s];
-    if (j < 0 || j >= n) continue;
-    const double4 q = ldg256(r0 + j);
-    const double4 w = ldg256(r1 + j);
-    const double dx = q.x - ps.x, dy = q.y - ps.y, dz = q.z - ps.z;
-    const double r2 = dx * dx + dy * dy + dz * dz;
-    const double t = q.w - r2;
-    double W = w.x * (t * t * t);                       // c6(h_j) (h_j^2 - r^2)^3
-    W = (W < 0.0) ? 0.0 : W;                            // nsc:589 (NaN stays NaN, as in numpy)
-    a_rho += w.y * W;
-    a_num += w.z * W;
-    a_dust += w.w * W;
-  }
-  a_rho = cg::reduce(tile, a_rho, cg::plus<double>());
-  a_num = cg::reduce(tile, a_num, cg::plus<double>());
-  a_dust = cg::reduce(tile, a_dust, cg::plus<double>());
-  if (lane == 0) { rho[i] = a_rho; dust[i] = a_dust; num[i] = a_num; }
-}
-
-int launch_density(sphb200_ctx* ctx, int n, int k, const int32_t* list, double* rho, double* dust, double* num,
-                   cudaStream_t st) {
-  density_kernel<HY_G><<<ceil_div(n, HY_THREADS / HY_G), HY_THREADS, 0, st>>>(
-      n, k, list, bufp<double4>(ctx->r0), bufp<double4>(ctx->r1), rho, dust, num, ctx->skip_id, ctx->skip_from);
-  ctx->launches += 1;
-  CUDA_TRY(cudaGetLastError());
-  return 0;
-}
-
+// Pass policies.  `rec` pointers may point to shared memory (tile form) or global memory (list form).
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double group_sum(double v) {                    // sum over the HY_G lanes of a target
+#pragma unroll
+  for (int d = HY_G / 2; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+  return v;
+}
+
+struct DensityPass {
+  static constexpr int REC = 48;
+  static constexpr bool USE_K = false, HAS_FINAL = false;
+  struct Params { const RecD* rec; double* rho; double* dust; double* num; RecP* rp; };
+  struct Self { double x, y, z; };
+  struct Acc { double rho, num, dust; };
+  __device__ static const char* records(const Params& p) { return reinterpret_cast<const char*>(p.rec); }
+  __device__ static void zero(Acc& a) { a.rho = a.num = a.dust = 0.0; }
+  __device__ static void self(Self& s, const double* pos, const double*, int, const Params&) {
+    const double2 a = ld2(pos), b = ld2(pos + 2);
+    s.x = a.x; s.y = a.y; s.z = b.x;
+  }
+  __device__ static void pair(Acc& a, const Self& s, const double* r, double) {
+    const double2 xy = ld2(r), zh = ld2(r + 2), w = ld2(r + 4);
+    const double dx = xy.x - s.x, dy = xy.y - s.y, dz = zh.x - s.z;
+    const double r2 = dx * dx + dy * dy + dz * dz;
+    const double t = fabs(zh.y) - r2;
+    const double t3 = t * t * t;
+    double PA = w.x * t3, PB = w.y * t3;                 // c6(h_j) m_j (h_j^2 - r^2)^3
+    PA = (PA < 0.0) ? 0.0 : PA;                          // nsc:589 (NaN stays NaN, as in numpy)
+    PB = (PB < 0.0) ? 0.0 : PB;
+    const bool dust = __double2hiint(zh.y) < 0;          // sign bit of h2s
+    a.rho += dust ? 0.0 : PA;
+    a.dust += dust ? PA : 0.0;
+    a.num += PB;
+  }
+  struct Final {};
+  __device__ static const double* kptr(const Params&) { return nullptr; }
+  __device__ static void store(Acc& a, const Self&, int i, bool lead, bool active, const Params& p, Final&) {
+    a.rho = group_sum(a.rho); a.num = group_sum(a.num); a.dust = group_sum(a.dust);
+    if (lead && active) { p.rho[i] = a.rho; p.dust[i] = a.dust; p.num[i] = a.num; if (p.rp) p.rp[i].rho = a.rho; }
+  }
+  __device__ static void final_init(Final&) {}
+  __device__ static void final_flush(Final&, const Params&) {}
+};
+
 // Pi_i = sum_j -alpha/2 (2 cbar_ij - 3 w_ij) w_ij / rhobar_ij,  alpha = 1            nsc:641-649
-// then r3[i] = {6 c6_i A_i, 6 c6_i m_i Pi_i [gas_i]} for the force pass.
-template <int G>
-__global__ void __launch_bounds__(HY_THREADS)
-pi_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __restrict__ r0, const double4* __restrict__ r1,
-          const double4* __restrict__ r2, const double* __restrict__ rho, const double* __restrict__ coefA,
-          double* __restrict__ Pi, rec2* __restrict__ r3, const uint32_t* __restrict__ skip_id, int skip_from) {
-  cg::thread_block_tile<G> tile = cg::tiled_partition<G>(cg::this_thread_block());
-  const int i = blockIdx.x * (HY_THREADS / G) + tile.meta_group_rank();
-  if (i >= n) return;
-  if (skip_id && (int)skip_id[i] >= skip_from) return;     // ghost: Pi and r3 arrive from its owner
-  const int lane = tile.thread_rank();
-  const int32_t* row = list + (int64_t)i * k;
-  const int js = row[0];
-  double4 ps = make_double4(0, 0, 0, 0), vs = make_double4(0, 0, 0, 0);
-  if (js >= 0) { ps = r0[js]; vs = r2[js]; }
-  const double rho_i = rho[i];
-  const double cs_i = r2[i].w;
-  double acc = 0.0;
-  for (int s = lane; s < k; s += G) {
-    const int j = row[s];
-    if (j < 0 || j >= n) continue;
-    const double4 q = ldg256(r0 + j);
-    const double4 v = ldg256(r2 + j);
-    const double dx = q.x - ps.x, dy = q.y - ps.y, dz = q.z - ps.z;
-    const double dvx = v.x - vs.x, dvy = v.y - vs.y, dvz = v.z - vs.z;
-    const double r2_ = dx * dx + dy * dy + dz * dz;
+struct PiPass {
+  static constexpr int REC = 80;
+  static constexpr bool USE_K = false, HAS_FINAL = false;
+  struct Params { const RecP* rec; const double* aux; double* Pi; double* recK; };
+  struct Self { double x, y, z, vx, vy, vz, cs_i, rho_i; };
+  struct Acc { double v; };
+  __device__ static const char* records(const Params& p) { return reinterpret_cast<const char*>(p.rec); }
+  __device__ static void zero(Acc& a) { a.v = 0.0; }
+  __device__ static void self(Self& s, const double* pos, const double* own, int, const Params&) {
+    const double2 a = ld2(pos), b = ld2(pos + 2), c = ld2(pos + 4), d = ld2(pos + 6), e = ld2(own + 8);
+    s.x = a.x; s.y = a.y; s.z = b.x; s.vx = c.x; s.vy = c.y; s.vz = d.x;
+    s.cs_i = e.x; s.rho_i = e.y;
+  }
+  __device__ static void pair(Acc& a, const Self& s, const double* r, double) {
+    const double2 xy = ld2(r), zh = ld2(r + 2), v01 = ld2(r + 4), v2a = ld2(r + 6), cr = ld2(r + 8);
+    const double dx = xy.x - s.x, dy = xy.y - s.y, dz = zh.x - s.z;
+    const double dvx = v01.x - s.vx, dvy = v01.y - s.vy, dvz = v2a.x - s.vz;
+    const double r2 = dx * dx + dy * dy + dz * dz;
     // one rsqrt and one reciprocal instead of sqrt + two divisions (each an fp64 software sequence);
     // the extra roundings are ~1e-16 relative, the tolerance is 1e-10
-    double w = (dvx * dx + dvy * dy + dvz * dz) * rsqrt(r2_ + 0.01 * q.w);  // nsc:643
-    w = (w > 0.0) ? 0.0 : w;                                               // nsc:644
-    const double inv_rho_avg = 2.0 * __drcp_rn(rho[j] + rho_i);            // nsc:646
-    const double cbar = 0.5 * (v.w + cs_i);                                // nsc:647
-    acc += (-0.5 * (cbar * 2.0 - 3.0 * w) * w) * inv_rho_avg;              // nsc:649
+    double w = (dvx * dx + dvy * dy + dvz * dz) * rsqrt(r2 + 0.01 * zh.y);   // nsc:643
+    w = (w > 0.0) ? 0.0 : w;                                                // nsc:644
+    const double inv_rho_avg = 2.0 * __drcp_rn(cr.y + s.rho_i);             // nsc:646
+    const double cbar = 0.5 * (cr.x + s.cs_i);                              // nsc:647
+    a.v += (-0.5 * (cbar * 2.0 - 3.0 * w) * w) * inv_rho_avg;               // nsc:649
   }
-  acc = cg::reduce(tile, acc, cg::plus<double>());
-  if (lane == 0) {
-    Pi[i] = acc;
-    const double4 w = r1[i];
-    const double K = 6.0 * w.x;
-    rec2 o; o.a = K * coefA[i]; o.b = K * (w.y * acc);
-    r3[i] = o;
+  struct Final {};
+  __device__ static const double* kptr(const Params&) { return nullptr; }
+  __device__ static void store(Acc& a, const Self&, int i, bool lead, bool active, const Params& p, Final&) {
+    a.v = group_sum(a.v);
+    if (lead && active) { p.Pi[i] = a.v; p.recK[i] = p.aux[i] * a.v; }
   }
-}
+  __device__ static void final_init(Final&) {}
+  __device__ static void final_flush(Final&, const Params&) {}
+};
 
-// r3[i] = {6 c6_i A_i, 6 c6_i m_i Pi_i [gas_i]} from the current Pi array (after the ghosts' Pi were
-// overwritten with their owners' values; the pi pass itself skips ghost rows)
-__global__ void __launch_bounds__(256)
-repack_pi_kernel(int n, const double4* __restrict__ r1, const double* __restrict__ coefA, const double* __restrict__ Pi,
-                 rec2* __restrict__ r3) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const double4 w = r1[i];
-  const double K = 6.0 * w.x;
-  rec2 o; o.a = K * coefA[i]; o.b = K * (w.y * Pi[i]);
-  r3[i] = o;
-}
-
-int launch_repack_pi(sphb200_ctx* ctx, int n, cudaStream_t st) {
-  repack_pi_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, bufp<double4>(ctx->r1), bufp<double>(ctx->aux), bufp<double>(ctx->pi_),
-                                                     bufp<rec2>(ctx->r3));
-  ctx->launches += 1;
-  CUDA_TRY(cudaGetLastError());
-  return 0;
-}
-
-int launch_pi(sphb200_ctx* ctx, int n, int k, const int32_t* list, const double* rho, cudaStream_t st) {
-  SPH_TRY(devbuf_reserve(ctx->pi_, (size_t)(n + 1) * sizeof(double)));
-  pi_kernel<HY_G><<<ceil_div(n, HY_THREADS / HY_G), HY_THREADS, 0, st>>>(
-      n, k, list, bufp<double4>(ctx->r0), bufp<double4>(ctx->r1), bufp<double4>(ctx->r2), rho, bufp<double>(ctx->aux),
-      bufp<double>(ctx->pi_), bufp<rec2>(ctx->r3), ctx->skip_id, ctx->skip_from);
-  ctx->launches += 1;
-  CUDA_TRY(cudaGetLastError());
-  return 0;
-}
-
-// ---------------------------------------------------------------------------------------------
 // hydro_accel_i = -(1/rho_i) sum_j 1/2 (A_j gb_ij + A_i ga_ij)                       nsc:615,619
 // visc_accel_i  = -sum_j 1/2 (m_j Pi_j [gas_j] gb_ij + m_i Pi_i [gas_i] ga_ij)      nsc:651-652
 // visc_heat_i   = (m_i/2) sum_j 1/2 (same bracket) . dv_ij                           nsc:653-654
 // with gb_ij = -6 c6(h_j) (h_j^2 - r^2)^2 dx_ij, ga_ij the same with h_i — NOT clamped outside the
 // support (nsc:591-592).
-template <int G>
-__global__ void __launch_bounds__(HY_THREADS)
-force_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __restrict__ r0,
-             const double4* __restrict__ r2, const rec2* __restrict__ r3, const double* __restrict__ rho,
-             const double* __restrict__ mass, double* __restrict__ hydro_accel, double* __restrict__ visc_accel,
-             double* __restrict__ visc_heat, const uint32_t* __restrict__ skip_id, int skip_from) {
-  cg::thread_block_tile<G> tile = cg::tiled_partition<G>(cg::this_thread_block());
-  const int i = blockIdx.x * (HY_THREADS / G) + tile.meta_group_rank();
-  if (i >= n) return;
-  if (skip_id && (int)skip_id[i] >= skip_from) {            // ghost: not advanced here; keep its outputs defined
-    if (tile.thread_rank() == 0) {
-      for (int c = 0; c < 3; ++c) { hydro_accel[3 * (int64_t)i + c] = 0.0; visc_accel[3 * (int64_t)i + c] = 0.0; }
-      visc_heat[i] = 0.0;
-    }
-    return;
+struct ForcePass {
+  static constexpr int REC = 80;
+  static constexpr bool USE_K = true, HAS_FINAL = false;
+  struct Params { const RecP* rec; const double* recK; const double* mass; double* hacc; double* vacc; double* heat; };
+  struct Self { double x, y, z, vx, vy, vz, h2_i, AK_i, PK_i, rho_i; };
+  struct Acc { double px, py, pz, qx, qy, qz, qh; };
+  __device__ static const char* records(const Params& p) { return reinterpret_cast<const char*>(p.rec); }
+  __device__ static void zero(Acc& a) { a.px = a.py = a.pz = a.qx = a.qy = a.qz = a.qh = 0.0; }
+  __device__ static void self(Self& s, const double* pos, const double* own, int i, const Params& p) {
+    const double2 a = ld2(pos), b = ld2(pos + 2), c = ld2(pos + 4), d = ld2(pos + 6);
+    s.x = a.x; s.y = a.y; s.z = b.x; s.vx = c.x; s.vy = c.y; s.vz = d.x;
+    s.h2_i = own[3]; s.AK_i = own[7]; s.rho_i = own[9];
+    s.PK_i = p.recK[i];
   }
-  const int lane = tile.thread_rank();
-  const int32_t* row = list + (int64_t)i * k;
-  const int js = row[0];
-  double4 ps = make_double4(0, 0, 0, 0), vs = make_double4(0, 0, 0, 0);
-  if (js >= 0) { ps = r0[js]; vs = r2[js]; }
-  const double h2_i = r0[i].w;
-  const rec2 ci = r3[i];
-  double px = 0, py = 0, pz = 0, qx = 0, qy = 0, qz = 0, qh = 0;
-  for (int s = lane; s < k; s += G) {
-    const int j = row[s];
-    if (j < 0 || j >= n) continue;
-    const double4 q = ldg256(r0 + j);
-    const double4 v = ldg256(r2 + j);
-    const rec2 cj = r3[j];
-    const double dx = q.x - ps.x, dy = q.y - ps.y, dz = q.z - ps.z;
-    const double r2_ = dx * dx + dy * dy + dz * dz;
-    const double tb = q.w - r2_, ta = h2_i - r2_;
+  __device__ static void pair(Acc& a, const Self& s, const double* r, double PK_j) {
+    const double2 xy = ld2(r), zh = ld2(r + 2), v01 = ld2(r + 4), v2a = ld2(r + 6);
+    const double dx = xy.x - s.x, dy = xy.y - s.y, dz = zh.x - s.z;
+    const double r2 = dx * dx + dy * dy + dz * dz;
+    const double tb = zh.y - r2, ta = s.h2_i - r2;
     const double tb2 = tb * tb, ta2 = ta * ta;
-    const double sP = cj.a * tb2 + ci.a * ta2;
-    const double sV = cj.b * tb2 + ci.b * ta2;
-    px += sP * dx; py += sP * dy; pz += sP * dz;
-    qx += sV * dx; qy += sV * dy; qz += sV * dz;
-    qh += sV * ((v.x - vs.x) * dx + (v.y - vs.y) * dy + (v.z - vs.z) * dz);
+    const double sP = v2a.y * tb2 + s.AK_i * ta2;
+    const double sV = PK_j * tb2 + s.PK_i * ta2;
+    a.px += sP * dx; a.py += sP * dy; a.pz += sP * dz;
+    a.qx += sV * dx; a.qy += sV * dy; a.qz += sV * dz;
+    a.qh += sV * ((v01.x - s.vx) * dx + (v01.y - s.vy) * dy + (v2a.x - s.vz) * dz);
   }
-  px = cg::reduce(tile, px, cg::plus<double>()); py = cg::reduce(tile, py, cg::plus<double>());
-  pz = cg::reduce(tile, pz, cg::plus<double>()); qx = cg::reduce(tile, qx, cg::plus<double>());
-  qy = cg::reduce(tile, qy, cg::plus<double>()); qz = cg::reduce(tile, qz, cg::plus<double>());
-  qh = cg::reduce(tile, qh, cg::plus<double>());
-  if (lane == 0) {
-    const double inv = 0.5 / rho[i];                    // bracket = -1/2 s dx ; accel = -sum(bracket)/rho
-    hydro_accel[3 * (int64_t)i + 0] = px * inv;
-    hydro_accel[3 * (int64_t)i + 1] = py * inv;
-    hydro_accel[3 * (int64_t)i + 2] = pz * inv;
-    visc_accel[3 * (int64_t)i + 0] = 0.5 * qx;
-    visc_accel[3 * (int64_t)i + 1] = 0.5 * qy;
-    visc_accel[3 * (int64_t)i + 2] = 0.5 * qz;
-    visc_heat[i] = -0.25 * mass[i] * qh;
-  }
-}
-
-int launch_force(sphb200_ctx* ctx, int n, int k, const int32_t* list, const double* rho, const double* mass,
-                 double* hydro_accel, double* visc_accel, double* visc_heat, cudaStream_t st) {
-  force_kernel<HY_G><<<ceil_div(n, HY_THREADS / HY_G), HY_THREADS, 0, st>>>(
-      n, k, list, bufp<double4>(ctx->r0), bufp<double4>(ctx->r2), bufp<rec2>(ctx->r3), rho, mass, hydro_accel, visc_accel,
-      visc_heat, ctx->skip_id, ctx->skip_from);
-  ctx->launches += 1;
-  CUDA_TRY(cudaGetLastError());
-  return 0;
-}
-
-// ---------------------------------------------------------------------------------------------
-// f_un_neighbor[s,i] = sum_j m_num_j f_un[j,s] W_ij                                  nsc:624-626
-// One lane per (target, species block); S <= 32 species handled by the lanes of one warp.
-__global__ void __launch_bounds__(HY_THREADS)
-species_kernel(int n, int k, int S, const int32_t* __restrict__ list, const double4* __restrict__ r0,
-               const double4* __restrict__ r1, const double* __restrict__ f_un, double* __restrict__ out) {
-  const int warp = (blockIdx.x * HY_THREADS + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (warp >= n) return;
-  const int i = warp;
-  const int32_t* row = list + (int64_t)i * k;
-  const int js = row[0];
-  double4 ps = make_double4(0, 0, 0, 0);
-  if (js >= 0) ps = r0[js];
-  for (int s0 = 0; s0 < S; s0 += 32) {
-    const int sp = s0 + lane;
-    double acc = 0.0;
-    for (int s = 0; s < k; ++s) {
-      const int j = row[s];
-      if (j < 0 || j >= n) continue;
-      const double4 q = ldg256(r0 + j);
-      const double4 w = ldg256(r1 + j);
-      const double dx = q.x - ps.x, dy = q.y - ps.y, dz = q.z - ps.z;
-      const double t = q.w - (dx * dx + dy * dy + dz * dz);
-      double W = w.x * (t * t * t);
-      W = (W < 0.0) ? 0.0 : W;
-      if (sp < S) acc += w.z * f_un[(int64_t)j * S + sp] * W;
+  struct Final {};
+  __device__ static const double* kptr(const Params& p) { return p.recK; }
+  __device__ static void store(Acc& a, const Self& s, int i, bool lead, bool active, const Params& p, Final&) {
+    a.px = group_sum(a.px); a.py = group_sum(a.py); a.pz = group_sum(a.pz);
+    a.qx = group_sum(a.qx); a.qy = group_sum(a.qy); a.qz = group_sum(a.qz); a.qh = group_sum(a.qh);
+    if (!lead) return;
+    if (!active) {                                       // ghost / non-finite target: keep its outputs defined
+      for (int c = 0; c < 3; ++c) { p.hacc[3 * (int64_t)i + c] = 0.0; p.vacc[3 * (int64_t)i + c] = 0.0; }
+      p.heat[i] = 0.0;
+      return;
     }
-    if (sp < S) out[(int64_t)sp * n + i] = acc;
+    const double inv = 0.5 / s.rho_i;                    // bracket = -1/2 s dx ; accel = -sum(bracket)/rho
+    p.hacc[3 * (int64_t)i + 0] = a.px * inv;
+    p.hacc[3 * (int64_t)i + 1] = a.py * inv;
+    p.hacc[3 * (int64_t)i + 2] = a.pz * inv;
+    p.vacc[3 * (int64_t)i + 0] = 0.5 * a.qx;
+    p.vacc[3 * (int64_t)i + 1] = 0.5 * a.qy;
+    p.vacc[3 * (int64_t)i + 2] = 0.5 * a.qz;
+    p.heat[i] = -0.25 * p.mass[i] * a.qh;
   }
-}
+  __device__ static void final_init(Final&) {}
+  __device__ static void final_flush(Final&, const Params&) {}
+};
 
-int launch_species(sphb200_ctx* ctx, int n, int k, int S, const int32_t* list, const double* f_un, double* out,
-                   cudaStream_t st) {
-  species_kernel<<<ceil_div((int64_t)n * 32, HY_THREADS), HY_THREADS, 0, st>>>(n, k, S, list, bufp<double4>(ctx->r0),
-                                                                            bufp<double4>(ctx->r1), f_un, out);
-  ctx->launches += 1;
-  CUDA_TRY(cudaGetLastError());
-  return 0;
-}
-
-// ---------------------------------------------------------------------------------------------
 // crossing_time: min over gas i of h_i / max_j |v_j - v_i|, zeros ignored, + 1e-4; dt_0/10 if none.
-// Here "self" is the row index (nsc:780 uses velocities[j]).
-__global__ void crossing_init_kernel(unsigned long long* slot) { *slot = 0xffffffffffffffffull; }
-
-// velocities (N,3) -> 32-byte records so that a neighbour costs one sector pair instead of three
-// strided 8-byte loads
-__global__ void __launch_bounds__(256) vel_pack_kernel(int n, const double* __restrict__ vel, double4* __restrict__ rec) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) rec[i] = make_double4(vel[3 * (int64_t)i], vel[3 * (int64_t)i + 1], vel[3 * (int64_t)i + 2], 0.0);
-}
-
-template <int G>
-__global__ void __launch_bounds__(HY_THREADS)
-crossing_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __restrict__ vrec,
-                const double* __restrict__ sizes, const double* __restrict__ ptype, const uint32_t* __restrict__ id,
-                int n_owned, unsigned long long* slot) {
-  __shared__ unsigned long long smin;
-  cg::thread_block_tile<G> tile = cg::tiled_partition<G>(cg::this_thread_block());
-  const int i = min(blockIdx.x * (HY_THREADS / G) + (int)tile.meta_group_rank(), n - 1);   // tail groups repeat n-1
-  if (threadIdx.x == 0) smin = 0xffffffffffffffffull;
-  __syncthreads();
-  const int lane = tile.thread_rank();
-  const int32_t* row = list + (int64_t)i * k;
-  const double4 vi = vrec[i];
-  double mx = 0.0;
-  bool nan = false;
-  for (int s = lane; s < k; s += G) {
-    const int j = row[s];
-    if (j < 0 || j >= n) continue;
-    const double4 vj = ldg256(vrec + j);
-    const double ax = vj.x - vi.x, ay = vj.y - vi.y, az = vj.z - vi.z;
-    const double v2 = ax * ax + ay * ay + az * az;
-    if (v2 != v2) nan = true;                           // np.max propagates NaN
-    mx = fmax(mx, v2);
+// Here "self" is the row index (nsc:780 uses velocities[j]).  Records = the (N,3) velocity array itself.
+struct CrossingPass {
+  static constexpr int REC = 24;
+  static constexpr bool USE_K = false, HAS_FINAL = true;
+  struct Params { const double* vel; const double* sizes; const double* ptype; const uint32_t* id; uint32_t n_owned;
+                  unsigned long long* slot; };
+  struct Self { double vx, vy, vz; };
+  struct Acc { double mx; int nan; };
+  __device__ static const char* records(const Params& p) { return reinterpret_cast<const char*>(p.vel); }
+  __device__ static void zero(Acc& a) { a.mx = 0.0; a.nan = 0; }
+  __device__ static void self(Self& s, const double*, const double* own, int, const Params&) {
+    s.vx = own[0]; s.vy = own[1]; s.vz = own[2];
   }
-  mx = cg::reduce(tile, mx, cg::greater<double>());
-  nan = tile.any(nan);
-  unsigned long long u = 0xffffffffffffffffull;
-  // ghost particles of a slab decomposition (caller index >= n_owned) belong to another rank's minimum
-  if (lane == 0 && ptype[i] == 0.0 && (!id || (int)id[i] < n_owned)) {
-    double ct = nan ? 0.0 : sizes[i] / sqrt(mx);        // nan_to_num: NaN -> 0
-    if (ct != ct) ct = 0.0;                             // 0/0
-    if (ct > DBL_MAX) ct = DBL_MAX;                     // nan_to_num: +inf -> largest finite
-    if (ct < -DBL_MAX) ct = -DBL_MAX;
-    if (ct != 0.0) {
-      // ordered encoding for signed doubles
-      long long b = __double_as_longlong(ct);
-      u = (b >= 0) ? ((unsigned long long)b | 0x8000000000000000ull) : ~(unsigned long long)b;
+  __device__ static void pair(Acc& a, const Self& s, const double* r, double) {
+    const double ax = r[0] - s.vx, ay = r[1] - s.vy, az = r[2] - s.vz;
+    const double v2 = ax * ax + ay * ay + az * az;
+    if (v2 != v2) a.nan = 1;                             // np.max propagates NaN
+    a.mx = fmax(a.mx, v2);
+  }
+  struct Final { unsigned long long u; };
+  __device__ static const double* kptr(const Params&) { return nullptr; }
+  __device__ static void final_init(Final& f) { f.u = 0xffffffffffffffffull; }
+  __device__ static void store(Acc& a, const Self&, int i, bool lead, bool active, const Params& p, Final& f) {
+#pragma unroll
+    for (int d = HY_G / 2; d > 0; d >>= 1) {
+      a.mx = fmax(a.mx, __shfl_xor_sync(0xffffffffu, a.mx, d));
+      a.nan |= __shfl_xor_sync(0xffffffffu, a.nan, d);
+    }
+    // ghost particles of a slab decomposition (caller index >= n_owned) belong to another rank's minimum
+    if (lead && active && p.ptype[i] == 0.0 && (!p.id || p.id[i] < p.n_owned)) {
+      double ct = a.nan ? 0.0 : p.sizes[i] / sqrt(a.mx);  // nan_to_num: NaN -> 0
+      if (ct != ct) ct = 0.0;                             // 0/0
+      if (ct > DBL_MAX) ct = DBL_MAX;                     // nan_to_num: +inf -> largest finite
+      if (ct < -DBL_MAX) ct = -DBL_MAX;
+      if (ct != 0.0) {
+        const long long b = __double_as_longlong(ct);     // ordered encoding for signed doubles
+        const unsigned long long u = (b >= 0) ? ((unsigned long long)b | 0x8000000000000000ull) : ~(unsigned long long)b;
+        if (u < f.u) f.u = u;
+      }
     }
   }
-  // one global atomic per CTA, not per particle (a single hot address serialises in L2)
-  if (u != 0xffffffffffffffffull) atomicMin(&smin, u);
-  __syncthreads();
-  if (threadIdx.x == 0 && smin != 0xffffffffffffffffull) atomicMin(slot, smin);
+  __device__ static void final_flush(Final& f, const Params& p) {    // one global atomic per warp
+    unsigned long long u = f.u;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+      const unsigned long long o = __shfl_xor_sync(0xffffffffu, u, d);
+      if (o < u) u = o;
+    }
+    if ((threadIdx.x & 31) == 0 && u != 0xffffffffffffffffull) atomicMin(p.slot, u);
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
+// TILE form
+// ---------------------------------------------------------------------------------------------
+struct TilePassArgs {
+  const GridSpec* spec;
+  const uint32_t* cell_start;
+  const uint16_t* list16;      // (N,k) tile offsets
+  int n, k;
+};
+
+struct TpMisc {
+  int tbegin[2], tend[2], tbase[3];
+  int len[4];
+  int o_lo, r_lo, r_hi, crowded;
+  uint64_t bar;
+};
+
+template <class P>
+__global__ void __launch_bounds__(HY_THREADS) tile_pass_kernel(TilePassArgs a, typename P::Params p) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  // layout: records [TILE_HALF_CAP * REC] | K [TILE_HALF_CAP * 8 if USE_K] | rows uint16 [TILE_HALF_TARGETS * k] | TileRows | misc
+  constexpr int OFF_K = TILE_HALF_CAP * P::REC;
+  constexpr int OFF_L = OFF_K + (P::USE_K ? TILE_HALF_CAP * 8 : 0);
+  unsigned char* trec = smem;
+  double* tk = reinterpret_cast<double*>(smem + OFF_K);
+  uint16_t* rowsm = reinterpret_cast<uint16_t*>(smem + OFF_L);
+  const int off_rows = (OFF_L + TILE_HALF_TARGETS * a.k * 2 + 15) & ~15;
+  TileRows* rows = reinterpret_cast<TileRows*>(smem + off_rows);
+  TpMisc* misc = reinterpret_cast<TpMisc*>(smem + off_rows + 384);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const GridSpec g = *a.spec;
+  const char* grec = P::records(p);
+  const double* gk = P::kptr(p);
+  if (tid == 0) { mbar_init(&misc->bar, 1); mbar_fence_init(); }
+  uint32_t phase = 0;
+  typename P::Final fin;
+  P::final_init(fin);
+  const int nunits = 2 * g.ngroups;
+  for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
+    const int group = unit >> 1, hz = unit & 1;
+    int gx, gy, gz;
+    group_coords(g, group, &gx, &gy, &gz);
+    const int cz = 2 * gz + hz;
+    if (cz >= g.nz) continue;
+    __syncthreads();                                          // previous unit done with every buffer
+    if (warp == 0) {
+      tile_rows(g, a.cell_start, gx, gy, gz, lane, rows);
+      int b = 0, e = 0, r = 0;
+      const bool have = (lane < 4) && group_target_run(g, a.cell_start, gx, gy, gz, lane, &b, &e, &r);
+      if (lane < 4) misc->len[lane] = have ? (e - b) : 0;
+      if ((lane >> 1) == hz && lane < 4) { misc->tbegin[lane & 1] = b; misc->tend[lane & 1] = have ? e : b; }
+    }
+    __syncthreads();
+    if (tid == 0) {
+      const int l0 = misc->tend[0] - misc->tbegin[0], l1 = misc->tend[1] - misc->tbegin[1];
+      misc->tbase[0] = 0; misc->tbase[1] = l0; misc->tbase[2] = l0 + l1;
+      const int zlo = max(cz - 1, 0), zhi = min(cz + 1, g.nz - 1);
+      misc->r_lo = (zlo - rows->z0) * rows->ysp;
+      misc->r_hi = (zhi - rows->z0 + 1) * rows->ysp;
+      misc->o_lo = rows->toff[misc->r_lo];
+      // the same decision the k-NN kernel took for this group: the targets of a crowded group have global rows
+      misc->crowded = tile_crowded(g, rows, misc->len) ? 1 : 0;
+    }
+    __syncthreads();
+    const int ntgt = misc->tbase[2];
+    if (ntgt == 0 || misc->crowded) continue;
+    const int o_lo = misc->o_lo;
+    // ---- stage: one bulk copy per row of records (+ the 8-byte coefficients); the targets' rows by plain loads ----
+    if (warp == 0) {
+      fence_proxy_async();
+      const int r = misc->r_lo + lane;
+      const bool on = r < misc->r_hi;
+      const int plen = on ? (rows->toff[r + 1] - rows->toff[r]) : 0;
+      unsigned tot = (unsigned)plen * (unsigned)(P::REC + (P::USE_K ? 8 : 0));
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, d);
+      if (lane == 0) mbar_expect_tx(&misc->bar, tot);
+      __syncwarp();
+      if (plen) {
+        const int o = rows->toff[r] - o_lo, ps = rows->ps[r];
+        bulk_g2s(trec + (size_t)o * P::REC, grec + (size_t)ps * P::REC, (unsigned)plen * P::REC, &misc->bar);
+        if (P::USE_K) bulk_g2s(tk + o, gk + ps, (unsigned)plen * 8u, &misc->bar);
+      }
+    }
+    {
+      const int k = a.k;
+#pragma unroll 1
+      for (int q = 0; q < 2; ++q) {
+        const int len = (misc->tend[q] - misc->tbegin[q]) * k;
+        const uint16_t* src = a.list16 + (int64_t)misc->tbegin[q] * k;
+        uint16_t* dst = rowsm + misc->tbase[q] * k;
+        if ((((size_t)src | (size_t)dst) & 3) == 0) {
+          const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
+          uint32_t* d32 = reinterpret_cast<uint32_t*>(dst);
+          for (int e = tid; e < (len >> 1); e += HY_THREADS) d32[e] = s32[e];
+          if ((len & 1) && tid == 0) dst[len - 1] = src[len - 1];
+        } else {
+          for (int e = tid; e < len; e += HY_THREADS) dst[e] = src[e];
+        }
+      }
+    }
+    mbar_wait(&misc->bar, phase);
+    phase ^= 1u;
+    __syncthreads();
+    // ---- targets: HY_G lanes each ----
+    const int sub = lane & (HY_G - 1);
+    for (int t0 = 0; t0 < ntgt; t0 += (HY_THREADS / HY_G)) {
+      const int t = t0 + warp * (32 / HY_G) + (lane / HY_G);
+      const bool valid = t < ntgt;
+      const int q = (valid && t >= misc->tbase[1]) ? 1 : 0;
+      const int i = valid ? misc->tbegin[q] + (t - misc->tbase[q]) : 0;
+      const uint16_t* row = rowsm + (valid ? t : 0) * a.k;
+      const unsigned s0 = row[0];
+      const bool active = valid && s0 < LIST_MISSING;
+      typename P::Self self;
+      typename P::Acc acc;
+      P::zero(acc);
+      if (active) {
+        const double* rs = reinterpret_cast<const double*>(trec + (size_t)(s0 - o_lo) * P::REC);
+        P::self(self, rs, rs, i, p);
+        for (int s = sub; s < a.k; s += HY_G) {
+          const unsigned o = row[s];
+          if (o >= LIST_MISSING) continue;
+          const double* r = reinterpret_cast<const double*>(trec + (size_t)(o - o_lo) * P::REC);
+          P::pair(acc, self, r, P::USE_K ? tk[o - o_lo] : 0.0);
+        }
+      }
+      const bool escaped = valid && s0 == LIST_ESCAPED;        // its row is in the global list: the LIST form writes it
+      P::store(acc, self, i, sub == 0 && valid && !escaped, active, p, fin);
+    }
+  }
+  if (P::HAS_FINAL) P::final_flush(fin, p);
 }
+
+template <class P>
+static int tile_pass_smem(int k) {
+  const int off_l = TILE_HALF_CAP * P::REC + (P::USE_K ? TILE_HALF_CAP * 8 : 0);
+  return ((off_l + TILE_HALF_TARGETS * k * 2 + 15) & ~15) + 384 + (int)sizeof(TpMisc) + 16;
+}
+
+template <class P>
+static int launch_tile_pass(sphb200_ctx* ctx, int n, int k, const uint16_t* list16, const typename P::Params& p, cudaStream_t st) {
+  TilePassArgs a;
+  a.spec = bufp<GridSpec>(ctx->grid_dev);
+  a.cell_start = bufp<uint32_t>(ctx->cell_start);
+  a.list16 = list16;
+  a.n = n; a.k = k;
+  const int smem = tile_pass_smem<P>(k);
+  if (smem > 220 * 1024) SPH_FAIL("tile pass: k=%d needs %d B of shared memory", k, smem);
+  CUDA_TRY(cudaFuncSetAttribute(tile_pass_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  int per_sm = (227 * 1024) / (smem + 1024);
+  if (per_sm < 1) per_sm = 1;
+  if (per_sm > 8) per_sm = 8;
+  tile_pass_kernel<P><<<148 * per_sm, HY_THREADS, smem, st>>>(a, p);
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// LIST form: int32 rows in global memory.  targets == nullptr: every particle i, row i; otherwise the
+// particles targets[0 .. *ntargets) with row t for entry t (escaped rows of a session, stored by slot).
+// ---------------------------------------------------------------------------------------------
+struct ListPassArgs {
+  const int32_t* list;
+  const int* targets;
+  const int* ntargets;
+  int n, k;
+  const uint32_t* skip_id;     // slab decomposition: ghosts are not targets
+  uint32_t skip_from;
+};
+
+template <class P>
+__global__ void __launch_bounds__(HY_THREADS) list_pass_kernel(ListPassArgs a, typename P::Params p) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int sub = lane & (HY_G - 1);
+  constexpr int TPW = 32 / HY_G;                              // targets per warp
+  const int ntarget = a.targets ? *a.ntargets : a.n;
+  const char* grec = P::records(p);
+  const double* gk = P::kptr(p);
+  typename P::Final fin;
+  P::final_init(fin);
+  const int wstride = gridDim.x * (HY_THREADS / 32) * TPW;
+  for (int base = (blockIdx.x * (HY_THREADS / 32) + warp) * TPW; base < ntarget; base += wstride) {
+    const int t = base + lane / HY_G;
+    const bool valid = t < ntarget;
+    const int i = valid ? (a.targets ? a.targets[t] : t) : 0;
+    const int32_t* row = a.list + (int64_t)(valid ? (a.targets ? t : i) : 0) * a.k;
+    const bool active = valid && !(a.skip_id && a.skip_id[i] >= a.skip_from);
+    typename P::Self self;
+    typename P::Acc acc;
+    P::zero(acc);
+    if (active) {
+      const int js = row[0];
+      __align__(16) double zrec[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+      const double* own = reinterpret_cast<const double*>(grec + (size_t)i * P::REC);
+      const double* pos = (js >= 0 && js < a.n) ? reinterpret_cast<const double*>(grec + (size_t)js * P::REC) : zrec;
+      P::self(self, pos, own, i, p);
+      for (int s = sub; s < a.k; s += HY_G) {
+        const int j = row[s];
+        if (j < 0 || j >= a.n) continue;
+        P::pair(acc, self, reinterpret_cast<const double*>(grec + (size_t)j * P::REC), P::USE_K ? gk[j] : 0.0);
+      }
+    }
+    P::store(acc, self, i, sub == 0 && valid, active, p, fin);
+  }
+  if (P::HAS_FINAL) P::final_flush(fin, p);
+}
+
+template <class P>
+static int launch_list_pass(sphb200_ctx* ctx, int n, int k, const int32_t* list, const int* targets, const int* ntargets,
+                            const typename P::Params& p, cudaStream_t st) {
+  ListPassArgs a;
+  a.list = list; a.targets = targets; a.ntargets = ntargets; a.n = n; a.k = k;
+  a.skip_id = ctx->skip_id; a.skip_from = ctx->skip_from;
+  const int per_block = HY_THREADS / HY_G;
+  int blocks = targets ? 148 * 4 : ceil_div(n, per_block);
+  if (blocks > 148 * 64) blocks = 148 * 64;                  // grid-stride beyond that
+  list_pass_kernel<P><<<blocks, HY_THREADS, 0, st>>>(a, p);
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// Run one pass over the rows `r`: the tile form over the uint16 rows plus the list form over the escaped
+// targets, or the list form over everything.
+template <class P>
+static int run_pass(sphb200_ctx* ctx, int n, int k, const RowsRef& r, const typename P::Params& p, cudaStream_t st) {
+  if (r.list16) {
+    SPH_TRY(launch_tile_pass<P>(ctx, n, k, r.list16, p, st));
+    return launch_list_pass<P>(ctx, n, k, r.list, r.targets, r.ntargets, p, st);
+  }
+  return launch_list_pass<P>(ctx, n, k, r.list, nullptr, nullptr, p, st);
+}
+
+int launch_density(sphb200_ctx* ctx, int n, int k, const RowsRef& rows, double* rho, double* dust, double* num, cudaStream_t st) {
+  DensityPass::Params p = {bufp<RecD>(ctx->recD), rho, dust, num, bufp<RecP>(ctx->recP)};
+  return run_pass<DensityPass>(ctx, n, k, rows, p, st);
+}
+
+int launch_pi(sphb200_ctx* ctx, int n, int k, const RowsRef& rows, cudaStream_t st) {
+  PiPass::Params p = {bufp<RecP>(ctx->recP), bufp<double>(ctx->aux), bufp<double>(ctx->pi_), bufp<double>(ctx->recK)};
+  return run_pass<PiPass>(ctx, n, k, rows, p, st);
+}
+
+int launch_force(sphb200_ctx* ctx, int n, int k, const RowsRef& rows, const double* mass, double* hydro_accel,
+                 double* visc_accel, double* visc_heat, cudaStream_t st) {
+  ForcePass::Params p = {bufp<RecP>(ctx->recP), bufp<double>(ctx->recK), mass, hydro_accel, visc_accel, visc_heat};
+  return run_pass<ForcePass>(ctx, n, k, rows, p, st);
+}
+
+// Owner-computed values of ghost particles arrive after a pass (slab decomposition): put them where the next pass
+// reads them.  what = 0: rho[] -> RecP.rho;  1: Pi[] -> recK = aux * Pi.
+__global__ void __launch_bounds__(256)
+repack_kernel(int n, int what, const double* __restrict__ rho, const double* __restrict__ Pi, const double* __restrict__ aux,
+              RecP* __restrict__ rp, double* __restrict__ recK) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (what == 0) rp[i].rho = rho[i];
+  else recK[i] = aux[i] * Pi[i];
+}
+
+int launch_repack(sphb200_ctx* ctx, int n, int what, const double* rho, cudaStream_t st) {
+  repack_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, what, rho, bufp<double>(ctx->pi_), bufp<double>(ctx->aux),
+                                                 bufp<RecP>(ctx->recP), bufp<double>(ctx->recK));
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// ---- crossing time -----------------------------------------------------------------------------
+__global__ void crossing_init_kernel(unsigned long long* slot) { *slot = 0xffffffffffffffffull; }
 
 __global__ void crossing_final_kernel(const unsigned long long* slot, double dt_0, double* out) {
   const unsigned long long u = *slot;
@@ -377,17 +582,68 @@ __global__ void crossing_final_kernel(const unsigned long long* slot, double dt_
   *out = __longlong_as_double(b) + 0.0001;
 }
 
-int launch_crossing_time(sphb200_ctx* ctx, int n, int k, const int32_t* list, const double* vel, const double* sizes,
-                         const double* ptype, double dt_0, double* out_dev, const uint32_t* id, int n_owned, cudaStream_t st) {
+int launch_crossing_time(sphb200_ctx* ctx, int n, int k, const RowsRef& rows, const double* vel, const double* sizes,
+                         const double* ptype, double dt_0, double* out_dev, const uint32_t* id, uint32_t n_owned, cudaStream_t st) {
   SPH_TRY(devbuf_reserve(ctx->tmp0, 64));
   unsigned long long* slot = bufp<unsigned long long>(ctx->tmp0);
-  SPH_TRY(devbuf_reserve(ctx->r2, (size_t)(n + 1) * sizeof(double4)));   // scratch here; pack() rewrites it later
-  double4* vrec = bufp<double4>(ctx->r2);
   crossing_init_kernel<<<1, 1, 0, st>>>(slot);
-  vel_pack_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, vel, vrec);
-  crossing_kernel<HY_G><<<ceil_div(n, HY_THREADS / HY_G), HY_THREADS, 0, st>>>(n, k, list, vrec, sizes, ptype, id, n_owned, slot);
+  CrossingPass::Params p = {vel, sizes, ptype, id, n_owned, slot};
+  SPH_TRY(run_pass<CrossingPass>(ctx, n, k, rows, p, st));
   crossing_final_kernel<<<1, 1, 0, st>>>(slot, dt_0, out_dev);
-  ctx->launches += 4;
+  ctx->launches += 2;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// f_un_neighbor[s,i] = sum_j m_num_j f_un[j,s] W_ij                                  nsc:624-626
+// 8 lanes per target (each takes every 8th neighbour); the weight of a pair is computed once and applied to
+// up to 16 species held in registers; the lanes' partial sums are combined with shuffles.
+// ---------------------------------------------------------------------------------------------
+#define SP_CHUNK 16
+__global__ void __launch_bounds__(HY_THREADS)
+species_kernel(int n, int k, int S, const int32_t* __restrict__ list, const RecD* __restrict__ rec,
+               const double* __restrict__ f_un, double* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int sub = lane & (HY_G - 1);
+  const int t = (blockIdx.x * HY_THREADS + threadIdx.x) / HY_G;
+  const bool valid = t < n;
+  const int i = valid ? t : 0;
+  const int32_t* row = list + (int64_t)i * k;
+  const int js = valid ? row[0] : -1;
+  double sx = 0, sy = 0, sz = 0;
+  if (js >= 0 && js < n) { sx = rec[js].x; sy = rec[js].y; sz = rec[js].z; }
+  for (int s0 = 0; s0 < S; s0 += SP_CHUNK) {
+    double acc[SP_CHUNK];
+#pragma unroll
+    for (int c = 0; c < SP_CHUNK; ++c) acc[c] = 0.0;
+    if (valid) {
+      for (int s = sub; s < k; s += HY_G) {
+        const int j = row[s];
+        if (j < 0 || j >= n) continue;
+        const double* r = reinterpret_cast<const double*>(rec + j);
+        const double2 xy = ld2(r), zh = ld2(r + 2), w = ld2(r + 4);
+        const double dx = xy.x - sx, dy = xy.y - sy, dz = zh.x - sz;
+        const double tt = fabs(zh.y) - (dx * dx + dy * dy + dz * dz);
+        double PB = w.y * (tt * tt * tt);                  // m_num_j c6(h_j) (h_j^2 - r^2)^3
+        PB = (PB < 0.0) ? 0.0 : PB;
+        const double* f = f_un + (int64_t)j * S + s0;
+#pragma unroll
+        for (int c = 0; c < SP_CHUNK; ++c) if (s0 + c < S) acc[c] += f[c] * PB;
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < SP_CHUNK; ++c) {
+      const double v = group_sum(acc[c]);
+      if (valid && sub == 0 && s0 + c < S) out[(int64_t)(s0 + c) * n + i] = v;
+    }
+  }
+}
+
+int launch_species(sphb200_ctx* ctx, int n, int k, int S, const int32_t* list, const double* f_un, double* out,
+                   cudaStream_t st) {
+  species_kernel<<<ceil_div((int64_t)n * HY_G, HY_THREADS), HY_THREADS, 0, st>>>(n, k, S, list, bufp<RecD>(ctx->recD), f_un, out);
+  ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -396,49 +652,47 @@ int launch_crossing_time(sphb200_ctx* ctx, int n, int k, const int32_t* list, co
 // F1 in the device-resident step: dust-gas drag on the packed records          nsc:719-742
 // (code_running.py:455,462-463,473).  Only dust neighbours carry a term, so the per-particle MRN
 // means stay in the caller's order and are fetched through `id` for those neighbours alone; the
-// reaction on the dust particle is a sparse fp64 RED.
-template <int G>
+// reaction on the dust particle is a sparse fp64 RED.  LIST form over int32 rows of every particle.
+// ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(HY_THREADS)
-drag_kernel(int n, int k, const int32_t* __restrict__ list, const double4* __restrict__ r0,
-            const double4* __restrict__ r1, const double4* __restrict__ r2, const uint32_t* __restrict__ id,
-            const double* __restrict__ mg, const double* __restrict__ mc, double* __restrict__ onto,
-            double* __restrict__ reaction) {
-  cg::thread_block_tile<G> tile = cg::tiled_partition<G>(cg::this_thread_block());
-  const int i = blockIdx.x * (HY_THREADS / G) + tile.meta_group_rank();
-  if (i >= n) return;
-  const int lane = tile.thread_rank();
+drag_kernel(int n, int k, const int32_t* __restrict__ list, const RecD* __restrict__ rd, const RecP* __restrict__ rp,
+            const uint32_t* __restrict__ id, const double* __restrict__ mg, const double* __restrict__ mc,
+            double* __restrict__ onto, double* __restrict__ reaction) {
+  const int lane = threadIdx.x & 31;
+  const int sub = lane & (HY_G - 1);
+  const int t = (blockIdx.x * HY_THREADS + threadIdx.x) / HY_G;
+  const bool valid = t < n;
+  const int i = valid ? t : 0;
   const int32_t* row = list + (int64_t)i * k;
-  const double4 ps = r0[i];
-  const double4 vs = r2[i];
+  const RecP ps = rp[i];
   double ax = 0, ay = 0, az = 0;
-  for (int s = lane; s < k; s += G) {
-    const int j = row[s];
-    if (j < 0 || j >= n) continue;
-    const double4 w = ldg256(r1 + j);
-    if (w.w == 0.0) continue;                             // [type_j == 2] (m_dust of the record)
-    const double4 q = ldg256(r0 + j);
-    const double4 v = ldg256(r2 + j);
-    const double dx = q.x - ps.x, dy = q.y - ps.y, dz = q.z - ps.z;
-    const double r2_ = dx * dx + dy * dy + dz * dz;
-    const double t = q.w - r2_;
-    const double wf = w.w * w.x * (t * t * t);            // Weigh2_dust: m c6(h_j) (h_j^2 - r^2)^3, nsc:678-681
-    if (!(wf > 0.0)) continue;                            // [weight_factor > 0]
-    const double du = v.x - vs.x, dv = v.y - vs.y, dw = v.z - vs.z;
-    const double speed = sqrt(du * du + dv * dv + dw * dw);
-    const uint32_t g = id ? id[j] : (uint32_t)j;
-    const double c = wf / mg[g] * mc[g] * speed;          // nsc:738
-    const double gx = c * du, gy = c * dv, gz = c * dw;
-    ax += gx; ay += gy; az += gz;
-    if (j != i) {                                         // nsc:741
-      if (gx != 0.0) atomicAdd(reaction + 3 * (int64_t)j, -gx);
-      if (gy != 0.0) atomicAdd(reaction + 3 * (int64_t)j + 1, -gy);
-      if (gz != 0.0) atomicAdd(reaction + 3 * (int64_t)j + 2, -gz);
+  if (valid) {
+    for (int s = sub; s < k; s += HY_G) {
+      const int j = row[s];
+      if (j < 0 || j >= n) continue;
+      const RecD q = rd[j];
+      if (__double2hiint(q.h2s) >= 0) continue;             // [type_j == 2]: the dust flag of the record
+      const double dx = q.x - ps.x, dy = q.y - ps.y, dz = q.z - ps.z;
+      const double r2_ = dx * dx + dy * dy + dz * dz;
+      const double tt = fabs(q.h2s) - r2_;
+      const double wf = q.wA * (tt * tt * tt);              // Weigh2_dust: m c6(h_j) (h_j^2 - r^2)^3, nsc:678-681
+      if (!(wf > 0.0)) continue;                            // [weight_factor > 0]
+      const RecP v = rp[j];
+      const double du = v.vx - ps.vx, dv = v.vy - ps.vy, dw = v.vz - ps.vz;
+      const double speed = sqrt(du * du + dv * dv + dw * dw);
+      const uint32_t g = id ? id[j] : (uint32_t)j;
+      const double c = wf / mg[g] * mc[g] * speed;          // nsc:738
+      const double gx = c * du, gy = c * dv, gz = c * dw;
+      ax += gx; ay += gy; az += gz;
+      if (j != i) {                                         // nsc:741
+        if (gx != 0.0) atomicAdd(reaction + 3 * (int64_t)j, -gx);
+        if (gy != 0.0) atomicAdd(reaction + 3 * (int64_t)j + 1, -gy);
+        if (gz != 0.0) atomicAdd(reaction + 3 * (int64_t)j + 2, -gz);
+      }
     }
   }
-  ax = cg::reduce(tile, ax, cg::plus<double>());
-  ay = cg::reduce(tile, ay, cg::plus<double>());
-  az = cg::reduce(tile, az, cg::plus<double>());
-  if (lane == 0) { onto[3 * (int64_t)i] = ax; onto[3 * (int64_t)i + 1] = ay; onto[3 * (int64_t)i + 2] = az; }
+  ax = group_sum(ax); ay = group_sum(ay); az = group_sum(az);
+  if (valid && sub == 0) { onto[3 * (int64_t)i] = ax; onto[3 * (int64_t)i + 1] = ay; onto[3 * (int64_t)i + 2] = az; }
 }
 
 __device__ __forceinline__ double drag_nan_to_num(double v) {
@@ -469,10 +723,67 @@ int launch_drag(sphb200_ctx* ctx, int n, int k, const int32_t* list, const uint3
                 const double* mc, const double* rho, const double* rho_dust, const double* ptype, double* onto,
                 double* reaction, double* visc_accel, cudaStream_t st) {
   CUDA_TRY(cudaMemsetAsync(reaction, 0, (size_t)n * 3 * sizeof(double), st));
-  drag_kernel<HY_G><<<ceil_div(n, HY_THREADS / HY_G), HY_THREADS, 0, st>>>(
-      n, k, list, bufp<double4>(ctx->r0), bufp<double4>(ctx->r1), bufp<double4>(ctx->r2), id, mg, mc, onto, reaction);
+  drag_kernel<<<ceil_div((int64_t)n * HY_G, HY_THREADS), HY_THREADS, 0, st>>>(
+      n, k, list, bufp<RecD>(ctx->recD), bufp<RecP>(ctx->recP), id, mg, mc, onto, reaction);
   drag_apply_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, onto, reaction, rho, rho_dust, ptype, visc_accel);
   ctx->launches += 2;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// uint16 tile-offset rows (+ the escaped rows of the global list, by slot) -> int32 rows in the sorted index
+// space, unordered, missing = n.  For the consumers off the hot path: download of "neighbor", drag, checkpoints.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+expand_list_kernel(int n, int k, const GridSpec* __restrict__ spec, const uint32_t* __restrict__ cell_start,
+                   const uint32_t* __restrict__ keys, const uint16_t* __restrict__ list16, const int32_t* __restrict__ glist,
+                   int32_t* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint16_t* row = list16 + (int64_t)i * k;
+  int32_t* o = out + (int64_t)i * k;
+  const unsigned s0 = row[0];
+  if (s0 == LIST_ESCAPED) {
+    const int slot = (int)row[1] | ((int)row[2] << 16);
+    for (int s = 0; s < k; ++s) o[s] = glist[(int64_t)slot * k + s];
+    return;
+  }
+  if (s0 == LIST_MISSING) { for (int s = 0; s < k; ++s) o[s] = n; return; }
+  const GridSpec g = *spec;
+  const uint32_t key = keys[i];
+  const int cx = key % g.nx, cy = (key / g.nx) % g.ny, cz = key / (g.nx * g.ny);
+  const int gx = cx >> 1, gy = cy >> 1, gz = cz >> 1;
+  const int x0 = max(2 * gx - 1, 0), x1 = min(2 * gx + 2, g.nx - 1);
+  const int y0 = max(2 * gy - 1, 0), y1 = min(2 * gy + 2, g.ny - 1);
+  const int z0 = max(2 * gz - 1, 0), z1 = min(2 * gz + 2, g.nz - 1);
+  const int ysp = y1 - y0 + 1, nrows = ysp * (z1 - z0 + 1);
+  int ps[TILE_MAX_ROWS], toff[TILE_MAX_ROWS + 1];
+  int run = 0;
+  for (int r = 0; r < TILE_MAX_ROWS; ++r) {
+    int rs = 0, re = 0;
+    if (r < nrows) {
+      const int base = ((z0 + r / ysp) * g.ny + (y0 + r % ysp)) * g.nx;
+      rs = (int)cell_start[base + x0]; re = (int)cell_start[base + x1 + 1];
+    }
+    ps[r] = rs & ~1;
+    toff[r] = run;
+    run += (re > rs) ? (((re + 1) & ~1) - ps[r]) : 0;
+  }
+  toff[TILE_MAX_ROWS] = run;
+  for (int s = 0; s < k; ++s) {
+    const int off = row[s];
+    if (off >= (int)LIST_MISSING) { o[s] = n; continue; }
+    int r = 0;
+    while (r < TILE_MAX_ROWS - 1 && off >= toff[r + 1]) ++r;
+    o[s] = ps[r] + (off - toff[r]);
+  }
+}
+
+int launch_expand_list(sphb200_ctx* ctx, int n, int k, const uint16_t* list16, const int32_t* glist, int32_t* out, cudaStream_t st) {
+  expand_list_kernel<<<ceil_div(n, 128), 128, 0, st>>>(n, k, bufp<GridSpec>(ctx->grid_dev), bufp<uint32_t>(ctx->cell_start),
+                                                      bufp<uint32_t>(ctx->keys), list16, glist, out);
+  ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;
 }

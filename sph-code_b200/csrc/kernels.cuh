@@ -2,23 +2,25 @@
 #pragma once
 #include "common.cuh"
 
-// cells.cu
-int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint, cudaStream_t st);
+// cells.cu: cell list on the device; guess = previous k-th distances in SOURCE order (nullptr: none); sync_host
+// copies the chosen grid back to ctx->grid (function-level API only: one host synchronisation)
+int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint, const double* guess, bool sync_host,
+                cudaStream_t st);
 
 // session.cu
 void session_free(sphb200_ctx* ctx);
 
-// knn.cu
+// knn.cu (general kernel: warp per target, any block width)
 int knn_cap_for(int k);
-int launch_knn(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, int32_t* list, double* dists,
+int launch_knn(sphb200_ctx* ctx, int n, int k, double dist, int use_guess, double guess_factor, int32_t* list, double* dists,
                double* h_out, int32_t* nontriv, cudaStream_t st);
-int launch_knn_worklist(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, double guess_factor,
+int launch_knn_worklist(sphb200_ctx* ctx, int n, int k, double dist, int use_guess, double guess_factor,
                         const int* worklist, const int* nwork, int32_t* list, double* dists, double* h_out, int32_t* nontriv,
-                        cudaStream_t st);
-// knn_cell.cu (fast path: one warp per cell, one lane per target, candidates staged by bulk copies)
-int knn_cell_max_k();
-int launch_knn_cell(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, double margin, int32_t* list,
-                    double* dists, double* h_out, int32_t* nontriv, cudaStream_t st);
+                        int by_slot, cudaStream_t st);
+// knn_group.cu (fast path: one CTA per 2x2x2 cell group, candidates staged by bulk copies, fp32 filter + fp64 exact)
+int knn_group_max_k();
+int launch_knn_group(sphb200_ctx* ctx, int n, int k, double dist, int use_guess, double margin, uint16_t* list16,
+                     int32_t* list, double* dists, double* h_out, int32_t* nontriv, cudaStream_t st);
 int launch_knn_unsort(sphb200_ctx* ctx, const int32_t* list, const double* dists, const double* h, const int32_t* nontriv,
                       int n, int k, int64_t* idx_out, double* dist_out, int64_t* nontriv_out, double* h_out,
                       cudaStream_t st);
@@ -34,18 +36,27 @@ struct PackIn {
   const double* mu;         // (N)
   const double* gamma;      // (N)
 };
+// Neighbour rows of a pass.  list16 != nullptr: (N,k) uint16 tile offsets (tile.cuh) for the cell-tiled kernels, and
+// `list` holds the int32 rows of the escaped targets targets[0 .. *ntargets) by slot.  list16 == nullptr: `list`
+// holds (N,k) int32 rows of every particle.
+struct RowsRef {
+  const uint16_t* list16;
+  const int32_t* list;
+  const int* targets;
+  const int* ntargets;
+};
 int launch_pack(sphb200_ctx* ctx, int n, const PackIn& in, cudaStream_t st);
 int launch_convert_list(sphb200_ctx* ctx, const int64_t* nb, int n, int k, int32_t* list, cudaStream_t st);
-int launch_density(sphb200_ctx* ctx, int n, int k, const int32_t* list, double* rho, double* dust, double* num,
-                   cudaStream_t st);
-int launch_pi(sphb200_ctx* ctx, int n, int k, const int32_t* list, const double* rho, cudaStream_t st);
-int launch_repack_pi(sphb200_ctx* ctx, int n, cudaStream_t st);
-int launch_force(sphb200_ctx* ctx, int n, int k, const int32_t* list, const double* rho, const double* mass,
-                 double* hydro_accel, double* visc_accel, double* visc_heat, cudaStream_t st);
+int launch_density(sphb200_ctx* ctx, int n, int k, const RowsRef& rows, double* rho, double* dust, double* num, cudaStream_t st);
+int launch_pi(sphb200_ctx* ctx, int n, int k, const RowsRef& rows, cudaStream_t st);
+int launch_repack(sphb200_ctx* ctx, int n, int what, const double* rho, cudaStream_t st);
+int launch_force(sphb200_ctx* ctx, int n, int k, const RowsRef& rows, const double* mass, double* hydro_accel,
+                 double* visc_accel, double* visc_heat, cudaStream_t st);
 int launch_species(sphb200_ctx* ctx, int n, int k, int S, const int32_t* list, const double* f_un, double* out,
                    cudaStream_t st);
-int launch_crossing_time(sphb200_ctx* ctx, int n, int k, const int32_t* list, const double* vel, const double* sizes,
-                         const double* ptype, double dt_0, double* out_dev, const uint32_t* id, int n_owned, cudaStream_t st);
+int launch_crossing_time(sphb200_ctx* ctx, int n, int k, const RowsRef& rows, const double* vel, const double* sizes,
+                         const double* ptype, double dt_0, double* out_dev, const uint32_t* id, uint32_t n_owned, cudaStream_t st);
+int launch_expand_list(sphb200_ctx* ctx, int n, int k, const uint16_t* list16, const int32_t* glist, int32_t* out, cudaStream_t st);
 
 // loopgen.cu  (loop generation, nsc:673-816)
 struct LoopIn {

@@ -29,10 +29,11 @@ namespace cg = cooperative_groups;
 template <int G>
 __global__ void __launch_bounds__(KNN_THREADS)
 knn_kernel(const double4* __restrict__ r0, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ cell_start,
-           GridSpec g, int n, int k, double dist2, int cap, const double* __restrict__ h_guess, double guess_factor,
+           const GridSpec* __restrict__ spec, int n, int k, double dist2, int cap, int use_guess, double guess_factor,
            int32_t* __restrict__ list, double* __restrict__ dists, double* __restrict__ h_out,
            int32_t* __restrict__ nontriv, int* __restrict__ flags, const int* __restrict__ worklist,
-           const int* __restrict__ nwork) {
+           const int* __restrict__ nwork, int by_slot, const uint32_t* __restrict__ skip_id, uint32_t skip_from) {
+  const GridSpec g = *spec;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cg::thread_block blk = cg::this_thread_block();
   cg::thread_block_tile<G> tile = cg::tiled_partition<G>(blk);
@@ -46,19 +47,25 @@ knn_kernel(const double4* __restrict__ r0, const uint32_t* __restrict__ keys, co
   const int ntarget = worklist ? *nwork : n;
   for (int tgt = blockIdx.x * GROUPS + grp; tgt < ntarget; tgt += gridDim.x * GROUPS) {
   const int i = worklist ? worklist[tgt] : tgt;
+  const int64_t row = (int64_t)(by_slot ? tgt : i) * k;     // session: escaped rows are stored by work-list slot
   const double4 p = r0[i];
   const uint32_t key = keys[i];
   const int cx = key % g.nx, cy = (key / g.nx) % g.ny, cz = key / (g.nx * g.ny);
   const double c3 = g.c * g.c * g.c;
 
   if (!(isfinite(p.x) && isfinite(p.y) && isfinite(p.z))) {   // NaN/inf target: no neighbours (cKDTree raises)
-    for (int s = lane; s < k; s += G) { list[(int64_t)i * k + s] = n; if (dists) dists[(int64_t)i * k + s] = 0.0; }
+    for (int s = lane; s < k; s += G) { list[row + s] = n; if (dists) dists[row + s] = 0.0; }
     if (lane == 0) { nontriv[i] = 0; h_out[i] = 0.0; atomicAdd(&flags[FL_KNN_NONFINITE], 1); }
+    continue;
+  }
+  if (skip_id && skip_id[i] >= skip_from) {                   // ghost of a slab decomposition: an empty, well-defined row
+    for (int s = lane; s < k; s += G) { list[row + s] = n; if (dists) dists[row + s] = 0.0; }
+    if (lane == 0) { nontriv[i] = 0; h_out[i] = p.w; }
     continue;
   }
   int m = 1;
   double R2try = -1.0;
-  if (h_guess) { double hg = h_guess[i] * guess_factor; if (hg > 0.0) { R2try = hg * hg; m = (int)(hg * g.inv_c) + 1; } }
+  if (use_guess) { double hg = p.w * guess_factor; if (hg > 0.0) { R2try = hg * hg; m = (int)fmin(hg * g.inv_c, 1.0e6) + 1; } }
   int count = 0;
   bool done = false;
   int iter = 0, rescans = -1, widened = 0;
@@ -156,7 +163,6 @@ knn_kernel(const double4* __restrict__ r0, const uint32_t* __restrict__ keys, co
     const double R2lim = whole ? dist2 : fmin(dist2, rsafe * rsafe);
     const int ysp = y1 - y0 + 1;
     const int nrows = ysp * (z1 - z0 + 1);
-    const int64_t row = (int64_t)i * k;
     unsigned long long last_k = 0ull; int last_j = -1;
     int nsel = 0;
     for (; nsel < k; ++nsel) {
@@ -199,7 +205,6 @@ knn_kernel(const double4* __restrict__ r0, const uint32_t* __restrict__ keys, co
   if (count > cap) count = cap;
   // ---- rank by counting; rank < k are the neighbours, in ascending (d^2, index) order ----
   const int nsel = count < k ? count : k;
-  const int64_t row = (int64_t)i * k;
   for (int e = lane; e < count; e += G) {
     const unsigned long long ke = keybuf[e];
     const int je = idxbuf[e];
@@ -233,8 +238,8 @@ int knn_cap_for(int k) {
   return cap;
 }
 
-static int launch_knn_impl(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, double guess_factor, int32_t* list, double* dists,
-                           double* h_out, int32_t* nontriv, const int* worklist, const int* nwork, cudaStream_t st) {
+static int launch_knn_impl(sphb200_ctx* ctx, int n, int k, double dist, int use_guess, double guess_factor, int32_t* list, double* dists,
+                           double* h_out, int32_t* nontriv, const int* worklist, const int* nwork, int by_slot, cudaStream_t st) {
   if (k < 1) SPH_FAIL("knn: k must be >= 1");
   const int cap = knn_cap_for(k);
   const int G = ctx->knn_group;
@@ -252,8 +257,9 @@ static int launch_knn_impl(sphb200_ctx* ctx, int n, int k, double dist, const do
   do {                                                                                                         \
     if (smem > 48 * 1024)                                                                                      \
       CUDA_TRY(cudaFuncSetAttribute(knn_kernel<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));  \
-    knn_kernel<GG><<<blocks, KNN_THREADS, smem, st>>>(r0, keys, cs, ctx->grid, n, k, dist2, cap, h_guess, guess_factor, list, \
-                                                      dists, h_out, nontriv, flags, worklist, nwork);          \
+    knn_kernel<GG><<<blocks, KNN_THREADS, smem, st>>>(r0, keys, cs, bufp<GridSpec>(ctx->grid_dev), n, k, dist2, cap, use_guess, \
+                                                      guess_factor, list, dists, h_out, nontriv, flags, worklist, nwork, by_slot, \
+                                                      ctx->skip_id, ctx->skip_from);                           \
   } while (0)
   if (G == 32) KNN_LAUNCH(32);
   else if (G == 16) KNN_LAUNCH(16);
@@ -265,17 +271,18 @@ static int launch_knn_impl(sphb200_ctx* ctx, int n, int k, double dist, const do
   return 0;
 }
 
-int launch_knn(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, int32_t* list, double* dists,
+int launch_knn(sphb200_ctx* ctx, int n, int k, double dist, int use_guess, double guess_factor, int32_t* list, double* dists,
                double* h_out, int32_t* nontriv, cudaStream_t st) {
-  return launch_knn_impl(ctx, n, k, dist, h_guess, 1.0, list, dists, h_out, nontriv, nullptr, nullptr, st);
+  return launch_knn_impl(ctx, n, k, dist, use_guess, guess_factor, list, dists, h_out, nontriv, nullptr, nullptr, 0, st);
 }
 
-// h_guess (may be nullptr): previous k-th distances; the first trial radius is guess * guess_factor, which
-// sizes the block and normally settles the target in one scan
-int launch_knn_worklist(sphb200_ctx* ctx, int n, int k, double dist, const double* h_guess, double guess_factor,
+// use_guess: the records carry the previous k-th distances (r0[i].w); the first trial radius is guess *
+// guess_factor, which sizes the block and normally settles the target in one scan.  by_slot: row of work-list
+// entry t goes to list[t * k] (session: the global list holds only the escaped rows) instead of list[i * k].
+int launch_knn_worklist(sphb200_ctx* ctx, int n, int k, double dist, int use_guess, double guess_factor,
                         const int* worklist, const int* nwork, int32_t* list, double* dists, double* h_out, int32_t* nontriv,
-                        cudaStream_t st) {
-  return launch_knn_impl(ctx, n, k, dist, h_guess, guess_factor, list, dists, h_out, nontriv, worklist, nwork, st);
+                        int by_slot, cudaStream_t st) {
+  return launch_knn_impl(ctx, n, k, dist, use_guess, guess_factor, list, dists, h_out, nontriv, worklist, nwork, by_slot, st);
 }
 
 // Sorted-space rows -> the reference's return layout (original particle order, int64 indices,

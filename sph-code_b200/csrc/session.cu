@@ -5,7 +5,7 @@
 #include "common.cuh"
 #include "kernels.cuh"
 #include "../../include/sphb200.h"
-#include <cub/cub.cuh>
+#include "tile.cuh"
 #include <float.h>
 #include <math.h>
 #include <new>
@@ -514,14 +514,29 @@ perturb_kernel(int n, const uint32_t* __restrict__ id, int n_owned, double amp, 
     pos[3 * (int64_t)i + c] = __dadd_rn(pos[3 * (int64_t)i + c], __dmul_rn(amp, perturb_unit(g, c, seed)));
 }
 
+#define SB_XLIST 45          // int32 rows of every particle expanded from the uint16 tile rows (download, drag)
+
+// neighbour rows of the last search, in the form the passes take them (kernels.cuh RowsRef)
+static RowsRef rows_of(sphb200_ctx* ctx) {
+  RowsRef r;
+  if (ctx->list_is_global) { r.list16 = nullptr; r.list = bufp<int32_t>(ctx->list); r.targets = nullptr; r.ntargets = nullptr; }
+  else {
+    r.list16 = bufp<uint16_t>(ctx->list16); r.list = bufp<int32_t>(ctx->list);
+    r.targets = bufp<int>(ctx->worklist); r.ntargets = bufp<int>(ctx->flags) + FL_KNN_NWORK;
+  }
+  return r;
+}
+// (N,k) int32 rows of every particle in the sorted index space (unordered, missing = n): off the hot path
+static int full_rows(sphb200_ctx* ctx, cudaStream_t st, const int32_t** out);
+
 // ------------------------------------------------------------------------------------------------
 static int phase_crossing(sphb200_ctx* ctx, cudaStream_t st) {
   Session& s = sess(ctx);
   double* scal = bufp<double>(ctx->scal);
   if (!s.has_list) SPH_FAIL("session: no neighbour list yet (call startup first)");
-  return launch_crossing_time(ctx, (int)s.n, s.k, bufp<int32_t>(ctx->list), fld(ctx, F_VEL), fld(ctx, F_H),
+  return launch_crossing_time(ctx, (int)s.n, s.k, rows_of(ctx), fld(ctx, F_VEL), fld(ctx, F_H),
                               fld(ctx, F_TYPE), s.sc.dt_0, scal + SC_CT,
-                              s.n_owned >= 0 ? bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]) : nullptr, (int)s.n_owned, st);
+                              s.n_owned >= 0 ? bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]) : nullptr, (uint32_t)s.n_owned, st);
 }
 
 static int phase_dt_clamp(sphb200_ctx* ctx, cudaStream_t st) {
@@ -540,7 +555,8 @@ static int phase_dt_clamp(sphb200_ctx* ctx, cudaStream_t st) {
 // straight into the new order while the search runs (uploads gather through the current `id`).
 static int phase_sort(sphb200_ctx* ctx, cudaStream_t st, unsigned mask = ~0u) {
   Session& s = sess(ctx);
-  SPH_TRY(build_cells(ctx, fld(ctx, F_POS), s.n, ctx->cell_edge, st));
+  // the previous k-th distances (still in the old order) ride into the sorted records as the next trial radii
+  SPH_TRY(build_cells(ctx, fld(ctx, F_POS), s.n, ctx->cell_edge, bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]), false, st));
   ReorderArgs a;
   for (int f = 0; f < F_NFIELDS; ++f) { a.src[f] = fld(ctx, f, 0); a.dst[f] = fld(ctx, f, 1); }
   a.id_src = bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]);
@@ -563,14 +579,17 @@ static int phase_knn(sphb200_ctx* ctx, cudaStream_t st) {
   Session& s = sess(ctx);
   SPH_TRY(devbuf_reserve(ctx->list, (size_t)s.n * s.k * sizeof(int32_t)));
   double* knnh = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]);
-  // previous k-th distance (reordered with the state) as the first trial radius; zeros before start-up
-  const double* guess = s.use_guess ? knnh : nullptr;
-  if (ctx->knn_fast && s.k <= knn_cell_max_k())
-    SPH_TRY(launch_knn_cell(ctx, (int)s.n, s.k, s.dist, guess, ctx->knn_margin, bufp<int32_t>(ctx->list), nullptr,
-                            fld(ctx, F_H), bufp<int32_t>(ctx->sbuf[SB_NONTRIV]), st));
-  else
-    SPH_TRY(launch_knn(ctx, (int)s.n, s.k, s.dist, nullptr, bufp<int32_t>(ctx->list), nullptr, fld(ctx, F_H),
-                       bufp<int32_t>(ctx->sbuf[SB_NONTRIV]), st));
+  // previous k-th distance (in the sorted records, r0.w) as the first trial radius; zeros before start-up
+  if (ctx->knn_fast && s.k >= 3 && s.k <= knn_group_max_k()) {
+    SPH_TRY(devbuf_reserve(ctx->list16, (size_t)s.n * s.k * sizeof(uint16_t) + 64));
+    SPH_TRY(launch_knn_group(ctx, (int)s.n, s.k, s.dist, s.use_guess, ctx->knn_margin, bufp<uint16_t>(ctx->list16),
+                             bufp<int32_t>(ctx->list), nullptr, fld(ctx, F_H), bufp<int32_t>(ctx->sbuf[SB_NONTRIV]), st));
+    ctx->list_is_global = 0;
+  } else {
+    SPH_TRY(launch_knn(ctx, (int)s.n, s.k, s.dist, s.use_guess, 1.0 + ctx->knn_margin, bufp<int32_t>(ctx->list), nullptr,
+                       fld(ctx, F_H), bufp<int32_t>(ctx->sbuf[SB_NONTRIV]), st));
+    ctx->list_is_global = 1;
+  }
   copy_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>(s.n, fld(ctx, F_H), knnh);
   ctx->launches += 1;
   s.has_list = 1;
@@ -586,20 +605,22 @@ static int phase_pack(sphb200_ctx* ctx, cudaStream_t st) {
 }
 static int phase_density(sphb200_ctx* ctx, cudaStream_t st) {
   Session& s = sess(ctx);
-  return launch_density(ctx, (int)s.n, s.k, bufp<int32_t>(ctx->list), outp(ctx, O_RHO), outp(ctx, O_DUST), outp(ctx, O_NUM), st);
+  return launch_density(ctx, (int)s.n, s.k, rows_of(ctx), outp(ctx, O_RHO), outp(ctx, O_DUST), outp(ctx, O_NUM), st);
 }
 static int phase_pi(sphb200_ctx* ctx, cudaStream_t st) {
   Session& s = sess(ctx);
-  return launch_pi(ctx, (int)s.n, s.k, bufp<int32_t>(ctx->list), outp(ctx, O_RHO), st);
+  return launch_pi(ctx, (int)s.n, s.k, rows_of(ctx), st);
 }
 static int phase_force(sphb200_ctx* ctx, cudaStream_t st) {
   Session& s = sess(ctx);
-  SPH_TRY(launch_force(ctx, (int)s.n, s.k, bufp<int32_t>(ctx->list), outp(ctx, O_RHO), fld(ctx, F_MASS), outp(ctx, O_HACC),
-                       outp(ctx, O_VACC), outp(ctx, O_HEAT), st));
+  SPH_TRY(launch_force(ctx, (int)s.n, s.k, rows_of(ctx), fld(ctx, F_MASS), outp(ctx, O_HACC), outp(ctx, O_VACC),
+                       outp(ctx, O_HEAT), st));
   if (!s.drag) return 0;
   SPH_TRY(devbuf_reserve(ctx->sbuf[SB_ONTO], (size_t)s.n * 3 * sizeof(double)));      // code_running.py:455,462-463,473
   SPH_TRY(devbuf_reserve(ctx->sbuf[SB_REACT], (size_t)s.n * 3 * sizeof(double)));
-  return launch_drag(ctx, (int)s.n, s.k, bufp<int32_t>(ctx->list), bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]),
+  const int32_t* full = nullptr;
+  SPH_TRY(full_rows(ctx, st, &full));
+  return launch_drag(ctx, (int)s.n, s.k, full, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]),
                      bufp<double>(ctx->sbuf[SB_GM]), bufp<double>(ctx->sbuf[SB_GC]), outp(ctx, O_RHO), outp(ctx, O_DUST),
                      fld(ctx, F_TYPE), bufp<double>(ctx->sbuf[SB_ONTO]), bufp<double>(ctx->sbuf[SB_REACT]),
                      outp(ctx, O_VACC), st);
@@ -701,10 +722,20 @@ struct SkipGhosts {
   void refresh() {
     Session& s = sess(ctx);
     ctx->skip_id = (s.n_owned >= 0 && s.n_owned < s.n) ? bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]) : nullptr;
-    ctx->skip_from = (int)s.n_owned;
+    ctx->skip_from = (uint32_t)s.n_owned;
   }
   ~SkipGhosts() { ctx->skip_id = nullptr; }
 };
+
+static int full_rows(sphb200_ctx* ctx, cudaStream_t st, const int32_t** out) {
+  Session& s = sess(ctx);
+  if (ctx->list_is_global) { *out = bufp<int32_t>(ctx->list); return 0; }
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_XLIST], (size_t)s.n * s.k * sizeof(int32_t)));
+  SPH_TRY(launch_expand_list(ctx, (int)s.n, s.k, bufp<uint16_t>(ctx->list16), bufp<int32_t>(ctx->list),
+                             bufp<int32_t>(ctx->sbuf[SB_XLIST]), st));
+  *out = bufp<int32_t>(ctx->sbuf[SB_XLIST]);
+  return 0;
+}
 
 extern "C" {
 
@@ -840,6 +871,7 @@ int sphb200_session_upload(sphb200_ctx* ctx, const char* name, const void* src, 
     ctx->launches += 1;
     CUDA_TRY(cudaGetLastError());
     s.has_list = 1;
+    ctx->list_is_global = 1;                          // restored rows are plain int32 rows: the passes take the LIST form
     return 0;
   }
   const int f = find_field(name);
@@ -850,7 +882,8 @@ int sphb200_session_upload(sphb200_ctx* ctx, const char* name, const void* src, 
   const uint32_t* id = bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]);
   sort_in_kernel<<<ceil_div(count, 256), 256, 0, st>>>((int)s.n, w, id, (const double*)src, dstp);
   ctx->launches += 1;
-  if (!strcmp(name, "visc_pi")) SPH_TRY(launch_repack_pi(ctx, (int)s.n, st));   // force-pass coefficients follow Pi
+  if (!strcmp(name, "visc_pi")) SPH_TRY(launch_repack(ctx, (int)s.n, 1, nullptr, st));   // force-pass coefficients follow Pi
+  if (!strcmp(name, "densities")) SPH_TRY(launch_repack(ctx, (int)s.n, 0, outp(ctx, O_RHO), st));   // the Pi pass reads rho from the records
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -873,8 +906,9 @@ int sphb200_session_download(sphb200_ctx* ctx, const char* name, void* dst, int6
   if (!strcmp(name, "neighbor")) {
     if (!s.has_list) SPH_FAIL("session_download: no neighbour list");
     if (count != s.n * s.k) SPH_FAIL("session_download: neighbor needs %lld values", (long long)(s.n * s.k));
-    unsort_list_sorted_kernel<<<ceil_div(n, 128), 128, 0, st>>>(n, s.k, id, bufp<int32_t>(ctx->list), bufp<double4>(ctx->r0),
-                                                              (int64_t*)dst);
+    const int32_t* full = nullptr;
+    SPH_TRY(full_rows(ctx, st, &full));
+    unsort_list_sorted_kernel<<<ceil_div(n, 128), 128, 0, st>>>(n, s.k, id, full, bufp<double4>(ctx->r0), (int64_t*)dst);
   } else if (!strcmp(name, "scalars")) {               // raw device scalars: [6] ct, [7] dt, [8] d, [9] age, [10] max_dist, [11] n_slow
     if (count < 0 || count > SC_COUNT) SPH_FAIL("session_download: scalars holds %d values", SC_COUNT);
     CUDA_TRY(cudaMemcpyAsync(dst, ctx->scal.p, (size_t)count * sizeof(double), cudaMemcpyDeviceToDevice, st));
@@ -919,7 +953,8 @@ static int field_at(sphb200_ctx* ctx, const char* name, const int64_t* idx, int6
   else gather_at_kernel<<<ceil_div(count * w, 256), 256, 0, st>>>(count, w, (int)s.n, idx, pos, p, buf, bufp<int>(ctx->flags));
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
-  if (scatter && !strcmp(name, "visc_pi")) SPH_TRY(launch_repack_pi(ctx, (int)s.n, st));
+  if (scatter && !strcmp(name, "visc_pi")) SPH_TRY(launch_repack(ctx, (int)s.n, 1, nullptr, st));
+  if (scatter && !strcmp(name, "densities")) SPH_TRY(launch_repack(ctx, (int)s.n, 0, outp(ctx, O_RHO), st));
   return 0;
 }
 
