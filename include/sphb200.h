@@ -158,6 +158,25 @@ int sphb200_session_startup(sphb200_ctx* ctx, void* stream);
 /* one pass of the while-body, code_running.py:217-540 (gas/dust only, gravity and chemistry zero; drag as
  * set by sphb200_session_set_drag, off by default) */
 int sphb200_session_step(sphb200_ctx* ctx, void* stream);
+/* ---- slab decomposition on the device (the reference has only independent replicas,
+ * sph/code_script_3.sl:19).  domain.py drives the collectives; these entry points keep everything N-sized on
+ * the GPU.  Rows are NCOL >= 19 doubles: the 17 state columns, the k-NN trial radius, the global particle id.
+ *   enable_gid      the session carries a global id per particle (column 18 of uploaded / downloaded rows);
+ *   migrate_pack    phase 0: classify against the slab faces bounds[0..world] (device), counts_out (device
+ *                   int32[world + 1]) = movers per destination rank, then the number of particles that stay;
+ *                   phase 1: drop the ghosts, write the movers to rows_out grouped by destination, compact the
+ *                   rest (caller index = compacted position); then call set_count(kept, kept);
+ *   receive_rows    append rows from other ranks as owned particles (movers) or as ghosts;
+ *   halo_pack       phase 0: count the owned particles within w of every other rank's slab (counts_out int32[world]);
+ *                   phase 1: pack them as rows grouped by destination, with their caller indices in idx_out (the
+ *                   send lists later ghost refreshes gather at with sphb200_session_gather). */
+int sphb200_session_enable_gid(sphb200_ctx* ctx);
+int sphb200_session_migrate_pack(sphb200_ctx* ctx, int phase, const double* bounds, int world, int rank, double* rows_out,
+                                 int64_t cap_rows, int ncol, int* counts_out, void* stream);
+int sphb200_session_set_count(sphb200_ctx* ctx, int64_t n, int64_t n_owned);
+int sphb200_session_receive_rows(sphb200_ctx* ctx, const double* rows, int64_t n_new, int ncol, int as_ghosts, void* stream);
+int sphb200_session_halo_pack(sphb200_ctx* ctx, int phase, const double* bounds, int world, int rank, double w, double* rows_out,
+                              int64_t* idx_out, int64_t cap_rows, int ncol, int* counts_out, void* stream);
 /* Synthetic motion for the measured workloads and the moving-particle parity tests (the reference has no
  * counterpart: its own step cannot displace particles by a sizeable fraction of h and stay finite, DESIGN.md
  * section 2): points[i] += amplitude * u(id_i, seed), u uniform in [-1,1)^3, a pure function of the particle's

@@ -48,6 +48,11 @@ SIGNATURES = {
     "sphb200_session_upload_rows": [c_ptr, c_ptr, c_i64, c_int, c_ptr],
     "sphb200_session_startup": [c_ptr, c_ptr],
     "sphb200_session_step": [c_ptr, c_ptr],
+    "sphb200_session_enable_gid": [c_ptr],
+    "sphb200_session_migrate_pack": [c_ptr, c_int, c_ptr, c_int, c_int, c_ptr, c_i64, c_int, c_ptr, c_ptr],
+    "sphb200_session_set_count": [c_ptr, c_i64, c_i64],
+    "sphb200_session_receive_rows": [c_ptr, c_ptr, c_i64, c_int, c_int, c_ptr],
+    "sphb200_session_halo_pack": [c_ptr, c_int, c_ptr, c_int, c_int, c_dbl, c_ptr, c_ptr, c_i64, c_int, c_ptr, c_ptr],
     "sphb200_session_perturb": [c_ptr, c_dbl, ctypes.c_uint64, c_ptr],
     "sphb200_session_scalar": [c_ptr, ctypes.c_char_p, ctypes.POINTER(c_dbl), c_ptr],
     "sphb200_session_set_scalar": [c_ptr, ctypes.c_char_p, c_dbl],

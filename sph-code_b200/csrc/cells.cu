@@ -140,8 +140,8 @@ cell_key_kernel(const double* __restrict__ pts, int64_t n, const GridSpec* __res
 
 // ---- exclusive scan of counts[0 .. ncells] in place (three small kernels, fixed launch sizes) ----
 __global__ void __launch_bounds__(256)
-scan_tiles_kernel(const GridSpec* __restrict__ spec, uint32_t* __restrict__ a, uint32_t* __restrict__ tops) {
-  const int m = spec->ncells + 1;
+scan_tiles_kernel(const GridSpec* __restrict__ spec, int m_host, uint32_t* __restrict__ a, uint32_t* __restrict__ tops) {
+  const int m = spec ? spec->ncells + 1 : m_host;
   const int base = blockIdx.x * SCAN_TILE;
   if (base >= m) return;
   __shared__ uint32_t wsum[8];
@@ -171,8 +171,8 @@ scan_tiles_kernel(const GridSpec* __restrict__ spec, uint32_t* __restrict__ a, u
     before += v[q];
   }
 }
-__global__ void __launch_bounds__(1024) scan_tops_kernel(const GridSpec* __restrict__ spec, uint32_t* __restrict__ tops) {
-  const int ntiles = (spec->ncells + 1 + SCAN_TILE - 1) / SCAN_TILE;
+__global__ void __launch_bounds__(1024) scan_tops_kernel(const GridSpec* __restrict__ spec, int m_host, uint32_t* __restrict__ tops) {
+  const int ntiles = ((spec ? spec->ncells + 1 : m_host) + SCAN_TILE - 1) / SCAN_TILE;
   __shared__ uint32_t wsum[32];
   __shared__ uint32_t carry_s;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -208,8 +208,8 @@ __global__ void __launch_bounds__(1024) scan_tops_kernel(const GridSpec* __restr
   }
 }
 __global__ void __launch_bounds__(256)
-scan_add_kernel(const GridSpec* __restrict__ spec, uint32_t* __restrict__ a, const uint32_t* __restrict__ tops) {
-  const int m = spec->ncells + 1;
+scan_add_kernel(const GridSpec* __restrict__ spec, int m_host, uint32_t* __restrict__ a, const uint32_t* __restrict__ tops) {
+  const int m = spec ? spec->ncells + 1 : m_host;
   const int base = blockIdx.x * SCAN_TILE;
   if (base >= m) return;
   const uint32_t add = tops[blockIdx.x];
@@ -287,6 +287,19 @@ gather_pos_kernel(const double* __restrict__ pts, const uint32_t* __restrict__ p
   r0[i] = make_double4(pts[3 * p], pts[3 * p + 1], pts[3 * p + 2], guess ? guess[p] : 0.0);
 }
 
+// in-place exclusive scan of a[0 .. m) (host-known length); a[m] is not touched
+int scan_exclusive_u32(sphb200_ctx* ctx, uint32_t* a, int m, cudaStream_t st) {
+  if (m <= 0) return 0;
+  const int blocks = ceil_div(m, SCAN_TILE);
+  SPH_TRY(devbuf_reserve(ctx->scan_tops, ((size_t)blocks + 1) * sizeof(uint32_t)));
+  scan_tiles_kernel<<<blocks, 256, 0, st>>>(nullptr, m, a, bufp<uint32_t>(ctx->scan_tops));
+  scan_tops_kernel<<<1, 1024, 0, st>>>(nullptr, m, bufp<uint32_t>(ctx->scan_tops));
+  scan_add_kernel<<<blocks, 256, 0, st>>>(nullptr, m, a, bufp<uint32_t>(ctx->scan_tops));
+  ctx->launches += 3;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
 int devbuf_reserve(DevBuf& b, size_t bytes) {
   if (bytes <= b.bytes) return 0;
   if (b.p) { cudaFree(b.p); b.p = nullptr; b.bytes = 0; }
@@ -336,9 +349,9 @@ int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint
   grid_choose_kernel<<<1, 256, 0, st>>>(part, bb_blocks, n, ctx->cell_occ, edge_hint, max_cells, spec, scal + SC_BBOX);
   zero_counts_kernel<<<148 * 4, 256, 0, st>>>(spec, cs);
   cell_key_kernel<<<nblk, 256, 0, st>>>(pts, n, spec, keys_src, rank, cs);
-  scan_tiles_kernel<<<scan_blocks, 256, 0, st>>>(spec, cs, bufp<uint32_t>(ctx->scan_tops));
-  scan_tops_kernel<<<1, 1024, 0, st>>>(spec, bufp<uint32_t>(ctx->scan_tops));
-  scan_add_kernel<<<scan_blocks, 256, 0, st>>>(spec, cs, bufp<uint32_t>(ctx->scan_tops));
+  scan_tiles_kernel<<<scan_blocks, 256, 0, st>>>(spec, 0, cs, bufp<uint32_t>(ctx->scan_tops));
+  scan_tops_kernel<<<1, 1024, 0, st>>>(spec, 0, bufp<uint32_t>(ctx->scan_tops));
+  scan_add_kernel<<<scan_blocks, 256, 0, st>>>(spec, 0, cs, bufp<uint32_t>(ctx->scan_tops));
   scan_guard_kernel<<<1, 1, 0, st>>>(spec, cs);
   scatter_kernel<<<nblk, 256, 0, st>>>(n, keys_src, rank, cs, bufp<uint32_t>(ctx->perm), bufp<uint32_t>(ctx->keys));
   cell_order_kernel<<<148 * 4, 256, 0, st>>>(spec, cs, bufp<uint32_t>(ctx->perm), rank);

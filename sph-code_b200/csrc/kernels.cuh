@@ -7,6 +7,8 @@
 int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint, const double* guess, bool sync_host,
                 cudaStream_t st);
 
+int scan_exclusive_u32(sphb200_ctx* ctx, uint32_t* a, int m, cudaStream_t st);
+
 // session.cu
 void session_free(sphb200_ctx* ctx);
 

@@ -31,6 +31,8 @@ static const char* kOutName[O_NOUT] = {"densities", "num_densities", "dust_densi
 #define SB_GC 41
 #define SB_ONTO 42           // drag: accel_onto, accel_reaction (sorted order, scratch of the force phase)
 #define SB_REACT 43
+#define SB_GID 46            // slab decomposition: global particle id (double), travels with the particle
+#define SB_GID_ALT 47
 
 struct SessionScalars {      // host mirror of the run parameters
   double dt_0, max_age, n_int, raise_factor, au;
@@ -50,6 +52,8 @@ struct Session {
   int grown = 0;             // particles were appended since the last kick: the old arrays have the old
                              // length, so this step takes dv = a dt (:485) and new_smoothing = 1 (:535)
   int64_t n_owned = -1;      // slab decomposition: caller indices >= n_owned are ghosts (-1: none)
+  int has_gid = 0;           // SB_GID holds global ids (rows carry them in column 18)
+  int gid_cur = 0;
   SessionScalars sc;
 };
 // The session belongs to its context (ctx->session): two contexts on one GPU are two independent runs.
@@ -99,6 +103,7 @@ struct ReorderArgs {
   double* dst[F_NFIELDS];
   const uint32_t* id_src; uint32_t* id_dst;
   const double* knnh_src; double* knnh_dst;
+  const double* gid_src; double* gid_dst;     // nullptr: the session carries no global ids
 };
 
 __global__ void __launch_bounds__(256) reorder_kernel(int n, const uint32_t* __restrict__ perm, ReorderArgs a, unsigned mask) {
@@ -116,6 +121,7 @@ __global__ void __launch_bounds__(256) reorder_kernel(int n, const uint32_t* __r
   for (int f = 3; f < F_NFIELDS; ++f) if (mask >> f & 1u) a.dst[f][i] = a.src[f][p];
   a.id_dst[i] = a.id_src[p];
   a.knnh_dst[i] = a.knnh_src[p];
+  if (a.gid_src) a.gid_dst[i] = a.gid_src[p];
 }
 
 __global__ void __launch_bounds__(256) iota_kernel(int n, uint32_t* id, uint32_t first = 0) {
@@ -169,7 +175,7 @@ integrate_kernel(int n, const double* __restrict__ scal, double kB, double m_h, 
     const double e = nan_to_num_d(E[i]) + nan_to_num_d(heat[i] * dt);            // :490
     E[i] = e;
     T[i] = nan_to_num_d(e * (mu[i] * m_h) / (gamma[i] * mass[i] * kB));          // :491
-    slow = (v2 < 80000.0 * 80000.0) && (!id || (int)id[i] < n_owned);            // :493 (ghosts belong to their owner)
+    slow = (v2 < 80000.0 * 80000.0) && (!id || id[i] < (uint32_t)n_owned);            // :493 (ghosts belong to their owner)
     distsq[i] = slow ? x2 : INFINITY;
   }
   const int cnt = __syncthreads_count(slow);
@@ -431,7 +437,8 @@ scatter_at_kernel(int64_t count, int w, int n, const int64_t* __restrict__ cidx,
 // Whole particle rows (AoS, `ncol` doubles per particle: the eleven state fields in kFieldName order,
 // then the k-NN trial radius) <-> the session's sorted struct of arrays, in one pass.  The slab
 // decomposition moves particles between ranks as such rows (domain.py).
-struct RowArgs { double* f[F_NFIELDS]; double* knnh; const double* tag; };   // tag: optional caller-order column 18
+struct RowArgs { double* f[F_NFIELDS]; double* knnh; const double* tag; double* gid; };   // tag: optional caller-order column 18;
+                                                                                         // gid: session-order global ids <-> column 18
 #define ROW_STATE_COLS 18
 
 // One warp per 32 sorted particles: the 18 values of each particle are read field by field (coalesced)
@@ -453,12 +460,14 @@ rows_out_kernel(int n, int64_t n_rows, int ncol, const uint32_t* __restrict__ id
 #pragma unroll
     for (int f = 3; f < F_NFIELDS; ++f) tile[warp][lane][col++] = a.f[f][i];
     tile[warp][lane][col] = a.knnh[i];
+    if (a.gid) tile[warp][lane][ROW_STATE_COLS] = a.gid[i];
   }
   __syncwarp();
   for (int r = 0; r < 32; ++r) {
     const int64_t cr = __shfl_sync(0xffffffffu, c, r);
     if (cr >= 0 && cr < n_rows) {
       if (lane < ROW_STATE_COLS) dst[cr * ncol + lane] = tile[warp][r][lane];
+      else if (lane == ROW_STATE_COLS && a.gid && ncol > ROW_STATE_COLS) dst[cr * ncol + ROW_STATE_COLS] = tile[warp][r][ROW_STATE_COLS];
       else if (lane == ROW_STATE_COLS && a.tag) dst[cr * ncol + ROW_STATE_COLS] = a.tag[cr];
     }
   }
@@ -476,7 +485,7 @@ rows_in_kernel(int n, int ncol, const uint32_t* __restrict__ id, const double* _
   if (n_rows >= 0) c = (c >= first && c < first + n_rows) ? c - first : -1;  // only the caller indices [first, first + n_rows)
   for (int r = 0; r < 32; ++r) {
     const int64_t cr = __shfl_sync(0xffffffffu, c, r);
-    if (cr >= 0 && lane < ROW_STATE_COLS) tile[warp][r][lane] = src[cr * ncol + lane];
+    if (cr >= 0 && lane < ROW_STATE_COLS + ((a.gid && ncol > ROW_STATE_COLS) ? 1 : 0)) tile[warp][r][lane] = src[cr * ncol + lane];
   }
   __syncwarp();
   if (i < n && c >= 0) {
@@ -487,6 +496,7 @@ rows_in_kernel(int n, int ncol, const uint32_t* __restrict__ id, const double* _
 #pragma unroll
     for (int f = 3; f < F_NFIELDS; ++f) a.f[f][i] = tile[warp][lane][col++];
     a.knnh[i] = tile[warp][lane][col];
+    if (a.gid && ncol > ROW_STATE_COLS) a.gid[i] = tile[warp][lane][ROW_STATE_COLS];
   }
 }
 
@@ -504,11 +514,12 @@ __host__ __device__ __forceinline__ double perturb_unit(unsigned long long g, in
   return (double)(z >> 11) * (1.0 / 4503599627370496.0) - 1.0;      // (z >> 11) 2^-52 - 1, exact
 }
 __global__ void __launch_bounds__(256)
-perturb_kernel(int n, const uint32_t* __restrict__ id, int n_owned, double amp, unsigned long long seed, double* __restrict__ pos) {
+perturb_kernel(int n, const uint32_t* __restrict__ id, const double* __restrict__ gid, int n_owned, double amp,
+               unsigned long long seed, double* __restrict__ pos) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const uint32_t g = id[i];
-  if (n_owned >= 0 && (int)g >= n_owned) return;                     // ghosts follow their owners
+  if (n_owned >= 0 && id[i] >= (uint32_t)n_owned) return;              // ghosts follow their owners
+  const unsigned long long g = gid ? (unsigned long long)gid[i] : (unsigned long long)id[i];   // slabs: the GLOBAL id
 #pragma unroll
   for (int c = 0; c < 3; ++c)
     pos[3 * (int64_t)i + c] = __dadd_rn(pos[3 * (int64_t)i + c], __dmul_rn(amp, perturb_unit(g, c, seed)));
@@ -528,6 +539,131 @@ static RowsRef rows_of(sphb200_ctx* ctx) {
 }
 // (N,k) int32 rows of every particle in the sorted index space (unordered, missing = n): off the hot path
 static int full_rows(sphb200_ctx* ctx, cudaStream_t st, const int32_t** out);
+
+
+// ------------------------------------------------------------------------------------------------
+// Slab decomposition on the device (domain.py drives the collectives; nothing N-sized leaves the GPU).
+// Rows travel as NCOL = 19 doubles: the 17 state columns, the k-NN trial radius, the global id.
+// ------------------------------------------------------------------------------------------------
+#define MIG_MAX_WORLD 64
+struct MigScratch { int cnt[MIG_MAX_WORLD]; int base[MIG_MAX_WORLD + 1]; int fill[MIG_MAX_WORLD]; int n_keep; int overflow; };
+
+__device__ __forceinline__ int slab_of(double x, const double* __restrict__ bounds, int world, int self) {
+  if (!(x == x)) return self;                              // NaN stays where it is
+  int r = 0;
+  while (r < world - 1 && x >= bounds[r + 1]) ++r;         // x == face belongs to the upper slab
+  return r;
+}
+
+__global__ void mig_reset_kernel(MigScratch* m) {
+  const int t = threadIdx.x;
+  if (t < MIG_MAX_WORLD) { m->cnt[t] = 0; m->fill[t] = 0; }
+  if (t == 0) { m->n_keep = 0; m->overflow = 0; }
+}
+
+// pass 1: keep flag of every particle (owned and still inside this rank's slab), movers counted per destination
+__global__ void __launch_bounds__(256)
+mig_classify_kernel(int n, const uint32_t* __restrict__ id, uint32_t n_owned, const double* __restrict__ pos,
+                    const double* __restrict__ bounds, int world, int rank, uint32_t* __restrict__ flag,
+                    uint32_t* __restrict__ slot, MigScratch* m) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const bool owned = id[i] < n_owned;
+  int keep = 0;
+  if (owned) {
+    const int dest = slab_of(pos[3 * (int64_t)i], bounds, world, rank);
+    if (dest == rank) keep = 1; else atomicAdd(&m->cnt[dest], 1);
+  }
+  flag[i] = (uint32_t)keep;
+  slot[i] = (uint32_t)keep;                                // scanned in place afterwards
+}
+
+__global__ void mig_offsets_kernel(MigScratch* m, int world, const uint32_t* __restrict__ slot, const uint32_t* __restrict__ flag_last,
+                                   int n, int* __restrict__ counts_out) {
+  if (threadIdx.x == 0) {
+    int run = 0;
+    for (int r = 0; r < world; ++r) { m->base[r] = run; run += m->cnt[r]; if (counts_out) counts_out[r] = m->cnt[r]; }
+    m->base[world] = run;
+    if (slot) { m->n_keep = (int)slot[n - 1] + (int)flag_last[0]; if (counts_out) counts_out[world] = m->n_keep; }
+  }
+}
+
+struct MoveArgs {
+  const double* src[F_NFIELDS]; double* dst[F_NFIELDS];
+  const double* knnh_src; double* knnh_dst;
+  const double* gid_src; double* gid_dst;
+  uint32_t* id_dst;
+};
+
+// pass 2: kept particles move to their compacted slot (new caller index = slot); movers leave as rows
+__global__ void __launch_bounds__(256)
+mig_move_kernel(int n, const uint32_t* __restrict__ id, uint32_t n_owned, const double* __restrict__ bounds, int world, int rank,
+                const uint32_t* __restrict__ keepflag, const uint32_t* __restrict__ slot, MoveArgs a, double* __restrict__ rows_out,
+                int cap_rows, int ncol, MigScratch* m) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (keepflag[i]) {
+    const int64_t d = slot[i];
+#pragma unroll
+    for (int f = 0; f < 3; ++f)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) a.dst[f][3 * d + c] = a.src[f][3 * (int64_t)i + c];
+#pragma unroll
+    for (int f = 3; f < F_NFIELDS; ++f) a.dst[f][d] = a.src[f][i];
+    a.knnh_dst[d] = a.knnh_src[i];
+    a.gid_dst[d] = a.gid_src[i];
+    a.id_dst[d] = (uint32_t)d;
+    return;
+  }
+  if (!(id[i] < n_owned)) return;                          // ghost of the previous step: dropped
+  const int dest = slab_of(a.src[F_POS][3 * (int64_t)i], bounds, world, rank);
+  const int q = m->base[dest] + atomicAdd(&m->fill[dest], 1);
+  if (q >= cap_rows) { m->overflow = 1; return; }
+  double* row = rows_out + (int64_t)q * ncol;
+  int col = 0;
+#pragma unroll
+  for (int f = 0; f < 3; ++f)
+#pragma unroll
+    for (int c = 0; c < 3; ++c) row[col++] = a.src[f][3 * (int64_t)i + c];
+#pragma unroll
+  for (int f = 3; f < F_NFIELDS; ++f) row[col++] = a.src[f][i];
+  row[col++] = a.knnh_src[i];
+  row[col] = a.gid_src[i];
+}
+
+// halo: owned particles within w of another rank's slab, counted / packed per destination rank
+__global__ void __launch_bounds__(256)
+halo_count_kernel(int n, const double* __restrict__ pos, const double* __restrict__ bounds, int world, int rank, double w, MigScratch* m) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double x = pos[3 * (int64_t)i];
+  for (int r = 0; r < world; ++r)
+    if (r != rank && x >= bounds[r] - w && x < bounds[r + 1] + w) atomicAdd(&m->cnt[r], 1);
+}
+struct HaloArgs { const double* f[F_NFIELDS]; const double* knnh; const double* gid; };
+__global__ void __launch_bounds__(256)
+halo_pack_kernel(int n, const uint32_t* __restrict__ id, const double* __restrict__ bounds, int world, int rank, double w, HaloArgs a,
+                 double* __restrict__ rows_out, int64_t* __restrict__ idx_out, int cap_rows, int ncol, MigScratch* m) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double x = a.f[F_POS][3 * (int64_t)i];
+  for (int r = 0; r < world; ++r) {
+    if (r == rank || !(x >= bounds[r] - w && x < bounds[r + 1] + w)) continue;
+    const int q = m->base[r] + atomicAdd(&m->fill[r], 1);
+    if (q >= cap_rows) { m->overflow = 1; continue; }
+    double* row = rows_out + (int64_t)q * ncol;
+    int col = 0;
+#pragma unroll
+    for (int f = 0; f < 3; ++f)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) row[col++] = a.f[f][3 * (int64_t)i + c];
+#pragma unroll
+    for (int f = 3; f < F_NFIELDS; ++f) row[col++] = a.f[f][i];
+    row[col++] = a.knnh[i];
+    row[col] = a.gid[i];
+    idx_out[q] = (int64_t)id[i];                           // caller index: what sphb200_session_gather takes
+  }
+}
 
 // ------------------------------------------------------------------------------------------------
 static int phase_crossing(sphb200_ctx* ctx, cudaStream_t st) {
@@ -563,7 +699,10 @@ static int phase_sort(sphb200_ctx* ctx, cudaStream_t st, unsigned mask = ~0u) {
   a.id_dst = bufp<uint32_t>(ctx->sbuf[SB_ID + (s.id_cur ^ 1)]);
   a.knnh_src = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]);
   a.knnh_dst = bufp<double>(ctx->sbuf[SB_KNNH + (s.knnh_cur ^ 1)]);
+  a.gid_src = s.has_gid ? bufp<double>(ctx->sbuf[SB_GID + s.gid_cur]) : nullptr;
+  a.gid_dst = s.has_gid ? bufp<double>(ctx->sbuf[SB_GID + (s.gid_cur ^ 1)]) : nullptr;
   reorder_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, bufp<uint32_t>(ctx->perm), a, mask);
+  if (s.has_gid) s.gid_cur ^= 1;
   ctx->launches += 1;
   for (int f = 0; f < F_NFIELDS; ++f) if (mask >> f & 1u) s.cur[f] ^= 1;
   s.id_cur ^= 1;
@@ -711,6 +850,7 @@ static double* aux_field(sphb200_ctx* ctx, const char* name, bool for_upload) {
   if (!strcmp(name, "knn_h")) return bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]);
   if (!strcmp(name, "visc_pi")) return (ctx->pi_.bytes >= (size_t)s.n * sizeof(double)) ? bufp<double>(ctx->pi_) : nullptr;
   if (!for_upload && !strcmp(name, "dist_sq")) return bufp<double>(ctx->sbuf[SB_DISTSQ]);
+  if (!strcmp(name, "gid")) return s.has_gid ? bufp<double>(ctx->sbuf[SB_GID + s.gid_cur]) : nullptr;
   return nullptr;
 }
 
@@ -996,6 +1136,7 @@ static int download_rows_impl(sphb200_ctx* ctx, double* rows, int64_t n_rows, in
   for (int f = 0; f < F_NFIELDS; ++f) a.f[f] = fld(ctx, f);
   a.knnh = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]);
   a.tag = tag;
+  a.gid = s.has_gid ? bufp<double>(ctx->sbuf[SB_GID + s.gid_cur]) : nullptr;
   rows_out_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, n_rows, ncol, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]), a, rows);
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
@@ -1017,6 +1158,7 @@ int sphb200_session_upload_rows_at(sphb200_ctx* ctx, const double* rows, int64_t
   for (int f = 0; f < F_NFIELDS; ++f) a.f[f] = fld(ctx, f);
   a.knnh = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]);
   a.tag = nullptr;
+  a.gid = s.has_gid ? bufp<double>(ctx->sbuf[SB_GID + s.gid_cur]) : nullptr;
   rows_in_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, ncol, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]), rows, a, first, n_rows);
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
@@ -1076,6 +1218,7 @@ int sphb200_session_append_rows(sphb200_ctx* ctx, const double* rows, int64_t n_
   for (int f = 0; f < F_NFIELDS; ++f) a.f[f] = fld(ctx, f) + (size_t)n0 * kFieldWidth[f];
   a.knnh = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]) + n0;
   a.tag = nullptr;
+  a.gid = nullptr;
   rows_in_kernel<<<ceil_div(n_new, 256), 256, 0, st>>>((int)n_new, ncol, nullptr, rows, a);
   iota_kernel<<<ceil_div(n_new, 256), 256, 0, st>>>((int)n_new, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]) + n0, (uint32_t)n0);
   ctx->launches += 2;
@@ -1176,7 +1319,7 @@ cover_check_kernel(int n, const double* __restrict__ pos, const double* __restri
   if (threadIdx.x == 0) { s_bad = 0ull; s_h = 0ull; }
   __syncthreads();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n && (int)id[i] < n_owned) {
+  if (i < n && id[i] < (uint32_t)n_owned) {
     const double x = pos[3 * (int64_t)i], hh = h[i];
     const bool ok = ((x - hh) >= lo) && ((x + hh) < hi);
     if (!ok) atomicMax(&s_bad, (unsigned long long)__double_as_longlong(1.0));
@@ -1227,14 +1370,173 @@ int sphb200_session_buffer(sphb200_ctx* ctx, const char* name, void** ptr, int64
   SPH_FAIL("session_buffer: unknown buffer '%s'", name);
 }
 
+
+// ---- slab decomposition: device side ------------------------------------------------------------
+static MigScratch* mig_scratch(sphb200_ctx* ctx) { return reinterpret_cast<MigScratch*>(bufp<char>(ctx->tmp1)); }
+
+// the session carries global particle ids (column 18 of every row) from now on
+int sphb200_session_enable_gid(sphb200_ctx* ctx) {
+  if (!ctx) SPH_FAIL("null context");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
+  Session& s = sess(ctx);
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_GID], (size_t)s.n * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_GID_ALT], (size_t)s.n * sizeof(double)));
+  CUDA_TRY(cudaMemset(ctx->sbuf[SB_GID].p, 0, (size_t)s.n * sizeof(double)));
+  s.has_gid = 1; s.gid_cur = 0;
+  return 0;
+}
+
+// Drop the ghosts, send away the owned particles that left the slab [bounds[rank], bounds[rank+1]) and compact
+// the rest (new caller index = position in the compacted order).  rows_out (device, cap_rows x ncol) receives
+// the movers grouped by destination rank; counts_out (device int32[world + 1]) the movers per rank and, last, the
+// number of particles kept.  The caller reads counts_out, then calls sphb200_session_set_count(kept, kept).
+int sphb200_session_migrate_pack(sphb200_ctx* ctx, int phase, const double* bounds, int world, int rank, double* rows_out,
+                                 int64_t cap_rows, int ncol, int* counts_out, void* stream) {
+  if (!ctx || !bounds || (phase == 0 && !counts_out) || (phase == 1 && !rows_out && cap_rows > 0))
+    SPH_FAIL("session_migrate_pack: null argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
+  Session& s = sess(ctx);
+  if (!s.has_gid) SPH_FAIL("session_migrate_pack: call sphb200_session_enable_gid first");
+  if (world < 1 || world > MIG_MAX_WORLD || rank < 0 || rank >= world || ncol < ROW_STATE_COLS + 1)
+    SPH_FAIL("session_migrate_pack: bad arguments (world %d, rank %d, ncol %d)", world, rank, ncol);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int n = (int)s.n;
+  SPH_TRY(devbuf_reserve(ctx->tmp1, sizeof(MigScratch)));
+  SPH_TRY(devbuf_reserve(ctx->tmp2, (size_t)n * sizeof(uint32_t)));
+  SPH_TRY(devbuf_reserve(ctx->tmp3, (size_t)n * sizeof(uint32_t)));
+  MigScratch* m = mig_scratch(ctx);
+  uint32_t* flag = bufp<uint32_t>(ctx->tmp2);
+  uint32_t* slot = bufp<uint32_t>(ctx->tmp3);
+  const uint32_t* id = bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]);
+  const uint32_t n_owned = s.n_owned >= 0 ? (uint32_t)s.n_owned : (uint32_t)n;
+  if (phase == 0) {                                        // count: the caller sizes rows_out from counts_out
+    mig_reset_kernel<<<1, MIG_MAX_WORLD, 0, st>>>(m);
+    mig_classify_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, id, n_owned, fld(ctx, F_POS), bounds, world, rank, flag, slot, m);
+    SPH_TRY(scan_exclusive_u32(ctx, slot, n, st));
+    mig_offsets_kernel<<<1, 32, 0, st>>>(m, world, slot, flag + (n - 1), n, counts_out);
+    ctx->launches += 3;
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+  }
+  MoveArgs a;
+  for (int f = 0; f < F_NFIELDS; ++f) { a.src[f] = fld(ctx, f, 0); a.dst[f] = fld(ctx, f, 1); }
+  a.knnh_src = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]); a.knnh_dst = bufp<double>(ctx->sbuf[SB_KNNH + (s.knnh_cur ^ 1)]);
+  a.gid_src = bufp<double>(ctx->sbuf[SB_GID + s.gid_cur]); a.gid_dst = bufp<double>(ctx->sbuf[SB_GID + (s.gid_cur ^ 1)]);
+  a.id_dst = bufp<uint32_t>(ctx->sbuf[SB_ID + (s.id_cur ^ 1)]);
+  mig_move_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, id, n_owned, bounds, world, rank, flag, slot, a, rows_out, (int)cap_rows, ncol, m);
+  ctx->launches += 1;
+  for (int f = 0; f < F_NFIELDS; ++f) s.cur[f] ^= 1;
+  s.id_cur ^= 1; s.knnh_cur ^= 1; s.gid_cur ^= 1;
+  s.has_list = 0; s.pos_valid = 0;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// particle count after a migration / before ghosts arrive (host-side bookkeeping only)
+int sphb200_session_set_count(sphb200_ctx* ctx, int64_t n, int64_t n_owned) {
+  if (!ctx) SPH_FAIL("null context");
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
+  Session& s = sess(ctx);
+  if (n < 0 || n_owned > n) SPH_FAIL("session_set_count: bad counts (%lld, %lld)", (long long)n, (long long)n_owned);
+  s.n = n; s.n_owned = n_owned;
+  s.has_list = 0; s.pos_valid = 0;
+  return 0;
+}
+
+// Append rows that arrived from other ranks (same layout, column 18 = global id) behind the current particles,
+// as owned particles (movers: n_owned grows too; requires that no ghost is present) or as ghosts.
+int sphb200_session_receive_rows(sphb200_ctx* ctx, const double* rows, int64_t n_new, int ncol, int as_ghosts, void* stream) {
+  if (!ctx || (!rows && n_new > 0)) SPH_FAIL("session_receive_rows: null argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
+  Session& s = sess(ctx);
+  if (!s.has_gid) SPH_FAIL("session_receive_rows: call sphb200_session_enable_gid first");
+  if (n_new < 0 || ncol < ROW_STATE_COLS + 1) SPH_FAIL("session_receive_rows: needs (n_new >= 0, ncol >= 19)");
+  const int64_t n_owned = s.n_owned >= 0 ? s.n_owned : s.n;
+  if (!as_ghosts && n_owned != s.n) SPH_FAIL("session_receive_rows: owned rows cannot be appended behind ghosts");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int64_t n0 = s.n, n1 = s.n + n_new;
+  if (n1 >= (int64_t)0x7fffffff) SPH_FAIL("session_receive_rows: too many particles");
+  for (int f = 0; f < F_NFIELDS; ++f) {
+    const size_t w = kFieldWidth[f] * sizeof(double);
+    SPH_TRY(devbuf_grow(ctx->sbuf[2 * f + s.cur[f]], (size_t)n0 * w, (size_t)n1 * w, st));
+    SPH_TRY(devbuf_reserve(ctx->sbuf[2 * f + (s.cur[f] ^ 1)], (size_t)n1 * w + (size_t)n1 * w / 4));
+  }
+  SPH_TRY(devbuf_grow(ctx->sbuf[SB_ID + s.id_cur], n0 * sizeof(uint32_t), n1 * sizeof(uint32_t), st));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_ID + (s.id_cur ^ 1)], n1 * sizeof(uint32_t) + n1));
+  SPH_TRY(devbuf_grow(ctx->sbuf[SB_KNNH + s.knnh_cur], n0 * sizeof(double), n1 * sizeof(double), st));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_KNNH + (s.knnh_cur ^ 1)], n1 * sizeof(double) + 2 * n1));
+  SPH_TRY(devbuf_grow(ctx->sbuf[SB_GID + s.gid_cur], n0 * sizeof(double), n1 * sizeof(double), st));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_GID + (s.gid_cur ^ 1)], n1 * sizeof(double) + 2 * n1));
+  for (int o = 0; o < O_NOUT; ++o) SPH_TRY(devbuf_reserve(ctx->sbuf[SB_OUT + o], (size_t)n1 * kOutWidth[o] * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_NONTRIV], n1 * sizeof(int32_t)));
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_DISTSQ], n1 * sizeof(double)));
+  if (n_new > 0) {
+    RowArgs a;
+    for (int f = 0; f < F_NFIELDS; ++f) a.f[f] = fld(ctx, f) + (size_t)n0 * kFieldWidth[f];
+    a.knnh = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]) + n0;
+    a.gid = bufp<double>(ctx->sbuf[SB_GID + s.gid_cur]) + n0;
+    a.tag = nullptr;
+    rows_in_kernel<<<ceil_div(n_new, 256), 256, 0, st>>>((int)n_new, ncol, nullptr, rows, a);
+    iota_kernel<<<ceil_div(n_new, 256), 256, 0, st>>>((int)n_new, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]) + n0, (uint32_t)n0);
+    ctx->launches += 2;
+    CUDA_TRY(cudaGetLastError());
+  }
+  s.n = n1;
+  s.n_owned = as_ghosts ? n_owned : n1;
+  s.has_list = 0; s.pos_valid = 0;
+  return 0;
+}
+
+// Select the owned particles within w of another rank's slab and pack them as rows grouped by destination rank
+// (rows_out), with their caller indices (idx_out: the list later ghost refreshes gather at).  counts_out (device
+// int32[world]) = rows per destination.  Call after the movers were received (every particle owned).
+int sphb200_session_halo_pack(sphb200_ctx* ctx, int phase, const double* bounds, int world, int rank, double w, double* rows_out,
+                              int64_t* idx_out, int64_t cap_rows, int ncol, int* counts_out, void* stream) {
+  if (!ctx || !bounds || (phase == 0 && !counts_out) || (phase == 1 && cap_rows > 0 && (!rows_out || !idx_out)))
+    SPH_FAIL("session_halo_pack: null argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
+  Session& s = sess(ctx);
+  if (!s.has_gid) SPH_FAIL("session_halo_pack: call sphb200_session_enable_gid first");
+  if (world < 1 || world > MIG_MAX_WORLD || rank < 0 || rank >= world || ncol < ROW_STATE_COLS + 1)
+    SPH_FAIL("session_halo_pack: bad arguments (world %d, rank %d, ncol %d)", world, rank, ncol);
+  const int64_t n_owned = s.n_owned >= 0 ? s.n_owned : s.n;
+  if (n_owned != s.n) SPH_FAIL("session_halo_pack: ghosts present (call sphb200_session_migrate_pack first)");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int n = (int)s.n;
+  SPH_TRY(devbuf_reserve(ctx->tmp1, sizeof(MigScratch)));
+  MigScratch* m = mig_scratch(ctx);
+  if (phase == 0) {
+    mig_reset_kernel<<<1, MIG_MAX_WORLD, 0, st>>>(m);
+    halo_count_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, fld(ctx, F_POS), bounds, world, rank, w, m);
+    mig_offsets_kernel<<<1, 32, 0, st>>>(m, world, nullptr, nullptr, n, counts_out);
+    ctx->launches += 3;
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+  }
+  HaloArgs a;
+  for (int f = 0; f < F_NFIELDS; ++f) a.f[f] = fld(ctx, f);
+  a.knnh = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]);
+  a.gid = bufp<double>(ctx->sbuf[SB_GID + s.gid_cur]);
+  halo_pack_kernel<<<ceil_div(n, 256), 256, 0, st>>>(n, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]), bounds, world, rank, w, a,
+                                                     rows_out, idx_out, (int)cap_rows, ncol, m);
+  ctx->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
 int sphb200_session_perturb(sphb200_ctx* ctx, double amplitude, uint64_t seed, void* stream) {
   if (!ctx) SPH_FAIL("null context");
   CUDA_TRY(cudaSetDevice(ctx->device));
   if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
   Session& s = sess(ctx);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  perturb_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]), (int)s.n_owned,
-                                                     amplitude, (unsigned long long)seed, fld(ctx, F_POS));
+  perturb_kernel<<<ceil_div(s.n, 256), 256, 0, st>>>((int)s.n, bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]),
+                                                     s.has_gid ? bufp<double>(ctx->sbuf[SB_GID + s.gid_cur]) : nullptr,
+                                                     (int)s.n_owned, amplitude, (unsigned long long)seed, fld(ctx, F_POS));
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;

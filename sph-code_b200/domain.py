@@ -277,26 +277,43 @@ def distributed_percentile(sorted_local, q=90.0, group=None, pivots=1024, cap_hi
 
 class DistributedSession(object):
     """The device-resident time step (session.Session) over slabs: same phases, with the exchanges the
-    reference's formulas need folded into them.  State between steps lives in the rank's session
-    (owned rows first, ghosts after them, in the session's caller order)."""
+    reference's formulas need folded into them.  The owned particles never leave the rank's session: every step
+    a device kernel classifies them against the slab faces, only the movers and the halo rows are packed and
+    travel (sphb200_session_migrate_pack / _halo_pack / _receive_rows), and the session is compacted in place.
+    Host work per step: two count exchanges and the coverage check (three small synchronisations)."""
 
     PHASES = ("crossing", "dt_clamp", "exchange", "sort", "knn", "pack", "density", "pi", "force", "integrate")
 
-    def __init__(self, rows, bounds, k, dist_cut, dt_0, device, n_total=None, group=None):
+    def __init__(self, rows, bounds, k, dist_cut, dt_0, device, group=None, d=None):
         from . import constants as C
         from .session import Session
-        self._Session = Session
         self.C = C
         self.device = torch.device("cuda", device) if not isinstance(device, torch.device) else device
         self.group = group
-        self.ex = SlabExchange(bounds, group=group)
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.bounds = [float(b) for b in bounds]
+        assert len(self.bounds) == self.world + 1
+        self.lo, self.hi = self.bounds[self.rank], self.bounds[self.rank + 1]
+        # finite stand-ins for the outer faces: the device kernels compare against plain doubles
+        big = 1.0e300
+        self._bounds_dev = torch.tensor([max(min(b, big), -big) for b in self.bounds], dtype=torch.float64, device=self.device)
         self.k, self.dist_cut, self.dt_0 = int(k), float(dist_cut), float(dt_0)
-        self.rows = rows.to(self.device).contiguous()             # owned rows until the first session exists
-        self.sess = None
-        self.n_own = int(self.rows.shape[0])
-        self.d = float(C.d_default)
+        rows = torch.as_tensor(rows).to(self.device).contiguous()
+        n0 = int(rows.shape[0])
+        self.sess = Session(max(n0, 1), self.k, self.dist_cut, device=self.device.index, dt_0=self.dt_0)
+        for name, v in (("age", 0.0), ("d", float(C.d_default) if d is None else float(d)), ("dt", self.dt_0), ("ct", 0.0)):
+            self.sess.set_scalar(name, v)
+        self.sess.enable_gid()
+        if n0 > 0:
+            self.sess.upload_rows(rows)
+        else:                                                     # an empty slab: one placeholder that the first exchange drops
+            ph = torch.full((1, NCOL), float("nan"), dtype=torch.float64, device=self.device)
+            self.sess.upload_rows(ph)
+            self.sess.set_count(1, 0)
+        self.n_own = n0
         self.w = None
         self.halo_redo = 0
+        self.migrated = 0
         self.hmax = 0.0
         self._hist = None
         self._cover = None
@@ -304,8 +321,6 @@ class DistributedSession(object):
         nt = torch.tensor([float(self.n_own)], dtype=torch.float64, device=self.device)
         dist.all_reduce(nt, op=dist.ReduceOp.SUM, group=group)
         self.n_total = int(nt.item())
-        # window size of the percentile's last gather: 3 pivot gaps of a rank holding 1.5x its share
-        self._cap_hint = 3 * int(math.ceil(1.5 * self.n_total / dist.get_world_size(group) / 1023.0)) + 64
 
     # -- construction helpers -----------------------------------------------------------------
     @classmethod
@@ -317,11 +332,8 @@ class DistributedSession(object):
         rows = rows_from_state(state)
         x = rows[:, 0]
         mine = (x >= bounds[rank]) & (x < bounds[rank + 1])
-        self = cls(torch.from_numpy(rows[mine]), bounds, state["N_NEIGH"], state["dist"],
-                   dt_0 if dt_0 is not None else state.get("dt_0", C.dt_0), device, group=group)
-        if "d" in state:
-            self.d = float(state["d"])
-        return self
+        return cls(torch.from_numpy(rows[mine]), bounds, state["N_NEIGH"], state["dist"],
+                   dt_0 if dt_0 is not None else state.get("dt_0", C.dt_0), device, group=group, d=state.get("d"))
 
     @classmethod
     def uniform_slabs(cls, n_per_rank, seed, k, dt_scale, device, group=None):
@@ -337,16 +349,37 @@ class DistributedSession(object):
         return cls(torch.from_numpy(rows), bounds, k, st["dist"], C.dt_0 * dt_scale, device, group=group)
 
     @classmethod
-    def synthetic(cls, kind, n, seed, k, dt_scale, device, scaling="weak", group=None):
-        """bench.py's workloads.  weak + uniform: `uniform_slabs` (n per rank, every rank draws its own slab);
-        strong (or clustered at sizes one host can draw): every rank draws the same n particles and keeps its
-        equal-count slab."""
+    def clustered_slabs(cls, n_total, seed, k, dt_scale, device, group=None, chunk=1000000):
+        """BASELINE configs[4]: the clustered cloud drawn in seeded chunks (ics.clustered_cloud_chunk), so that no
+        rank ever holds all n_total particles: every rank draws every chunk and keeps what falls into its slab.
+        The slab faces are the x-quantiles of the first chunk (equal counts to within sampling noise)."""
         from . import constants as C, ics
-        if kind == "uniform" and scaling == "weak":
-            return cls.uniform_slabs(int(n), seed, k, dt_scale, device, group=group)
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        first = ics.clustered_cloud_chunk(n_total, seed, 0, min(chunk, n_total))
+        bounds = equal_count_bounds(first["points"][:, 0], world)
+        parts = []
+        for c in range((n_total + chunk - 1) // chunk):
+            st = first if c == 0 else ics.clustered_cloud_chunk(n_total, seed, c, chunk)
+            x = st["points"][:, 0]
+            mine = (x >= bounds[rank]) & (x < bounds[rank + 1])
+            parts.append(rows_from_state(st, gid=st["gid"])[mine])
+        rows = np.concatenate(parts, axis=0)
+        return cls(torch.from_numpy(rows), bounds, k, first["dist"], C.dt_0 * dt_scale, device, group=group, d=first["d"])
+
+    @classmethod
+    def synthetic(cls, kind, n, seed, k, dt_scale, device, scaling="weak", group=None):
+        """bench.py's workloads.  weak: n particles per rank (uniform: every rank draws its own slab of a box
+        `world` times longer; clustered: chunked draw of the n x world cloud); strong: the n particles of the
+        single-GPU workload split into equal-count slabs."""
+        from . import constants as C, ics
         world = dist.get_world_size(group)
-        n_total = int(n) * (world if scaling == "weak" else 1)
-        st = ics.uniform_box(n_total, seed) if kind == "uniform" else ics.clustered_cloud(n_total, seed)
+        if scaling == "weak":
+            if kind == "uniform":
+                return cls.uniform_slabs(int(n), seed, k, dt_scale, device, group=group)
+            return cls.clustered_slabs(int(n) * world, seed, k, dt_scale, device, group=group)
+        if kind == "clustered":
+            return cls.clustered_slabs(int(n), seed, k, dt_scale, device, group=group)
+        st = ics.uniform_box(int(n), seed)
         return cls.from_global_state(st, device, dt_0=C.dt_0 * dt_scale, group=group)
 
     # -- small collectives --------------------------------------------------------------------
@@ -355,38 +388,57 @@ class DistributedSession(object):
         dist.all_reduce(t, op=op, group=self.group)
         return float(t.item())
 
+    def _counts_exchange(self, counts):
+        """counts: device int32 [world (+ extras)]: rows this rank sends to every rank.  Returns (send list, extras,
+        recv list) as Python ints: one all_to_all of `world` integers and ONE host synchronisation."""
+        sc = counts[:self.world].to(torch.int64)
+        rc = torch.empty_like(sc)
+        dist.all_to_all_single(rc, sc, group=self.group)
+        host = torch.cat([counts.to(torch.int64), rc]).tolist()
+        ne = counts.numel() - self.world
+        return host[:self.world], host[self.world:self.world + ne], host[self.world + ne:]
+
     def _refresh_ghosts(self, name):
         """Overwrite the ghosts' `name` with their owners' current values: gather at the send lists,
         one all_to_all, scatter into the ghost slots (no full-array traffic)."""
         send = self.sess.gather(name, self._send_cat)
         recv = torch.empty((self._n_ghost, send.shape[1]), dtype=torch.float64, device=self.device)
-        dist.all_to_all_single(recv, send, output_split_sizes=self.ex.recv_counts, input_split_sizes=self._send_counts,
+        dist.all_to_all_single(recv, send, output_split_sizes=self._recv_counts, input_split_sizes=self._send_counts,
                                group=self.group)
         self.sess.scatter(name, self._ghost_idx, recv)
 
     # -- (re)building the local particle set ----------------------------------------------------
-    def _open_session(self, rows, w):
-        """Ghost exchange for halo width w, then a session over owned + ghost rows."""
-        ghosts = self.ex.build_halo(rows, w)
-        self.rows = rows
-        self.n_own = int(rows.shape[0])
-        n_loc = self.n_own + int(ghosts.shape[0])
-        if self.sess is None:
-            s = self._Session(n_loc, self.k, self.dist_cut, device=self.device.index, dt_0=self.dt_0)
-            for name, v in (("age", 0.0), ("d", self.d), ("dt", self.dt_0), ("ct", 0.0), ("n_owned", self.n_own)):
-                s.set_scalar(name, v)
-        else:
-            s = self.sess
-            s.resize(n_loc, self.n_own)                            # keeps the device scalars: no host traffic
-        s.upload_rows_at(rows, 0)                                  # two pieces: no concatenated copy of the state
-        s.upload_rows_at(ghosts.contiguous(), self.n_own)
-        self.gid = torch.cat([rows[:, 18], ghosts[:, 18]])
-        self._send_cat = torch.cat(self.ex.send_idx)
-        self._send_counts = [int(i.numel()) for i in self.ex.send_idx]
-        self._n_ghost = int(ghosts.shape[0])
+    def _exchange(self, w):
+        """Movers to their new owners, then ghosts for halo width w.  Everything N-sized stays in the session."""
+        s = self.sess
+        # 1. migration: classify on the device, learn the counts, pack only the movers
+        counts = torch.empty(self.world + 1, dtype=torch.int32, device=self.device)
+        s.migrate_pack(0, self._bounds_dev, self.world, self.rank, None, counts)
+        send_list, (n_keep,), recv_list = self._counts_exchange(counts)
+        send_list[self.rank] = 0
+        send = torch.empty((sum(send_list), NCOL), dtype=torch.float64, device=self.device)
+        s.migrate_pack(1, self._bounds_dev, self.world, self.rank, send, None)
+        s.set_count(n_keep, n_keep)
+        recv = torch.empty((sum(recv_list), NCOL), dtype=torch.float64, device=self.device)
+        dist.all_to_all_single(recv, send, output_split_sizes=recv_list, input_split_sizes=send_list, group=self.group)
+        s.receive_rows(recv, as_ghosts=False)
+        self.migrated += sum(send_list)
+        self.n_own = n_keep + int(recv.shape[0])
+        # 2. halo: owned particles within w of another slab go there as ghosts
+        hc = torch.empty(self.world, dtype=torch.int32, device=self.device)
+        s.halo_pack(0, self._bounds_dev, self.world, self.rank, w, None, None, hc)
+        send_list, _, recv_list = self._counts_exchange(hc)
+        ns = sum(send_list)
+        send = torch.empty((ns, NCOL), dtype=torch.float64, device=self.device)
+        idx = torch.empty((ns,), dtype=torch.int64, device=self.device)
+        s.halo_pack(1, self._bounds_dev, self.world, self.rank, w, send, idx, None)
+        recv = torch.empty((sum(recv_list), NCOL), dtype=torch.float64, device=self.device)
+        dist.all_to_all_single(recv, send, output_split_sizes=recv_list, input_split_sizes=send_list, group=self.group)
+        s.receive_rows(recv, as_ghosts=True)
+        self._send_cat, self._send_counts, self._recv_counts = idx, send_list, recv_list
+        self._n_ghost = int(recv.shape[0])
         self._ghost_idx = torch.arange(self.n_own, self.n_own + self._n_ghost, dtype=torch.int64, device=self.device)
-        self.sess = s
-        self.w = w
+        self.w = float(w)
 
     def _length_hist(self):
         if self._hist is None:
@@ -408,19 +460,16 @@ class DistributedSession(object):
         view.copy_(stage)
         return stage
 
-    def _owned_rows(self):
-        """Current owned rows (state columns + trial radius + gid) out of the session."""
-        return self.sess.download_rows_tagged(self.n_own, NCOL, self.gid)
-
-    def _initial_halo_width(self, rows):
+    def _initial_halo_width(self):
         """1.6 x the k-th-neighbour distance expected at the mean number density of the global box."""
-        lo = rows[:, :3].min(dim=0).values if rows.shape[0] else torch.full((3,), float("inf"), device=self.device, dtype=torch.float64)
-        hi = rows[:, :3].max(dim=0).values if rows.shape[0] else torch.full((3,), float("-inf"), device=self.device, dtype=torch.float64)
+        pts = self.sess.download_tensor("points")[:max(self.n_own, 0)]
+        inf = float("inf")
+        lo = pts.min(dim=0).values if pts.shape[0] else torch.full((3,), inf, device=self.device, dtype=torch.float64)
+        hi = pts.max(dim=0).values if pts.shape[0] else torch.full((3,), -inf, device=self.device, dtype=torch.float64)
         dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=self.group)
         dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=self.group)
-        n_tot = self._allreduce(float(rows.shape[0]), dist.ReduceOp.SUM)
         vol = float(torch.prod(torch.clamp(hi - lo, min=1e-300)).item())
-        return 1.6 * (self.k * vol / (4.1887902047863905 * max(n_tot, 1.0))) ** (1.0 / 3.0)
+        return 1.6 * (self.k * vol / (4.1887902047863905 * max(self.n_total, 1.0))) ** (1.0 / 3.0)
 
     # -- phases -------------------------------------------------------------------------------
     def _search(self):
@@ -430,8 +479,8 @@ class DistributedSession(object):
         while True:
             self.sess.phase("sort")
             self.sess.phase("knn")
-            lo = self.ex.lo - self.ex.w if self.ex.rank > 0 else float("-inf")
-            hi = self.ex.hi + self.ex.w if self.ex.rank < self.ex.world - 1 else float("inf")
+            lo = self.lo - self.w if self.rank > 0 else float("-inf")
+            hi = self.hi + self.w if self.rank < self.world - 1 else float("inf")
             self.sess.cover_check(lo, hi)                          # [ball leaves the covered region, largest h] on the device
             if self._cover is None:
                 self._cover = self.sess.buffer_tensor("cover")
@@ -444,13 +493,12 @@ class DistributedSession(object):
                 raise RuntimeError("slab search: halo width %.3e still does not cover the k-th neighbours after %d "
                                    "doublings (largest h %.3e): non-finite positions?" % (self.w, redo, self.hmax))
             self.halo_redo += 1
-            self._open_session(self.rows, 2.0 * self.w)
+            self._exchange(2.0 * self.w)
         self._refresh_ghosts("sizes")
 
     def startup(self):
         """code_running.py:171-179 on slabs: first neighbour query + hydro_update, densities_0 <- densities."""
-        rows = self.ex.migrate(self.rows)
-        self._open_session(rows, self._initial_halo_width(rows))
+        self._exchange(self._initial_halo_width())
         self._search()
         for ph in ("pack", "density", "pi", "force"):
             self.phase(ph)
@@ -464,13 +512,10 @@ class DistributedSession(object):
             ct = s.download_raw("scalar:ct", 1)                    # device scalar, reduced in place: no host sync
             dist.all_reduce(ct, op=dist.ReduceOp.MIN, group=self.group)
             s.upload_raw("scalar:ct", ct)
-            self._ct_dev = ct
         elif name == "dt_clamp":
             s.phase("dt_clamp")
         elif name == "exchange":
-            rows = self.ex.migrate(self._owned_rows())
-            self.migrated = getattr(self, "migrated", 0) + int(getattr(self.ex, "last_migrated", 0))
-            self._open_session(rows, 1.25 * self.hmax)
+            self._exchange(1.25 * self.hmax)
         elif name == "sort":
             pass                                                  # part of "knn" here (the search may be redone)
         elif name == "knn":
@@ -504,71 +549,7 @@ class DistributedSession(object):
     def perturb(self, amplitude, seed):
         """Session.perturb for slabs: the displacement is a function of the particle's GLOBAL id, so every
         decomposition moves every particle identically (ics.perturbation is the host mirror)."""
-        g = self.gid[:self.n_own].to(torch.int64)
-        M = (1 << 64) - 1
-
-        def c64(v):                                               # uint64 constant as the int64 with the same bits
-            v &= M
-            return v - (1 << 64) if v >= (1 << 63) else v
-
-        def shr(z, b):                                            # logical shift right on int64 bit patterns
-            return (z >> b) & ((1 << (64 - b)) - 1)
-        cols = []
-        for c in range(3):
-            z = (g * 3 + (c + 1)) * c64(0x9E3779B97F4A7C15) + c64(int(seed) * 0xBF58476D1CE4E5B9)
-            z = z ^ shr(z, 30); z = z * c64(0xBF58476D1CE4E5B9)
-            z = z ^ shr(z, 27); z = z * c64(0x94D049BB133111EB)
-            z = z ^ shr(z, 31)
-            cols.append(shr(z, 11).to(torch.float64) * (1.0 / 4503599627370496.0) - 1.0)
-        disp = torch.stack(cols, dim=1) * float(amplitude)
-        idx = torch.arange(self.n_own, dtype=torch.int64, device=self.device)
-        self.sess.scatter("points", idx, self.sess.gather("points", idx) + disp)
-
-    def counters(self, reset=True):
-        c = self.sess.counters(reset)
-        c["halo_redo"] = self.halo_redo
-        c["migrated"] = getattr(self, "migrated", 0)
-        if reset:
-            self.halo_redo = 0
-            self.migrated = 0
-        return c
-
-    def median_h(self):
-        """Median smoothing length over ALL ranks' owned particles (approximated by the mean of the ranks' medians)."""
-        m = self.sess.download_tensor("sizes")[:self.n_own].median().reshape(1)
-        dist.all_reduce(m, op=dist.ReduceOp.SUM, group=self.group)
-        return float(m.item()) / dist.get_world_size(self.group)
-
-    def fp64_peak(self):
-        return self.sess.fp64_peak()
-
-    def close(self):
-        if self.sess is not None:
-            self.sess.close()
-            self.sess = None
-
-    def gather_neighbor_ids(self):
-        """(N_total, k) neighbour rows as GLOBAL particle ids, ordered by global id, on every rank (tests / verify)."""
-        nb = self.sess.download_tensor("neighbor")[:self.n_own]
-        g_all = torch.cat([self.gid.to(torch.int64), torch.full((1,), -1, dtype=torch.int64, device=self.device)])
-        rows = g_all[nb.clamp(max=self.sess.n)]                    # index n = missing neighbour -> -1
-        gid = self.gid[:self.n_own].to(torch.int64)
-        world = dist.get_world_size(self.group)
-        counts = [None] * world
-        dist.all_gather_object(counts, int(gid.numel()), group=self.group)
-        nmax = max(counts)
-        pad_g = torch.full((nmax,), -1, dtype=torch.int64, device=self.device); pad_g[:gid.numel()] = gid
-        pad_r = torch.full((nmax, rows.shape[1]), -1, dtype=torch.int64, device=self.device); pad_r[:gid.numel()] = rows
-        gs = [torch.empty_like(pad_g) for _ in range(world)]
-        rs = [torch.empty_like(pad_r) for _ in range(world)]
-        dist.all_gather(gs, pad_g, group=self.group)
-        dist.all_gather(rs, pad_r, group=self.group)
-        g = torch.cat([gs[r][:counts[r]] for r in range(world)])
-        v = torch.cat([rs[r][:counts[r]] for r in range(world)])
-        out = torch.empty_like(v)
-        out[g] = v
-        out[out < 0] = self.n_total
-        return out.cpu().numpy()
+        self.sess.perturb(amplitude, seed)
 
     # -- the Session interface bench.py and the tests use ---------------------------------------
     def phases(self):
@@ -581,14 +562,78 @@ class DistributedSession(object):
         self.sess.check()
 
     def launches(self):
-        return self.sess.launches()               # the context's counter is cumulative across sessions
+        return self.sess.launches()
 
     def scalar(self, name):
         return self.sess.scalar(name)
 
+    def counters(self, reset=True):
+        c = self.sess.counters(reset)
+        c["halo_redo"] = self.halo_redo
+        c["migrated"] = self.migrated
+        if reset:
+            self.halo_redo = 0
+            self.migrated = 0
+        return c
+
+    def median_h(self):
+        """Median smoothing length over the ranks' owned particles (mean of the ranks' medians)."""
+        h = self.sess.download_tensor("sizes")[:self.n_own]
+        m = (h.median() if h.numel() else torch.zeros((), dtype=torch.float64, device=self.device)).reshape(1)
+        cnt = torch.tensor([1.0 if h.numel() else 0.0], dtype=torch.float64, device=self.device)
+        both = torch.cat([m, cnt])
+        dist.all_reduce(both, op=dist.ReduceOp.SUM, group=self.group)
+        return float(both[0].item()) / max(float(both[1].item()), 1.0)
+
+    def fp64_peak(self):
+        return self.sess.fp64_peak()
+
+    def close(self):
+        if self.sess is not None:
+            self.sess.close()
+            self.sess = None
+
+    def download_owned(self, name):
+        """(global id, values) of this rank's owned particles."""
+        gid = self.sess.download_tensor("gid")[:self.n_own].to(torch.int64)
+        return gid, self.sess.download_tensor(name)[:self.n_own]
+
+    def _gather_by_gid(self, gid, val):
+        world = self.world
+        counts = [None] * world
+        dist.all_gather_object(counts, int(gid.numel()), group=self.group)
+        v2 = val if val.dim() == 2 else val[:, None]
+        nmax = max(max(counts), 1)
+        pad_g = torch.full((nmax,), -1, dtype=torch.int64, device=self.device); pad_g[:gid.numel()] = gid
+        pad_v = torch.zeros((nmax, v2.shape[1]), dtype=v2.dtype, device=self.device); pad_v[:gid.numel()] = v2
+        gs = [torch.empty_like(pad_g) for _ in range(world)]
+        vs = [torch.empty_like(pad_v) for _ in range(world)]
+        dist.all_gather(gs, pad_g, group=self.group)
+        dist.all_gather(vs, pad_v, group=self.group)
+        g = torch.cat([gs[r][:counts[r]] for r in range(world)])
+        v = torch.cat([vs[r][:counts[r]] for r in range(world)])
+        out = torch.empty_like(v)
+        out[g] = v
+        return out
+
+    def gather(self, name):
+        """Field `name` of ALL particles ordered by global id, on every rank (tests / small runs only)."""
+        gid, val = self.download_owned(name)
+        out = self._gather_by_gid(gid, val)
+        return out.cpu().numpy() if val.dim() == 2 else out[:, 0].cpu().numpy()
+
+    def gather_neighbor_ids(self):
+        """(N_total, k) neighbour rows as GLOBAL particle ids, ordered by global id, on every rank (tests / verify);
+        missing neighbours are N_total."""
+        nb = self.sess.download_tensor("neighbor")[:self.n_own]
+        g_local = self.sess.download_tensor("gid").to(torch.int64)
+        g_all = torch.cat([g_local, torch.full((1,), self.n_total, dtype=torch.int64, device=self.device)])
+        rows = g_all[nb.clamp(max=self.sess.n)]                    # local index n = missing neighbour
+        return self._gather_by_gid(g_local[:self.n_own], rows).cpu().numpy()
+
     # -- host-resident state (bench.py's e2e leg) ------------------------------------------------
     def make_host_state(self, upload_fields=None, download_fields=None):
-        rows = self._owned_rows()
+        rows = self.sess.download_rows(self.n_own, NCOL)
         cap = int(rows.shape[0] * 1.25) + 1024
         buf = torch.empty((cap, NCOL), dtype=torch.float64).pin_memory()
         buf[:rows.shape[0]].copy_(rows)
@@ -603,34 +648,10 @@ class DistributedSession(object):
         if perturb:
             self.perturb(*perturb)
         self.step()
-        out = self._owned_rows()
+        out = self.sess.download_rows(self.n_own, NCOL)
         if out.shape[0] > hs["buf"].shape[0]:
             hs["buf"] = torch.empty((int(out.shape[0] * 1.25), NCOL), dtype=torch.float64).pin_memory()
         hs["n"] = int(out.shape[0])
         hs["buf"][:hs["n"]].copy_(out, non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
         hs["h2d_bytes"] = hs["d2h_bytes"] = hs["n"] * NCOL * 8
-
-    def download_owned(self, name):
-        """(gid, values) of this rank's owned particles."""
-        return self.gid[:self.n_own].to(torch.int64), self.sess.download_tensor(name)[:self.n_own]
-
-    def gather(self, name):
-        """Field `name` of ALL particles ordered by gid, on every rank (tests / small runs only)."""
-        gid, val = self.download_owned(name)
-        world = dist.get_world_size(self.group)
-        counts = [None] * world
-        dist.all_gather_object(counts, int(gid.numel()), group=self.group)
-        v2 = val if val.dim() == 2 else val[:, None]
-        nmax = max(counts)
-        pad_g = torch.full((nmax,), -1, dtype=torch.int64, device=self.device); pad_g[:gid.numel()] = gid
-        pad_v = torch.zeros((nmax, v2.shape[1]), dtype=v2.dtype, device=self.device); pad_v[:gid.numel()] = v2
-        gs = [torch.empty_like(pad_g) for _ in range(world)]
-        vs = [torch.empty_like(pad_v) for _ in range(world)]
-        dist.all_gather(gs, pad_g, group=self.group)
-        dist.all_gather(vs, pad_v, group=self.group)
-        g = torch.cat([gs[r][:counts[r]] for r in range(world)])
-        v = torch.cat([vs[r][:counts[r]] for r in range(world)])
-        out = torch.empty_like(v)
-        out[g] = v
-        return out.cpu().numpy() if val.dim() == 2 else out[:, 0].cpu().numpy()

@@ -89,6 +89,35 @@ def clustered_cloud(n, seed):
     return _finish(points, rs, mass, particle_type, d, dist, dict(side=float(2 * r[-1]), kind="clustered"))
 
 
+def clustered_cloud_chunk(n_total, seed, chunk_index, chunk_size):
+    """Particles [chunk_index * chunk_size, ...) of a clustered cloud of n_total equal-mass particles, drawn with
+    their own RandomState(seed, chunk_index): any subset of chunks can be generated independently (BASELINE
+    configs[4]: 10^8 particles over 8 GPUs, no rank ever holds them all).  Same radial profile as
+    clustered_cloud; `gid` = global particle index; the length scale d is the analytic 90th-percentile radius
+    of the profile (the full-sample percentile clustered_cloud uses is not available to a single chunk)."""
+    first = chunk_index * chunk_size
+    n = int(min(chunk_size, n_total - first))
+    rs = np.random.RandomState([seed, chunk_index])
+    r = np.linspace(0, 25e14, 2001) ** 0.5 * C.AU
+    dr = np.diff(r)
+    dr = np.append(dr[0], dr)
+    rho_shape = (r ** 4 / (C.AU * 2e7) ** 4 + 1) ** -1
+    mu = 0.86 * C.mu_specie[0] + 0.14 * C.mu_specie[1]
+    rho = 1e6 * mu * C.amu * rho_shape
+    m_cum = np.cumsum(4 * np.pi * r ** 2 * rho * dr)
+    m_tot = m_cum[-1]
+    radii = np.interp(rs.rand(n) * m_tot, m_cum, r)
+    dirs = rs.normal(size=(n, 3))
+    dirs /= np.sqrt(np.sum(dirs ** 2, axis=1))[:, None]
+    points = dirs * radii[:, None]
+    mass = np.full(n, m_tot / n_total)
+    r90 = float(np.interp(0.9 * m_tot, m_cum, r))
+    d = ((r90 ** 2) ** 1.5 / n_total / 0.9 * C.N_INT_PER_PARTICLE) ** (1. / 3.)
+    st = _finish(points, rs, mass, np.zeros(n), d, 2. * r[-1], dict(side=float(2 * r[-1]), kind="clustered"))
+    st["gid"] = np.arange(first, first + n)
+    return st
+
+
 def perturbation(ids, amplitude, seed):
     """Host mirror of sphb200_session_perturb: the (len(ids), 3) displacement amplitude * u(id, seed), u uniform
     in [-1,1)^3 from a splitmix64 hash of (3 id + component, seed).  Bit-identical to the device kernel."""

@@ -19,7 +19,7 @@ STATE_FIELDS = {"points": 3, "velocities": 3, "total_accel": 3, "mass": 1, "size
 RESULT_FIELDS = {"densities": 1, "num_densities": 1, "dust_densities": 1, "visc_heat": 1, "hydro_accel": 3,
                  "visc_accel": 3, "pressure_accel": 3}
 # owner-computed per-particle arrays the slab-decomposed driver reads / overwrites for ghosts (domain.py)
-AUX_FIELDS = {"densities": 1, "visc_pi": 1, "knn_h": 1, "dist_sq": 1}
+AUX_FIELDS = {"densities": 1, "visc_pi": 1, "knn_h": 1, "dist_sq": 1, "gid": 1}
 # host-resident stepping (step_host): what crossing time / clamp / cell build / k-NN read, and what must
 # be re-uploaded after the early sort because "sort_keys" does not carry it into the new order
 HOST_EARLY_FIELDS = ("points", "velocities", "sizes", "particle_type")
@@ -231,6 +231,35 @@ class Session(object):
     def step(self):
         """One pass of the while-body (code_running.py:217-540), asynchronous on the current stream."""
         _lib.check(self.lib.sphb200_session_step(self.ctx.handle, self._stream()))
+
+    # -- slab decomposition (domain.py drives the collectives) ------------------------------------
+    def enable_gid(self):
+        _lib.check(self.lib.sphb200_session_enable_gid(self.ctx.handle))
+
+    def migrate_pack(self, phase, bounds, world, rank, rows_out, counts_out):
+        _lib.check(self.lib.sphb200_session_migrate_pack(
+            self.ctx.handle, int(phase), ctypes.c_void_p(bounds.data_ptr()), int(world), int(rank),
+            ctypes.c_void_p(rows_out.data_ptr()) if rows_out is not None and rows_out.numel() else None,
+            int(rows_out.shape[0]) if rows_out is not None else 0, 19,
+            ctypes.c_void_p(counts_out.data_ptr()) if counts_out is not None else None, self._stream()))
+
+    def set_count(self, n, n_owned):
+        _lib.check(self.lib.sphb200_session_set_count(self.ctx.handle, int(n), int(n_owned)))
+        self.n = int(n)
+
+    def receive_rows(self, rows, as_ghosts):
+        _lib.check(self.lib.sphb200_session_receive_rows(
+            self.ctx.handle, ctypes.c_void_p(rows.data_ptr()) if rows.numel() else None, int(rows.shape[0]), int(rows.shape[1]),
+            1 if as_ghosts else 0, self._stream()))
+        self.n += int(rows.shape[0])
+
+    def halo_pack(self, phase, bounds, world, rank, w, rows_out, idx_out, counts_out):
+        _lib.check(self.lib.sphb200_session_halo_pack(
+            self.ctx.handle, int(phase), ctypes.c_void_p(bounds.data_ptr()), int(world), int(rank), float(w),
+            ctypes.c_void_p(rows_out.data_ptr()) if rows_out is not None and rows_out.numel() else None,
+            ctypes.c_void_p(idx_out.data_ptr()) if idx_out is not None and idx_out.numel() else None,
+            int(rows_out.shape[0]) if rows_out is not None else 0, 19,
+            ctypes.c_void_p(counts_out.data_ptr()) if counts_out is not None else None, self._stream()))
 
     def perturb(self, amplitude, seed):
         """points += amplitude * u(id, seed) (synthetic motion between steps; ics.perturbation is the host mirror)."""

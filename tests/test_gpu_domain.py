@@ -1,5 +1,7 @@
-"""GPU, 2 ranks over NCCL (skipped on a single-GPU box): the slab-decomposed session against the CPU
-oracle's single-process run — neighbour sets bit-exact, state within 1e-10."""
+"""GPU, 2 and 4 ranks over NCCL (skipped where the box has fewer GPUs): the slab-decomposed session against the
+CPU oracle's single-process run with particles that MOVE between steps (so that migration really takes the
+all_to_all branch and the halo is rebuilt from scratch) — neighbour sets bit-exact, state within 1e-10
+(SURVEY.md §8e)."""
 import os
 import socket
 
@@ -36,7 +38,11 @@ def _worker(rank, world, port, n, nsteps):
 
         assert np.array_equal(ds.gather("sizes"), ref["sizes"])            # k-th distances bit-exact
         assert rel(ds.gather("densities"), ref["densities"]) < RTOL
+        amp = 0.2 * float(np.median(ref["sizes"]))
+        ids = np.arange(len(st["points"]))
         for it in range(nsteps):
+            ds.perturb(amp, 40 + it)
+            ref["points"] = ref["points"] + ics.perturbation(ids, amp, 40 + it)
             ds.step(); ds.check()
             ref = O.step(ref)
             assert ds.scalar("ct") == pytest.approx(ref["ct"], rel=1e-13), it
@@ -45,19 +51,21 @@ def _worker(rank, world, port, n, nsteps):
             for name in ("points", "velocities", "total_accel", "E_internal", "T", "sizes", "densities", "densities_0",
                          "visc_heat", "pressure_accel", "visc_accel"):
                 assert rel(ds.gather(name), ref[name]) < RTOL, (it, name, rel(ds.gather(name), ref[name]))
-        # neighbour rows of the owned particles, as sets of global ids
-        gid, _ = ds.download_owned("sizes")
-        nb = ds.sess.download_tensor("neighbor")[:ds.n_own].cpu().numpy()
-        g_all = ds.gid.cpu().numpy().astype(np.int64)
-        got = np.sort(g_all[nb], axis=1)
-        want = np.sort(ref["neighbor"][gid.cpu().numpy()], axis=1)
-        assert np.array_equal(got, want)
-        assert ds.n_own < n and ds.sess.n > ds.n_own                        # really decomposed, with ghosts
+            # neighbour rows of every particle, as sets of global ids
+            got = np.sort(ds.gather_neighbor_ids(), axis=1)
+            assert np.array_equal(got, np.sort(ref["neighbor"], axis=1)), it
+        stats = ds.counters()
+        tot = torch.tensor([float(stats["migrated"])], device=torch.device("cuda", rank), dtype=torch.float64)
+        dist.all_reduce(tot)
+        assert tot.item() > 0, "no particle migrated: the test does not exercise the exchange"
+        assert ds.n_own < len(st["points"]) and ds.sess.n > ds.n_own        # really decomposed, with ghosts
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-def test_two_slabs_match_single_process_oracle(built_lib):
+@pytest.mark.parametrize("world", [2, 4])
+def test_slabs_match_single_process_oracle(built_lib, world):
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
     import torch.multiprocessing as mp
-    mp.spawn(_worker, args=(2, _free_port(), 20000, 3), nprocs=2, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), 20000, 3), nprocs=world, join=True)
