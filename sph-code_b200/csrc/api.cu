@@ -79,6 +79,9 @@ int sphb200_set_option(sphb200_ctx* ctx, const char* name, double value) {
     if (g != 8 && g != 16 && g != 32) SPH_FAIL("knn_group must be 8, 16 or 32");
     ctx->knn_group = g;
   } else if (!strcmp(name, "knn_fast")) ctx->knn_fast = value != 0.0;
+  else if (!strcmp(name, "knn_atomic")) ctx->knn_atomic = value != 0.0;
+  else if (!strcmp(name, "knn_lane")) ctx->knn_lane = value != 0.0;
+  else if (!strcmp(name, "tile_cfg")) ctx->tile_cfg = (int)value;
   else if (!strcmp(name, "knn_margin")) { if (!(value >= 0)) SPH_FAIL("knn_margin must be >= 0"); ctx->knn_margin = value; }
   else SPH_FAIL("unknown option '%s'", name);
   return 0;
@@ -113,6 +116,7 @@ int sphb200_get_counter(sphb200_ctx* ctx, const char* name, int64_t* value_host,
   if (!strcmp(name, "knn_overflow")) return read_flag(ctx, FL_KNN_OVERFLOW, value_host, st);
   if (!strcmp(name, "knn_rescan")) return read_flag(ctx, FL_KNN_RESCAN, value_host, st);
   if (!strcmp(name, "knn_widen")) return read_flag(ctx, FL_KNN_WIDEN, value_host, st);
+  if (!strcmp(name, "knn_crowded")) return read_flag(ctx, FL_KNN_CROWDED, value_host, st);
   if (!strcmp(name, "knn_nonfinite")) return read_flag(ctx, FL_KNN_NONFINITE, value_host, st);
   if (!strcmp(name, "bad_index")) return read_flag(ctx, FL_BAD_INDEX, value_host, st);
   SPH_FAIL("unknown counter '%s'", name);
@@ -168,7 +172,7 @@ int sphb200_neighbors(sphb200_ctx* ctx, const double* points, int64_t n, int k, 
   SPH_TRY(check_nk(n, k));
   CUDA_TRY(cudaSetDevice(ctx->device));
   cudaStream_t st = as_stream(stream);
-  SPH_TRY(build_cells(ctx, points, n, ctx->cell_edge, nullptr, true, st));
+  SPH_TRY(build_cells(ctx, points, n, ctx->cell_edge, nullptr, k, true, st));
   SPH_TRY(devbuf_reserve(ctx->list, (size_t)n * k * sizeof(int32_t)));
   SPH_TRY(devbuf_reserve(ctx->tmp1, (size_t)n * k * sizeof(double)));
   SPH_TRY(devbuf_reserve(ctx->tmp2, (size_t)n * sizeof(double)));

@@ -12,16 +12,23 @@
 #define SCAN_TILE 2048             // elements per block of the scan (256 threads x 8)
 
 // ---- bounding box: per-block partial min/max of the finite coordinates ----
-__global__ void __launch_bounds__(256) bbox_partial_kernel(const double* __restrict__ pts, int64_t n, double* __restrict__ part) {
+#define BB_PART 8                  // doubles per block: min xyz, max xyz, sum of guess^-3, number of guesses
+__global__ void __launch_bounds__(256) bbox_partial_kernel(const double* __restrict__ pts, const double* __restrict__ guess,
+                                                           int64_t n, double* __restrict__ part) {
   double lo[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, hi[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
+  double dsum = 0.0, dcnt = 0.0;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
       const double v = pts[3 * i + a];
       if (isfinite(v)) { lo[a] = fmin(lo[a], v); hi[a] = fmax(hi[a], v); }
     }
+    if (guess) {
+      const double h = guess[i];
+      if (h > 0.0 && h < DBL_MAX) { dsum += 1.0 / (h * h * h); dcnt += 1.0; }
+    }
   }
-  __shared__ double sh[8][6];
+  __shared__ double sh[8][BB_PART];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
@@ -32,11 +39,18 @@ __global__ void __launch_bounds__(256) bbox_partial_kernel(const double* __restr
     }
     if (lane == 0) { sh[warp][a] = lo[a]; sh[warp][3 + a] = hi[a]; }
   }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    dsum += __shfl_xor_sync(0xffffffffu, dsum, d);
+    dcnt += __shfl_xor_sync(0xffffffffu, dcnt, d);
+  }
+  if (lane == 0) { sh[warp][6] = dsum; sh[warp][7] = dcnt; }
   __syncthreads();
-  if (threadIdx.x < 6) {
+  if (threadIdx.x < BB_PART) {
     double v = sh[0][threadIdx.x];
-    for (int w = 1; w < 8; ++w) v = (threadIdx.x < 3) ? fmin(v, sh[w][threadIdx.x]) : fmax(v, sh[w][threadIdx.x]);
-    part[blockIdx.x * 6 + threadIdx.x] = v;
+    for (int w = 1; w < 8; ++w)
+      v = (threadIdx.x < 3) ? fmin(v, sh[w][threadIdx.x]) : (threadIdx.x < 6) ? fmax(v, sh[w][threadIdx.x]) : v + sh[w][threadIdx.x];
+    part[blockIdx.x * BB_PART + threadIdx.x] = v;
   }
 }
 
@@ -82,21 +96,23 @@ __device__ void choose_grid(const double* bb, int64_t n, double occ, double edge
 }
 
 __global__ void __launch_bounds__(256)
-grid_choose_kernel(const double* __restrict__ part, int nblocks, int64_t n, double occ, double edge_hint, int max_cells,
+grid_choose_kernel(const double* __restrict__ part, int nblocks, int64_t n, double occ, double edge_hint, int knn_k, int max_cells,
                    GridSpec* __restrict__ spec, double* __restrict__ bbox_out) {
-  __shared__ double sh[256][6];
-  double v[6] = {DBL_MAX, DBL_MAX, DBL_MAX, -DBL_MAX, -DBL_MAX, -DBL_MAX};
+  __shared__ double sh[256][BB_PART];
+  double v[BB_PART] = {DBL_MAX, DBL_MAX, DBL_MAX, -DBL_MAX, -DBL_MAX, -DBL_MAX, 0.0, 0.0};
   for (int b = threadIdx.x; b < nblocks; b += blockDim.x)
 #pragma unroll
-    for (int a = 0; a < 6; ++a) v[a] = (a < 3) ? fmin(v[a], part[b * 6 + a]) : fmax(v[a], part[b * 6 + a]);
+    for (int a = 0; a < BB_PART; ++a)
+      v[a] = (a < 3) ? fmin(v[a], part[b * BB_PART + a]) : (a < 6) ? fmax(v[a], part[b * BB_PART + a]) : v[a] + part[b * BB_PART + a];
 #pragma unroll
-  for (int a = 0; a < 6; ++a) sh[threadIdx.x][a] = v[a];
+  for (int a = 0; a < BB_PART; ++a) sh[threadIdx.x][a] = v[a];
   __syncthreads();
   for (int s = 128; s > 0; s >>= 1) {
     if (threadIdx.x < s)
 #pragma unroll
-      for (int a = 0; a < 6; ++a)
-        sh[threadIdx.x][a] = (a < 3) ? fmin(sh[threadIdx.x][a], sh[threadIdx.x + s][a]) : fmax(sh[threadIdx.x][a], sh[threadIdx.x + s][a]);
+      for (int a = 0; a < BB_PART; ++a)
+        sh[threadIdx.x][a] = (a < 3) ? fmin(sh[threadIdx.x][a], sh[threadIdx.x + s][a])
+                           : (a < 6) ? fmax(sh[threadIdx.x][a], sh[threadIdx.x + s][a]) : sh[threadIdx.x][a] + sh[threadIdx.x + s][a];
     __syncthreads();
   }
   if (threadIdx.x == 0) {
@@ -105,6 +121,13 @@ grid_choose_kernel(const double* __restrict__ part, int nblocks, int64_t n, doub
     for (int a = 0; a < 6; ++a) bb[a] = sh[0][a];
     for (int a = 0; a < 3; ++a) if (!(bb[a] <= bb[3 + a])) ok = false;
     if (!ok) for (int a = 0; a < 6; ++a) bb[a] = 0.0;          // no finite coordinate: one cell, flagged
+    // With previous k-th neighbour distances at hand the cell edge follows the particles' own mean number
+    // density, n_p = mean_i k / (4 pi/3 h_i^3): a bounding box inflated by a few stragglers (or a dilute envelope
+    // around a dense cloud) then no longer makes the cells of the bulk hold more than `occ` particles.
+    if (!(edge_hint > 0.0) && knn_k > 0 && sh[0][7] >= 0.5 * (double)n) {
+      const double dens = (double)knn_k / 4.1887902047863905 * (sh[0][6] / sh[0][7]);
+      if (dens > 0.0 && dens < DBL_MAX) edge_hint = cbrt(occ / dens);
+    }
     GridSpec g;
     choose_grid(bb, n, occ, edge_hint, max_cells, &g);
     g.ok = ok ? 1 : 0;
@@ -319,8 +342,8 @@ void devbuf_free(DevBuf& b) {
 // ctx->keys the sorted cell keys, ctx->perm the sorted->source permutation, ctx->cell_start the
 // (ncells + 2) exclusive scan and ctx->r0 the sorted {x,y,z,guess} records.  Nothing synchronises unless
 // `sync_host` asks for the host copy ctx->grid (function-level API).
-int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint, const double* guess, bool sync_host,
-                cudaStream_t st) {
+int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint, const double* guess, int knn_k,
+                bool sync_host, cudaStream_t st) {
   if (n <= 0) SPH_FAIL("build_cells: empty particle set");
   if (n >= (int64_t)0x7fffffff) SPH_FAIL("build_cells: N=%lld exceeds the 2^31-1 particle limit per GPU", (long long)n);
   const int64_t max_cells64 = 2 * n + 4096;
@@ -328,7 +351,7 @@ int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint
   ctx->max_cells = max_cells;
   const int scan_blocks = ceil_div((int64_t)max_cells + 2, SCAN_TILE);
   SPH_TRY(devbuf_reserve(ctx->scal, SC_COUNT * sizeof(double)));
-  SPH_TRY(devbuf_reserve(ctx->tmp0, 64 + BB_BLOCKS * 6 * sizeof(double)));
+  SPH_TRY(devbuf_reserve(ctx->tmp0, 64 + BB_BLOCKS * BB_PART * sizeof(double)));
   SPH_TRY(devbuf_reserve(ctx->grid_dev, sizeof(GridSpec)));
   SPH_TRY(devbuf_reserve(ctx->keys, n * sizeof(uint32_t)));
   SPH_TRY(devbuf_reserve(ctx->keys_alt, n * sizeof(uint32_t)));
@@ -345,8 +368,8 @@ int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint
   uint32_t* rank = bufp<uint32_t>(ctx->perm_alt);
   int bb_blocks = ceil_div(n, 256); if (bb_blocks > BB_BLOCKS) bb_blocks = BB_BLOCKS;
   const int nblk = ceil_div(n, 256);
-  bbox_partial_kernel<<<bb_blocks, 256, 0, st>>>(pts, n, part);
-  grid_choose_kernel<<<1, 256, 0, st>>>(part, bb_blocks, n, ctx->cell_occ, edge_hint, max_cells, spec, scal + SC_BBOX);
+  bbox_partial_kernel<<<bb_blocks, 256, 0, st>>>(pts, guess, n, part);
+  grid_choose_kernel<<<1, 256, 0, st>>>(part, bb_blocks, n, ctx->cell_occ, edge_hint, knn_k, max_cells, spec, scal + SC_BBOX);
   zero_counts_kernel<<<148 * 4, 256, 0, st>>>(spec, cs);
   cell_key_kernel<<<nblk, 256, 0, st>>>(pts, n, spec, keys_src, rank, cs);
   scan_tiles_kernel<<<scan_blocks, 256, 0, st>>>(spec, 0, cs, bufp<uint32_t>(ctx->scan_tops));

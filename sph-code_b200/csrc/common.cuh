@@ -97,8 +97,11 @@ struct sphb200_ctx {
   double cell_occ = 16.0;          // target mean particles per cell (tunable)
   double cell_edge = 0.0;          // fixed cell edge (0 = from cell_occ)
   int knn_group = 32;              // lanes per target in the general k-NN kernel
+  int tile_cfg = 0;                // pair passes: 0 two stages per CTA, 1 one stage and more resident CTAs (hydro.cu)
+  int knn_lane = 0;                // session fast path: lane-per-target kernel (knn_lane.cu); 0: warp-per-target (knn_group.cu)
+  int knn_atomic = 0;              // fast path: filter survivors reserve their slot with shared-memory atomics
   int knn_fast = 1;                // 1: cell-tiled fast path (knn_cell.cu), 0: general kernel only
-  double knn_margin = 0.02;        // trial radius = previous k-th distance * (1 + margin)
+  double knn_margin = 0.10;        // trial radius = previous k-th distance * (1 + margin)
   GridSpec grid;                   // host copy; valid only after build_cells(..., sync_host = true)
   int max_cells = 0;               // capacity of cell_start the device-side grid choice may use
   int list_is_global = 0;          // 1: ctx->list holds int32 rows for EVERY particle (function API / restored checkpoint)

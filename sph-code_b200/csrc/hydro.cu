@@ -27,6 +27,7 @@
 
 #define HY_THREADS 256
 #define HY_G 8                 // lanes per target
+#define HY_U 7                 // neighbours per lane the unrolled loop covers (k <= 56)
 
 // ---------------------------------------------------------------------------------------------
 // Records (sorted order in the session, caller order in the function-level API)
@@ -42,6 +43,38 @@ struct __align__(16) RecD { double x, y, z, h2s, wA, wB; };
 struct __align__(16) RecP { double x, y, z, h2, vx, vy, vz, AK, cs, rho; };
 
 __device__ __forceinline__ double2 ld2(const double* p) { return *reinterpret_cast<const double2*>(p); }
+
+// A record as the pair functions see it: in global memory (LIST form) or in shared memory (TILE form).  The shared
+// form carries the 32-bit shared-window address and loads with ld.shared, so that the compiler never falls back to
+// generic loads (LD.E on a shared address is several times slower than LDS).
+struct RecG {
+  const double* p;
+  __device__ __forceinline__ double2 v2(int i) const { return *reinterpret_cast<const double2*>(p + i); }
+  __device__ __forceinline__ double v1(int i) const { return p[i]; }
+};
+struct RecS {
+  uint32_t a;
+  __device__ __forceinline__ double2 v2(int i) const {
+    double2 r;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(r.x), "=d"(r.y) : "r"(a + 8u * (uint32_t)i));
+    return r;
+  }
+  __device__ __forceinline__ double v1(int i) const {
+    double r;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(r) : "r"(a + 8u * (uint32_t)i));
+    return r;
+  }
+};
+__device__ __forceinline__ unsigned lds_u16(uint32_t addr) {
+  unsigned short v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
+  return (unsigned)v;
+}
+__device__ __forceinline__ double lds_f64(uint32_t addr) {
+  double r;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(r) : "r"(addr));
+  return r;
+}
 
 __global__ void __launch_bounds__(256)
 pack_kernel(int n, PackIn in, PhysConst pc, const double4* __restrict__ r0, RecD* __restrict__ rd, RecP* __restrict__ rp,
@@ -129,12 +162,12 @@ struct DensityPass {
   struct Acc { double rho, num, dust; };
   __device__ static const char* records(const Params& p) { return reinterpret_cast<const char*>(p.rec); }
   __device__ static void zero(Acc& a) { a.rho = a.num = a.dust = 0.0; }
-  __device__ static void self(Self& s, const double* pos, const double*, int, const Params&) {
-    const double2 a = ld2(pos), b = ld2(pos + 2);
+  template <class R> __device__ static void self(Self& s, R pos, R, int, const Params&) {
+    const double2 a = pos.v2(0), b = pos.v2(2);
     s.x = a.x; s.y = a.y; s.z = b.x;
   }
-  __device__ static void pair(Acc& a, const Self& s, const double* r, double) {
-    const double2 xy = ld2(r), zh = ld2(r + 2), w = ld2(r + 4);
+  template <class R> __device__ static void pair(Acc& a, const Self& s, R r, double) {
+    const double2 xy = r.v2(0), zh = r.v2(2), w = r.v2(4);
     const double dx = xy.x - s.x, dy = xy.y - s.y, dz = zh.x - s.z;
     const double r2 = dx * dx + dy * dy + dz * dz;
     const double t = fabs(zh.y) - r2;
@@ -166,13 +199,13 @@ struct PiPass {
   struct Acc { double v; };
   __device__ static const char* records(const Params& p) { return reinterpret_cast<const char*>(p.rec); }
   __device__ static void zero(Acc& a) { a.v = 0.0; }
-  __device__ static void self(Self& s, const double* pos, const double* own, int, const Params&) {
-    const double2 a = ld2(pos), b = ld2(pos + 2), c = ld2(pos + 4), d = ld2(pos + 6), e = ld2(own + 8);
+  template <class R> __device__ static void self(Self& s, R pos, R own, int, const Params&) {
+    const double2 a = pos.v2(0), b = pos.v2(2), c = pos.v2(4), d = pos.v2(6), e = own.v2(8);
     s.x = a.x; s.y = a.y; s.z = b.x; s.vx = c.x; s.vy = c.y; s.vz = d.x;
     s.cs_i = e.x; s.rho_i = e.y;
   }
-  __device__ static void pair(Acc& a, const Self& s, const double* r, double) {
-    const double2 xy = ld2(r), zh = ld2(r + 2), v01 = ld2(r + 4), v2a = ld2(r + 6), cr = ld2(r + 8);
+  template <class R> __device__ static void pair(Acc& a, const Self& s, R r, double) {
+    const double2 xy = r.v2(0), zh = r.v2(2), v01 = r.v2(4), v2a = r.v2(6), cr = r.v2(8);
     const double dx = xy.x - s.x, dy = xy.y - s.y, dz = zh.x - s.z;
     const double dvx = v01.x - s.vx, dvy = v01.y - s.vy, dvz = v2a.x - s.vz;
     const double r2 = dx * dx + dy * dy + dz * dz;
@@ -203,18 +236,19 @@ struct ForcePass {
   static constexpr int REC = 80;
   static constexpr bool USE_K = true, HAS_FINAL = false;
   struct Params { const RecP* rec; const double* recK; const double* mass; double* hacc; double* vacc; double* heat; };
-  struct Self { double x, y, z, vx, vy, vz, h2_i, AK_i, PK_i, rho_i; };
+  struct Self { double x, y, z, vx, vy, vz, h2_i, AK_i, PK_i, rho_i, m_i; };
   struct Acc { double px, py, pz, qx, qy, qz, qh; };
   __device__ static const char* records(const Params& p) { return reinterpret_cast<const char*>(p.rec); }
   __device__ static void zero(Acc& a) { a.px = a.py = a.pz = a.qx = a.qy = a.qz = a.qh = 0.0; }
-  __device__ static void self(Self& s, const double* pos, const double* own, int i, const Params& p) {
-    const double2 a = ld2(pos), b = ld2(pos + 2), c = ld2(pos + 4), d = ld2(pos + 6);
+  template <class R> __device__ static void self(Self& s, R pos, R own, int i, const Params& p) {
+    const double2 a = pos.v2(0), b = pos.v2(2), c = pos.v2(4), d = pos.v2(6);
     s.x = a.x; s.y = a.y; s.z = b.x; s.vx = c.x; s.vy = c.y; s.vz = d.x;
-    s.h2_i = own[3]; s.AK_i = own[7]; s.rho_i = own[9];
+    s.h2_i = own.v1(3); s.AK_i = own.v1(7); s.rho_i = own.v1(9);
     s.PK_i = p.recK[i];
+    s.m_i = p.mass[i];                                    // fetched early: its latency hides behind the pair loop
   }
-  __device__ static void pair(Acc& a, const Self& s, const double* r, double PK_j) {
-    const double2 xy = ld2(r), zh = ld2(r + 2), v01 = ld2(r + 4), v2a = ld2(r + 6);
+  template <class R> __device__ static void pair(Acc& a, const Self& s, R r, double PK_j) {
+    const double2 xy = r.v2(0), zh = r.v2(2), v01 = r.v2(4), v2a = r.v2(6);
     const double dx = xy.x - s.x, dy = xy.y - s.y, dz = zh.x - s.z;
     const double r2 = dx * dx + dy * dy + dz * dz;
     const double tb = zh.y - r2, ta = s.h2_i - r2;
@@ -243,7 +277,7 @@ struct ForcePass {
     p.vacc[3 * (int64_t)i + 0] = 0.5 * a.qx;
     p.vacc[3 * (int64_t)i + 1] = 0.5 * a.qy;
     p.vacc[3 * (int64_t)i + 2] = 0.5 * a.qz;
-    p.heat[i] = -0.25 * p.mass[i] * a.qh;
+    p.heat[i] = -0.25 * s.m_i * a.qh;
   }
   __device__ static void final_init(Final&) {}
   __device__ static void final_flush(Final&, const Params&) {}
@@ -260,11 +294,11 @@ struct CrossingPass {
   struct Acc { double mx; int nan; };
   __device__ static const char* records(const Params& p) { return reinterpret_cast<const char*>(p.vel); }
   __device__ static void zero(Acc& a) { a.mx = 0.0; a.nan = 0; }
-  __device__ static void self(Self& s, const double*, const double* own, int, const Params&) {
-    s.vx = own[0]; s.vy = own[1]; s.vz = own[2];
+  template <class R> __device__ static void self(Self& s, R, R own, int, const Params&) {
+    s.vx = own.v1(0); s.vy = own.v1(1); s.vz = own.v1(2);
   }
-  __device__ static void pair(Acc& a, const Self& s, const double* r, double) {
-    const double ax = r[0] - s.vx, ay = r[1] - s.vy, az = r[2] - s.vz;
+  template <class R> __device__ static void pair(Acc& a, const Self& s, R r, double) {
+    const double ax = r.v1(0) - s.vx, ay = r.v1(1) - s.vy, az = r.v1(2) - s.vz;
     const double v2 = ax * ax + ay * ay + az * az;
     if (v2 != v2) a.nan = 1;                             // np.max propagates NaN
     a.mx = fmax(a.mx, v2);
@@ -303,162 +337,224 @@ struct CrossingPass {
 };
 
 // ---------------------------------------------------------------------------------------------
-// TILE form
+// TILE form: producer / consumer pipeline over the half-groups of cells.
+// One producer warp computes the geometry of the NEXT unit and issues its bulk copies (records of the three
+// z-layers, the 8-byte coefficients, the uint16 rows of the unit's targets) into the other of two shared-memory
+// stages while the consumer warps work on the current one; "full" / "empty" mbarriers hand the stages over, so
+// the DRAM / L2 latency of a tile is hidden behind the arithmetic of the previous tile.
 // ---------------------------------------------------------------------------------------------
 struct TilePassArgs {
   const GridSpec* spec;
   const uint32_t* cell_start;
-  const uint16_t* list16;      // (N,k) tile offsets
+  const uint16_t* list16;      // (N, LIST_STRIDE(k)) tile offsets
   int n, k;
 };
 
-struct TpMisc {
-  int tbegin[2], tend[2], tbase[3];
-  int len[4];
-  int o_lo, r_lo, r_hi, crowded;
-  uint64_t bar;
+struct TpMeta {                // what the consumers need to know about a staged unit
+  int tbegin[2], tbase[3];
+  int o_lo, ntgt;
 };
 
 template <class P>
-__global__ void __launch_bounds__(HY_THREADS) tile_pass_kernel(TilePassArgs a, typename P::Params p) {
+struct TpLayout {              // byte offsets inside one stage
+  static constexpr int OFF_K = TILE_HALF_CAP * P::REC;
+  static constexpr int OFF_L = OFF_K + (P::USE_K ? TILE_HALF_CAP * 8 : 0);
+  __host__ __device__ static int off_meta(int ks) { return (OFF_L + TILE_HALF_TARGETS * ks * 2 + 15) & ~15; }
+  __host__ __device__ static int stage_bytes(int ks) { return (off_meta(ks) + (int)sizeof(TpMeta) + 127) & ~127; }
+};
+
+// geometry of one unit as the producer warp holds it in registers between "computed" and "issued"
+struct TpGeom {
+  int skip;                  // nothing to do for this unit (warp-uniform)
+  int b0, b1, l0, l1, o_lo;  // target runs of the half-group, first staged tile offset (warp-uniform)
+  int plen, o, ps;           // this lane's row: padded length, tile offset relative to o_lo, first padded sorted index
+};
+
+template <class P, int NCW, int NS>
+__global__ void __launch_bounds__(32 * (NCW + 1), (NS == 1) ? 2 : 1) tile_pass_kernel(TilePassArgs a, typename P::Params p) {
   extern __shared__ __align__(128) unsigned char smem[];
-  // layout: records [TILE_HALF_CAP * REC] | K [TILE_HALF_CAP * 8 if USE_K] | rows uint16 [TILE_HALF_TARGETS * k] | TileRows | misc
-  constexpr int OFF_K = TILE_HALF_CAP * P::REC;
-  constexpr int OFF_L = OFF_K + (P::USE_K ? TILE_HALF_CAP * 8 : 0);
-  unsigned char* trec = smem;
-  double* tk = reinterpret_cast<double*>(smem + OFF_K);
-  uint16_t* rowsm = reinterpret_cast<uint16_t*>(smem + OFF_L);
-  const int off_rows = (OFF_L + TILE_HALF_TARGETS * a.k * 2 + 15) & ~15;
-  TileRows* rows = reinterpret_cast<TileRows*>(smem + off_rows);
-  TpMisc* misc = reinterpret_cast<TpMisc*>(smem + off_rows + 384);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int ks = LIST_STRIDE(a.k);
+  const int stage_bytes = TpLayout<P>::stage_bytes(ks);
+  TileRows* rows = reinterpret_cast<TileRows*>(smem + NS * stage_bytes);               // producer's scratch
+  int* plen4 = reinterpret_cast<int*>(smem + NS * stage_bytes + 384);                   // target run lengths (producer)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NS * stage_bytes + 384 + 32);     // full[NS], empty[NS]
   const GridSpec g = *a.spec;
   const char* grec = P::records(p);
   const double* gk = P::kptr(p);
-  if (tid == 0) { mbar_init(&misc->bar, 1); mbar_fence_init(); }
-  uint32_t phase = 0;
-  typename P::Final fin;
-  P::final_init(fin);
+  if (tid == 0) {
+    for (int s = 0; s < NS; ++s) { mbar_init(&bars[s], 1); mbar_init(&bars[NS + s], NCW); }
+    mbar_fence_init();
+  }
+  __syncthreads();
   const int nunits = 2 * g.ngroups;
-  for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
-    const int group = unit >> 1, hz = unit & 1;
-    int gx, gy, gz;
-    group_coords(g, group, &gx, &gy, &gz);
-    const int cz = 2 * gz + hz;
-    if (cz >= g.nz) continue;
-    __syncthreads();                                          // previous unit done with every buffer
-    if (warp == 0) {
+
+  if (warp == NCW) {
+    // ================= producer warp =================
+    // The geometry of a unit (cell_start lookups: dependent global loads) is computed one unit AHEAD, while the
+    // previous unit's copies are in flight, so that a freed stage is refilled after one mbarrier wait only.
+    auto geometry = [&](int unit) -> TpGeom {
+      TpGeom gm;
+      gm.skip = 1; gm.b0 = gm.b1 = gm.l0 = gm.l1 = gm.o_lo = 0; gm.plen = gm.o = gm.ps = 0;
+      if (unit >= nunits) return gm;
+      const int group = unit >> 1, hz = unit & 1;
+      int gx, gy, gz;
+      group_coords(g, group, &gx, &gy, &gz);
+      const int cz = 2 * gz + hz;
+      if (cz >= g.nz) return gm;
+      __syncwarp();
       tile_rows(g, a.cell_start, gx, gy, gz, lane, rows);
       int b = 0, e = 0, r = 0;
       const bool have = (lane < 4) && group_target_run(g, a.cell_start, gx, gy, gz, lane, &b, &e, &r);
-      if (lane < 4) misc->len[lane] = have ? (e - b) : 0;
-      if ((lane >> 1) == hz && lane < 4) { misc->tbegin[lane & 1] = b; misc->tend[lane & 1] = have ? e : b; }
-    }
-    __syncthreads();
-    if (tid == 0) {
-      const int l0 = misc->tend[0] - misc->tbegin[0], l1 = misc->tend[1] - misc->tbegin[1];
-      misc->tbase[0] = 0; misc->tbase[1] = l0; misc->tbase[2] = l0 + l1;
-      const int zlo = max(cz - 1, 0), zhi = min(cz + 1, g.nz - 1);
-      misc->r_lo = (zlo - rows->z0) * rows->ysp;
-      misc->r_hi = (zhi - rows->z0 + 1) * rows->ysp;
-      misc->o_lo = rows->toff[misc->r_lo];
-      // the same decision the k-NN kernel took for this group: the targets of a crowded group have global rows
-      misc->crowded = tile_crowded(g, rows, misc->len) ? 1 : 0;
-    }
-    __syncthreads();
-    const int ntgt = misc->tbase[2];
-    if (ntgt == 0 || misc->crowded) continue;
-    const int o_lo = misc->o_lo;
-    // ---- stage: one bulk copy per row of records (+ the 8-byte coefficients); the targets' rows by plain loads ----
-    if (warp == 0) {
-      fence_proxy_async();
-      const int r = misc->r_lo + lane;
-      const bool on = r < misc->r_hi;
-      const int plen = on ? (rows->toff[r + 1] - rows->toff[r]) : 0;
-      unsigned tot = (unsigned)plen * (unsigned)(P::REC + (P::USE_K ? 8 : 0));
-#pragma unroll
-      for (int d = 16; d > 0; d >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, d);
-      if (lane == 0) mbar_expect_tx(&misc->bar, tot);
+      if (lane < 4) plen4[lane] = have ? (e - b) : 0;
+      gm.b0 = __shfl_sync(0xffffffffu, b, 2 * hz);
+      gm.b1 = __shfl_sync(0xffffffffu, b, 2 * hz + 1);
+      gm.l0 = __shfl_sync(0xffffffffu, have ? e - b : 0, 2 * hz);
+      gm.l1 = __shfl_sync(0xffffffffu, have ? e - b : 0, 2 * hz + 1);
       __syncwarp();
-      if (plen) {
-        const int o = rows->toff[r] - o_lo, ps = rows->ps[r];
-        bulk_g2s(trec + (size_t)o * P::REC, grec + (size_t)ps * P::REC, (unsigned)plen * P::REC, &misc->bar);
-        if (P::USE_K) bulk_g2s(tk + o, gk + ps, (unsigned)plen * 8u, &misc->bar);
+      const int zlo = max(cz - 1, 0), zhi = min(cz + 1, g.nz - 1);
+      const int r_lo = (zlo - rows->z0) * rows->ysp, r_hi = (zhi - rows->z0 + 1) * rows->ysp;
+      gm.o_lo = rows->toff[r_lo];
+      // the same decision the k-NN kernel took for this group: the targets of a crowded group have global rows
+      gm.skip = (gm.l0 + gm.l1 == 0) || tile_crowded(g, rows, plen4);
+      const int rr = r_lo + lane;
+      if (rr < r_hi) { gm.plen = rows->toff[rr + 1] - rows->toff[rr]; gm.o = rows->toff[rr] - gm.o_lo; gm.ps = rows->ps[rr]; }
+      __syncwarp();
+      return gm;
+    };
+    int it = 0;
+    TpGeom gm = geometry(blockIdx.x);
+    for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x, ++it) {
+      const int s = it % NS, j = it / NS;
+      if (j >= 1) mbar_wait(&bars[NS + s], (j - 1) & 1);                   // the consumers released this stage
+      unsigned char* sb = smem + s * stage_bytes;
+      TpMeta* meta = reinterpret_cast<TpMeta*>(sb + TpLayout<P>::off_meta(ks));
+      if (lane == 0) {
+        meta->tbegin[0] = gm.b0; meta->tbegin[1] = gm.b1;
+        meta->tbase[0] = 0; meta->tbase[1] = gm.l0; meta->tbase[2] = gm.l0 + gm.l1;
+        meta->o_lo = gm.o_lo;
+        meta->ntgt = gm.skip ? 0 : gm.l0 + gm.l1;
       }
-    }
-    {
-      const int k = a.k;
-#pragma unroll 1
-      for (int q = 0; q < 2; ++q) {
-        const int len = (misc->tend[q] - misc->tbegin[q]) * k;
-        const uint16_t* src = a.list16 + (int64_t)misc->tbegin[q] * k;
-        uint16_t* dst = rowsm + misc->tbase[q] * k;
-        if ((((size_t)src | (size_t)dst) & 3) == 0) {
-          const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
-          uint32_t* d32 = reinterpret_cast<uint32_t*>(dst);
-          for (int e = tid; e < (len >> 1); e += HY_THREADS) d32[e] = s32[e];
-          if ((len & 1) && tid == 0) dst[len - 1] = src[len - 1];
-        } else {
-          for (int e = tid; e < len; e += HY_THREADS) dst[e] = src[e];
+      __syncwarp();
+      if (gm.skip) {
+        if (lane == 0) mbar_expect_tx(&bars[s], 0u);                        // plain arrival: nothing to copy
+      } else {
+        fence_proxy_async();
+        unsigned tot = (unsigned)gm.plen * (unsigned)(P::REC + (P::USE_K ? 8 : 0));
+        if (lane == 0) tot += (unsigned)(gm.l0 + gm.l1) * (unsigned)(ks * 2);
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, d);
+        if (lane == 0) mbar_expect_tx(&bars[s], tot);
+        __syncwarp();
+        if (gm.plen) {
+          bulk_g2s(sb + (size_t)gm.o * P::REC, grec + (size_t)gm.ps * P::REC, (unsigned)gm.plen * P::REC, &bars[s]);
+          if (P::USE_K) bulk_g2s(sb + TpLayout<P>::OFF_K + (size_t)gm.o * 8, gk + gm.ps, (unsigned)gm.plen * 8u, &bars[s]);
         }
+        uint16_t* rowsm = reinterpret_cast<uint16_t*>(sb + TpLayout<P>::OFF_L);
+        if (lane == 0 && gm.l0) bulk_g2s(rowsm, a.list16 + (int64_t)gm.b0 * ks, (unsigned)gm.l0 * ks * 2u, &bars[s]);
+        if (lane == 1 && gm.l1) bulk_g2s(rowsm + (size_t)gm.l0 * ks, a.list16 + (int64_t)gm.b1 * ks, (unsigned)gm.l1 * ks * 2u, &bars[s]);
       }
+      gm = geometry(unit + gridDim.x);                                      // next unit, while these copies fly
     }
-    mbar_wait(&misc->bar, phase);
-    phase ^= 1u;
-    __syncthreads();
-    // ---- targets: HY_G lanes each ----
-    const int sub = lane & (HY_G - 1);
-    for (int t0 = 0; t0 < ntgt; t0 += (HY_THREADS / HY_G)) {
-      const int t = t0 + warp * (32 / HY_G) + (lane / HY_G);
-      const bool valid = t < ntgt;
-      const int q = (valid && t >= misc->tbase[1]) ? 1 : 0;
-      const int i = valid ? misc->tbegin[q] + (t - misc->tbase[q]) : 0;
-      const uint16_t* row = rowsm + (valid ? t : 0) * a.k;
-      const unsigned s0 = row[0];
-      const bool active = valid && s0 < LIST_MISSING;
-      typename P::Self self;
-      typename P::Acc acc;
-      P::zero(acc);
-      if (active) {
-        const double* rs = reinterpret_cast<const double*>(trec + (size_t)(s0 - o_lo) * P::REC);
-        P::self(self, rs, rs, i, p);
-        for (int s = sub; s < a.k; s += HY_G) {
-          const unsigned o = row[s];
-          if (o >= LIST_MISSING) continue;
-          const double* r = reinterpret_cast<const double*>(trec + (size_t)(o - o_lo) * P::REC);
-          P::pair(acc, self, r, P::USE_K ? tk[o - o_lo] : 0.0);
+    return;
+  }
+  // ================= consumer warps =================
+  typename P::Final fin;
+  P::final_init(fin);
+  const int sub = lane & (HY_G - 1);
+  int it = 0;
+  for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x, ++it) {
+    const int s = it % NS;
+    mbar_wait(&bars[s], (it / NS) & 1);                                     // the stage is filled
+    const unsigned char* sb = smem + s * stage_bytes;
+    const TpMeta* meta = reinterpret_cast<const TpMeta*>(sb + TpLayout<P>::off_meta(ks));
+    const int ntgt = meta->ntgt;
+    if (ntgt > 0) {
+      const uint32_t trec = smem_u32(sb);
+      const uint32_t tk = smem_u32(sb + TpLayout<P>::OFF_K);
+      const uint32_t rowsm = smem_u32(sb + TpLayout<P>::OFF_L);
+      const int o_lo = meta->o_lo, tb1 = meta->tbase[1], b0 = meta->tbegin[0], b1 = meta->tbegin[1];
+      for (int t0 = 0; t0 < ntgt; t0 += NCW * (32 / HY_G)) {
+        const int t = t0 + warp * (32 / HY_G) + (lane / HY_G);
+        const bool valid = t < ntgt;
+        const int i = valid ? ((t >= tb1) ? b1 + (t - tb1) : b0 + t) : 0;
+        const uint32_t row = rowsm + (uint32_t)((valid ? t : 0) * ks) * 2u;
+        const unsigned s0 = lds_u16(row);
+        const bool active = valid && s0 < LIST_MISSING;
+        typename P::Self self;
+        typename P::Acc acc;
+        P::zero(acc);
+        if (active) {
+          const RecS rs = {trec + (uint32_t)(s0 - o_lo) * (uint32_t)P::REC};
+          P::self(self, rs, rs, i, p);
+          if (lds_u16(row + 2u * (uint32_t)(a.k - 1)) < LIST_MISSING) {
+            // full row (missing entries sit at the end): branch-free, unrolled, so that the shared-memory reads of
+            // up to HY_U neighbours are in flight together
+            unsigned oo[HY_U];
+#pragma unroll
+            for (int u = 0; u < HY_U; ++u) oo[u] = (sub + HY_G * u < a.k) ? lds_u16(row + 2u * (uint32_t)(sub + HY_G * u)) : s0;
+#pragma unroll
+            for (int u = 0; u < HY_U; ++u) {
+              if (sub + HY_G * u < a.k) {
+                const RecS r = {trec + (uint32_t)(oo[u] - o_lo) * (uint32_t)P::REC};
+                P::pair(acc, self, r, P::USE_K ? lds_f64(tk + 8u * (uint32_t)(oo[u] - o_lo)) : 0.0);
+              }
+            }
+          } else {
+            for (int e = sub; e < a.k; e += HY_G) {
+              const unsigned o = lds_u16(row + 2u * (uint32_t)e);
+              if (o >= LIST_MISSING) continue;
+              const RecS r = {trec + (uint32_t)(o - o_lo) * (uint32_t)P::REC};
+              P::pair(acc, self, r, P::USE_K ? lds_f64(tk + 8u * (uint32_t)(o - o_lo)) : 0.0);
+            }
+          }
         }
+        const bool escaped = valid && s0 == LIST_ESCAPED;      // its row is in the global list: the LIST form writes it
+        P::store(acc, self, i, sub == 0 && valid && !escaped, active, p, fin);
       }
-      const bool escaped = valid && s0 == LIST_ESCAPED;        // its row is in the global list: the LIST form writes it
-      P::store(acc, self, i, sub == 0 && valid && !escaped, active, p, fin);
     }
+    __syncwarp();
+    if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&bars[NS + s])) : "memory");
   }
   if (P::HAS_FINAL) P::final_flush(fin, p);
 }
 
 template <class P>
-static int tile_pass_smem(int k) {
-  const int off_l = TILE_HALF_CAP * P::REC + (P::USE_K ? TILE_HALF_CAP * 8 : 0);
-  return ((off_l + TILE_HALF_TARGETS * k * 2 + 15) & ~15) + 384 + (int)sizeof(TpMisc) + 16;
+static int tile_pass_smem(int k, int ns) {
+  return ns * TpLayout<P>::stage_bytes(LIST_STRIDE(k)) + 384 + 32 + 64;
 }
 
-template <class P>
-static int launch_tile_pass(sphb200_ctx* ctx, int n, int k, const uint16_t* list16, const typename P::Params& p, cudaStream_t st) {
+template <class P, int NCW, int NS>
+static int launch_tile_pass_n(sphb200_ctx* ctx, int n, int k, const uint16_t* list16, const typename P::Params& p, int per_sm,
+                              cudaStream_t st) {
   TilePassArgs a;
   a.spec = bufp<GridSpec>(ctx->grid_dev);
   a.cell_start = bufp<uint32_t>(ctx->cell_start);
   a.list16 = list16;
   a.n = n; a.k = k;
-  const int smem = tile_pass_smem<P>(k);
-  if (smem > 220 * 1024) SPH_FAIL("tile pass: k=%d needs %d B of shared memory", k, smem);
-  CUDA_TRY(cudaFuncSetAttribute(tile_pass_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  int per_sm = (227 * 1024) / (smem + 1024);
-  if (per_sm < 1) per_sm = 1;
-  if (per_sm > 8) per_sm = 8;
-  tile_pass_kernel<P><<<148 * per_sm, HY_THREADS, smem, st>>>(a, p);
+  const int smem = tile_pass_smem<P>(k, NS);
+  CUDA_TRY(cudaFuncSetAttribute(tile_pass_kernel<P, NCW, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  tile_pass_kernel<P, NCW, NS><<<148 * per_sm, 32 * (NCW + 1), smem, st>>>(a, p);
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;
+}
+
+// tile_cfg 0: two stages per CTA (the producer runs a whole tile ahead), as many CTAs per SM as shared memory allows;
+//          1: one stage per CTA and two or more resident CTAs (more consumer warps per SM, fills hidden by the other CTAs)
+template <class P>
+static int launch_tile_pass(sphb200_ctx* ctx, int n, int k, const uint16_t* list16, const typename P::Params& p, cudaStream_t st) {
+  if (ctx->tile_cfg == 1) {
+    const int smem1 = tile_pass_smem<P>(k, 1);
+    const int per1 = (227 * 1024) / (smem1 + 1024);
+    if (per1 >= 2) return launch_tile_pass_n<P, 12, 1>(ctx, n, k, list16, p, per1 > 4 ? 4 : per1, st);
+  }
+  const int smem = tile_pass_smem<P>(k, 2);
+  if (smem > 226 * 1024) SPH_FAIL("tile pass: k=%d needs %d B of shared memory", k, smem);
+  const int per_sm = (227 * 1024) / (smem + 1024);
+  // one resident CTA: 16 consumer warps; two or more: 8 each
+  if (per_sm <= 1) return launch_tile_pass_n<P, 16, 2>(ctx, n, k, list16, p, 1, st);
+  return launch_tile_pass_n<P, 8, 2>(ctx, n, k, list16, p, per_sm > 3 ? 3 : per_sm, st);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -497,13 +593,14 @@ __global__ void __launch_bounds__(HY_THREADS) list_pass_kernel(ListPassArgs a, t
     if (active) {
       const int js = row[0];
       __align__(16) double zrec[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-      const double* own = reinterpret_cast<const double*>(grec + (size_t)i * P::REC);
-      const double* pos = (js >= 0 && js < a.n) ? reinterpret_cast<const double*>(grec + (size_t)js * P::REC) : zrec;
+      const RecG own = {reinterpret_cast<const double*>(grec + (size_t)i * P::REC)};
+      const RecG pos = {(js >= 0 && js < a.n) ? reinterpret_cast<const double*>(grec + (size_t)js * P::REC) : zrec};
       P::self(self, pos, own, i, p);
       for (int s = sub; s < a.k; s += HY_G) {
         const int j = row[s];
         if (j < 0 || j >= a.n) continue;
-        P::pair(acc, self, reinterpret_cast<const double*>(grec + (size_t)j * P::REC), P::USE_K ? gk[j] : 0.0);
+        const RecG r = {reinterpret_cast<const double*>(grec + (size_t)j * P::REC)};
+        P::pair(acc, self, r, P::USE_K ? gk[j] : 0.0);
       }
     }
     P::store(acc, self, i, sub == 0 && valid, active, p, fin);
@@ -741,7 +838,7 @@ expand_list_kernel(int n, int k, const GridSpec* __restrict__ spec, const uint32
                    int32_t* __restrict__ out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const uint16_t* row = list16 + (int64_t)i * k;
+  const uint16_t* row = list16 + (int64_t)i * LIST_STRIDE(k);
   int32_t* o = out + (int64_t)i * k;
   const unsigned s0 = row[0];
   if (s0 == LIST_ESCAPED) {

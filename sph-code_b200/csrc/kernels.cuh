@@ -4,8 +4,8 @@
 
 // cells.cu: cell list on the device; guess = previous k-th distances in SOURCE order (nullptr: none); sync_host
 // copies the chosen grid back to ctx->grid (function-level API only: one host synchronisation)
-int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint, const double* guess, bool sync_host,
-                cudaStream_t st);
+int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint, const double* guess, int knn_k,
+                bool sync_host, cudaStream_t st);
 
 int scan_exclusive_u32(sphb200_ctx* ctx, uint32_t* a, int m, cudaStream_t st);
 
@@ -23,6 +23,9 @@ int launch_knn_worklist(sphb200_ctx* ctx, int n, int k, double dist, int use_gue
 int knn_group_max_k();
 int launch_knn_group(sphb200_ctx* ctx, int n, int k, double dist, int use_guess, double margin, uint16_t* list16,
                      int32_t* list, double* dists, double* h_out, int32_t* nontriv, cudaStream_t st);
+// knn_lane.cu (session fast path: one target per lane, single trial radius, misses go to the general kernel)
+int launch_knn_lane(sphb200_ctx* ctx, int n, int k, double dist, int use_guess, double margin, uint16_t* list16,
+                    int32_t* list, double* h_out, int32_t* nontriv, cudaStream_t st);
 int launch_knn_unsort(sphb200_ctx* ctx, const int32_t* list, const double* dists, const double* h, const int32_t* nontriv,
                       int n, int k, int64_t* idx_out, double* dist_out, int64_t* nontriv_out, double* h_out,
                       cudaStream_t st);

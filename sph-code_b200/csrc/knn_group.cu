@@ -73,6 +73,7 @@ struct KgMisc {
   int group;
   int pad;
   uint64_t bar;
+  int cntF[KG_WARPS];                           // filter survivors of the warp's current target (atomic variant)
 };
 
 // Warp-wide maximum of (key, idx) pairs in lexicographic order (exact; used when float keys tie).
@@ -161,7 +162,7 @@ __device__ __forceinline__ double knn_emit(const KnnGroupArgs& a, int i, int sel
     int ps = -1;                                             // position of self among the kept entries
     if (s0) ps = __popc(b0 & ((1u << (__ffs(s0) - 1)) - 1u));
     else if (s1) ps = __popc(b0) + __popc(b1 & ((1u << (__ffs(s1) - 1)) - 1u));
-    uint16_t* out = a.list16 + row;
+    uint16_t* out = a.list16 + (int64_t)i * LIST_STRIDE(k);
     if (i0 >= 0) { const int pos = __popc(b0 & lt); out[(pos == ps) ? 0 : (pos < ps ? pos + 1 : pos)] = (uint16_t)i0; }
     if (i1 >= 0) { const int pos = __popc(b0) + __popc(b1 & lt); out[(pos == ps) ? 0 : (pos < ps ? pos + 1 : pos)] = (uint16_t)i1; }
     for (int s = nsel + lane; s < k; s += 32) out[s] = (uint16_t)LIST_MISSING;
@@ -170,89 +171,171 @@ __device__ __forceinline__ double knn_emit(const KnnGroupArgs& a, int i, int sel
   return (nsel > 0 && km > 0.0) ? km : 0.0;
 }
 
+// packed fp32 pairs (FADD2 / FMUL2 / FFMA2 on sm_100a): two candidates per instruction
+__device__ __forceinline__ unsigned long long f2_sub(unsigned long long a, unsigned long long b) {
+  unsigned long long r; asm("sub.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r;
+}
+__device__ __forceinline__ unsigned long long f2_mul(unsigned long long a, unsigned long long b) {
+  unsigned long long r; asm("mul.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r;
+}
+__device__ __forceinline__ unsigned long long f2_fma(unsigned long long a, unsigned long long b, unsigned long long c) {
+  unsigned long long r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r;
+}
+__device__ __forceinline__ unsigned long long f2_pack(float lo, float hi) {
+  return (unsigned long long)__float_as_uint(lo) | ((unsigned long long)__float_as_uint(hi) << 32);
+}
+
 // FILTER: candidates of the three z-layer segments whose fp32 distance to (pxf,pyf,pzf) is below T2f; their tile
-// offsets go to F (first KG_CAPF kept).  Rows have even bounds, so a float2 never straddles a segment end.
+// offsets go to F (first KG_CAPF kept).  Rows have even bounds, so a float2 never straddles a segment end; a pair
+// past the end of its segment is switched off through the threshold (no branch).  ATOM: survivors reserve their
+// slot with a shared-memory atomic (2 instructions per survivor) instead of ballot + popc prefix sums; the order
+// of F then depends on the hardware's arbitration (rows are unordered sets either way).
+template <bool ATOM>
 __device__ __forceinline__ int knn_filter(const float* __restrict__ xf, const float* __restrict__ yf, const float* __restrict__ zf,
-                                          const int (*seg)[2], float pxf, float pyf, float pzf, float T2f, uint16_t* F, int lane) {
+                                          const int (*seg)[2], float pxf, float pyf, float pzf, float T2f, uint16_t* F,
+                                          int* cntF, int lane) {
   const unsigned lt = (1u << lane) - 1u;
+  const unsigned long long PX = f2_pack(pxf, pxf), PY = f2_pack(pyf, pyf), PZ = f2_pack(pzf, pzf);
   int count = 0;
+  if (ATOM) { if (lane == 0) *cntF = 0; __syncwarp(); }
 #pragma unroll 1
   for (int s = 0; s < 3; ++s) {
     const int a = seg[s][0], b = seg[s][1];
 #pragma unroll 2
     for (int base = a; base < b; base += 64) {
       const int c = base + 2 * lane;
-      bool ok0 = false, ok1 = false;
-      if (c < b) {
-        const float2 X = *reinterpret_cast<const float2*>(xf + c);
-        const float2 Y = *reinterpret_cast<const float2*>(yf + c);
-        const float2 Z = *reinterpret_cast<const float2*>(zf + c);
-        const float dx0 = X.x - pxf, dy0 = Y.x - pyf, dz0 = Z.x - pzf;
-        const float dx1 = X.y - pxf, dy1 = Y.y - pyf, dz1 = Z.y - pzf;
-        const float d0 = fmaf(dz0, dz0, fmaf(dy0, dy0, dx0 * dx0));
-        const float d1 = fmaf(dz1, dz1, fmaf(dy1, dy1, dx1 * dx1));
-        ok0 = d0 < T2f; ok1 = d1 < T2f;                        // NaN (padding, non-finite particles) never passes
-      }
-      const unsigned b0 = __ballot_sync(0xffffffffu, ok0), b1 = __ballot_sync(0xffffffffu, ok1);
-      if (b0 | b1) {
-        const int n0 = __popc(b0);
-        const int p0 = count + __popc(b0 & lt), p1 = count + n0 + __popc(b1 & lt);
-        if (ok0 && p0 < KG_CAPF) F[p0] = (uint16_t)c;
-        if (ok1 && p1 < KG_CAPF) F[p1] = (uint16_t)(c + 1);
-        count += n0 + __popc(b1);
+      const float Tl = (c < b) ? T2f : -1.0f;                  // beyond the segment: never accepted
+      const unsigned long long X = *reinterpret_cast<const unsigned long long*>(xf + c);
+      const unsigned long long Y = *reinterpret_cast<const unsigned long long*>(yf + c);
+      const unsigned long long Z = *reinterpret_cast<const unsigned long long*>(zf + c);
+      const unsigned long long dx = f2_sub(X, PX), dy = f2_sub(Y, PY), dz = f2_sub(Z, PZ);
+      const unsigned long long d = f2_fma(dz, dz, f2_fma(dy, dy, f2_mul(dx, dx)));
+      const float d0 = __uint_as_float((unsigned)d), d1 = __uint_as_float((unsigned)(d >> 32));
+      const bool ok0 = d0 < Tl, ok1 = d1 < Tl;                 // NaN (padding, non-finite particles) never passes
+      if (ATOM) {
+        if (ok0) { const int p0 = atomicAdd(cntF, 1); if (p0 < KG_CAPF) F[p0] = (uint16_t)c; }
+        if (ok1) { const int p1 = atomicAdd(cntF, 1); if (p1 < KG_CAPF) F[p1] = (uint16_t)(c + 1); }
+      } else {
+        const unsigned b0 = __ballot_sync(0xffffffffu, ok0), b1 = __ballot_sync(0xffffffffu, ok1);
+        if (b0 | b1) {
+          const int n0 = __popc(b0);
+          const int p0 = count + __popc(b0 & lt), p1 = count + n0 + __popc(b1 & lt);
+          if (ok0 && p0 < KG_CAPF) F[p0] = (uint16_t)c;
+          if (ok1 && p1 < KG_CAPF) F[p1] = (uint16_t)(c + 1);
+          count += n0 + __popc(b1);
+        }
       }
     }
   }
+  if (ATOM) { __syncwarp(); count = *cntF; }
   return count;
 }
 
-// More than KG_CAP candidates inside the trial radius: find a threshold on the float-rounded keys that keeps
-// between k and KG_CAP of them (bisection, 4 ballots per step) and compact those to the front of the buffers.
-// Returns the new count, or -1 when no threshold separates them (more than KG_CAP - k equal keys).
-__device__ __forceinline__ int knn_reduce_to_cap(int k, int count, double R2try, double* keybuf, int* idxbuf, int lane) {
-  double kr[4]; int ir[4]; unsigned fr[4];
+// SESSION layout, selection in registers.  Every lane holds up to four candidates (exact d^2, tile offset; absent:
+// idx < 0) of which `count` are valid, count >= k.  Keeps the k smallest by (d^2, offset), writes them as the
+// target's uint16 row (unordered, self in column 0) and returns the squared k-th distance; ok = false when more
+// candidates tie in the float-rounded key than the removal step can separate (the caller escapes the target).
+// The float keys (rounded up, so monotone in the exact key) drive everything: a bisection on the key finds a
+// threshold that keeps between k and k + 3 candidates (four ballots per step), the at most three extra ones are
+// removed largest-first with REDUX-max, the exact (d^2, offset) order deciding only where float keys tie.
+#define KG_SLICES 4
+__device__ __forceinline__ double knn_select16(const KnnGroupArgs& a, int i, int self, int count, int nsl, double R2try,
+                                               double (&kr)[KG_SLICES], int (&ir)[KG_SLICES], int lane, bool& ok) {
+  const int k = a.k;
+  unsigned fr[KG_SLICES];
 #pragma unroll
-  for (int r = 0; r < 4; ++r) {
-    const int e = lane + 32 * r;
-    kr[r] = (e < count) ? keybuf[e] : -1.0;
-    ir[r] = (e < count) ? idxbuf[e] : -1;
-    fr[r] = (e < count) ? __float_as_uint(__double2float_ru(kr[r])) : 0xffffffffu;
+  for (int r = 0; r < KG_SLICES; ++r) fr[r] = (ir[r] >= 0) ? __float_as_uint(__double2float_ru(kr[r])) + 1u : 0u;   // 0 = absent
+  ok = true;
+  int kept = count;
+  if (count > k + 3) {
+    // keys of valid entries are in [1, hi); find tau with k <= #{0 < f < tau} <= k + 3
+    unsigned lo = __float_as_uint(__double2float_rd(0.35 * R2try)) + 1u, hi = __float_as_uint(__double2float_ru(R2try)) + 2u;
+    {
+      int c = 0;
+#pragma unroll
+      for (int r = 0; r < KG_SLICES; ++r) if (r < nsl) c += __popc(__ballot_sync(0xffffffffu, fr[r] != 0u && fr[r] < lo));
+      if (c >= k) lo = 1u;
+    }
+    unsigned tau = 0u;
+    for (int it = 0; it < 40; ++it) {
+      if (hi - lo <= 1u) break;
+      const unsigned mid = lo + ((hi - lo) >> 1);
+      int c = 0;
+#pragma unroll
+      for (int r = 0; r < KG_SLICES; ++r) if (r < nsl) c += __popc(__ballot_sync(0xffffffffu, fr[r] != 0u && fr[r] < mid));
+      if (c < k) lo = mid;
+      else if (c > k + 3) hi = mid;
+      else { tau = mid; kept = c; break; }
+    }
+    if (tau == 0u) { ok = false; return 0.0; }
+#pragma unroll
+    for (int r = 0; r < KG_SLICES; ++r) if (fr[r] >= tau) { fr[r] = 0u; ir[r] = -1; }
   }
-  unsigned lo = __float_as_uint(__double2float_rd(0.3 * R2try)), hi = __float_as_uint(__double2float_ru(R2try)) + 1u;
+  // remove the (kept - k) largest
+  for (int rm = kept; rm > k; --rm) {
+    unsigned fm = 0u;
+#pragma unroll
+    for (int r = 0; r < KG_SLICES; ++r) if (r < nsl) fm = max(fm, fr[r]);
+    const unsigned m = __reduce_max_sync(0xffffffffu, fm);
+    int owners = 0;
+#pragma unroll
+    for (int r = 0; r < KG_SLICES; ++r) if (r < nsl) owners += __popc(__ballot_sync(0xffffffffu, fr[r] == m));
+    if (owners == 1) {
+#pragma unroll
+      for (int r = 0; r < KG_SLICES; ++r) if (fr[r] == m) { fr[r] = 0u; ir[r] = -1; }
+    } else {                                                   // equal float keys: exact (key, offset) maximum among them
+      double kb = -1.0; int ib = -1;
+#pragma unroll
+      for (int r = 0; r < KG_SLICES; ++r)
+        if (r < nsl && fr[r] == m && (kr[r] > kb || (kr[r] == kb && ir[r] > ib))) { kb = kr[r]; ib = ir[r]; }
+      warp_max_pair(kb, ib);
+#pragma unroll
+      for (int r = 0; r < KG_SLICES; ++r) if (fr[r] == m && ir[r] == ib) { fr[r] = 0u; ir[r] = -1; }
+    }
+  }
+  // squared k-th distance: the exact maximum of what is left
+  double km = -1.0; int im = -1;
   {
-    int c = 0;
+    unsigned fm = 0u;
 #pragma unroll
-    for (int r = 0; r < 4; ++r) c += __popc(__ballot_sync(0xffffffffu, fr[r] < lo));
-    if (c >= k) lo = 0u;
-  }
-  unsigned tau = hi;
-  bool found = false;
-  for (int it = 0; it < 40; ++it) {
-    if (hi - lo <= 1u) break;
-    const unsigned mid = lo + ((hi - lo) >> 1);
-    int c = 0;
+    for (int r = 0; r < KG_SLICES; ++r) if (r < nsl) fm = max(fm, fr[r]);
+    const unsigned m = __reduce_max_sync(0xffffffffu, fm);
 #pragma unroll
-    for (int r = 0; r < 4; ++r) c += __popc(__ballot_sync(0xffffffffu, fr[r] < mid));
-    if (c < k) lo = mid;
-    else if (c > KG_CAP) hi = mid;
-    else { tau = mid; found = true; break; }
+    for (int r = 0; r < KG_SLICES; ++r)
+      if (r < nsl && fr[r] == m && m != 0u && (kr[r] > km || (kr[r] == km && ir[r] > im))) { km = kr[r]; im = ir[r]; }
+    warp_max_pair(km, im);
   }
-  if (!found) return -1;
-  __syncwarp();
+  // the row: kept entries in (slice, lane) order, self moved to column 0
   const unsigned lt = (1u << lane) - 1u;
-  int out = 0;
+  uint16_t* out = a.list16 + (int64_t)i * LIST_STRIDE(k);
+  unsigned bm[KG_SLICES];
+  int ps = -1, run = 0;
 #pragma unroll
-  for (int r = 0; r < 4; ++r) {
-    const bool keep = fr[r] < tau;
-    const unsigned b = __ballot_sync(0xffffffffu, keep);
-    if (keep) { const int p = out + __popc(b & lt); keybuf[p] = kr[r]; idxbuf[p] = ir[r]; }
-    out += __popc(b);
+  for (int r = 0; r < KG_SLICES; ++r) {
+    bm[r] = 0u;
+    if (r < nsl) {
+      bm[r] = __ballot_sync(0xffffffffu, ir[r] >= 0);
+      const unsigned sm = __ballot_sync(0xffffffffu, ir[r] == self);
+      if (sm) ps = run + __popc(bm[r] & ((1u << (__ffs(sm) - 1)) - 1u));
+      run += __popc(bm[r]);
+    }
   }
-  __syncwarp();
-  return out;
+  int basepos = 0;
+#pragma unroll
+  for (int r = 0; r < KG_SLICES; ++r) {
+    if (r < nsl) {
+      if (ir[r] >= 0) {
+        const int pos = basepos + __popc(bm[r] & lt);
+        out[(pos == ps) ? 0 : (pos < ps ? pos + 1 : pos)] = (uint16_t)ir[r];
+      }
+      basepos += __popc(bm[r]);
+    }
+  }
+  for (int s2 = basepos + lane; s2 < k; s2 += 32) out[s2] = (uint16_t)LIST_MISSING;
+  return (basepos > 0 && km > 0.0) ? km : 0.0;
 }
 
-template <bool SORTED>
+template <bool SORTED, bool ATOM>
 __global__ void __launch_bounds__(KG_THREADS, KG_MIN_CTAS) knn_group_kernel(KnnGroupArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -313,14 +396,14 @@ __global__ void __launch_bounds__(KG_THREADS, KG_MIN_CTAS) knn_group_kernel(KnnG
         const int i = misc->tbegin[q] + (t - misc->tbase[q]);
         const bool ghost = a.skip_id && a.skip_id[i] >= a.skip_from;
         if (ghost) {
-          if (a.list16) a.list16[(int64_t)i * a.k] = (uint16_t)LIST_MISSING;
+          if (a.list16) a.list16[(int64_t)i * LIST_STRIDE(a.k)] = (uint16_t)LIST_MISSING;
           if (SORTED) for (int s = 0; s < a.k; ++s) { a.list[(int64_t)i * a.k + s] = a.n; a.dists[(int64_t)i * a.k + s] = 0.0; }
           a.nontriv[i] = 0; a.h_out[i] = a.r0[i].w;
         } else {
           const int slot = atomicAdd(a.nwork, 1);
           a.worklist[slot] = i;
           if (a.list16) {
-            uint16_t* out = a.list16 + (int64_t)i * a.k;
+            uint16_t* out = a.list16 + (int64_t)i * LIST_STRIDE(a.k);
             out[0] = (uint16_t)LIST_ESCAPED;
             if (a.k > 2) { out[1] = (uint16_t)(slot & 0xffff); out[2] = (uint16_t)(slot >> 16); }
           }
@@ -387,7 +470,7 @@ __global__ void __launch_bounds__(KG_THREADS, KG_MIN_CTAS) knn_group_kernel(KnnG
       const bool finite = isfinite(p.x) && isfinite(p.y) && isfinite(p.z);
       const bool ghost = a.skip_id && a.skip_id[i] >= a.skip_from;
       if (!finite || ghost) {                                 // cKDTree raises on non-finite input; ghosts: an empty, well-defined row
-        if (a.list16) a.list16[(int64_t)i * a.k] = (uint16_t)LIST_MISSING;
+        if (a.list16) a.list16[(int64_t)i * LIST_STRIDE(a.k)] = (uint16_t)LIST_MISSING;
         if (SORTED) for (int s = 0; s < a.k; ++s) { a.list[(int64_t)i * a.k + s] = a.n; a.dists[(int64_t)i * a.k + s] = 0.0; }
         a.nontriv[i] = 0;
         a.h_out[i] = (ghost && finite) ? p.w : 0.0;
@@ -430,37 +513,38 @@ __global__ void __launch_bounds__(KG_THREADS, KG_MIN_CTAS) knn_group_kernel(KnnG
       const int i = t_i[t];
       const double4 p = tile[off];
       const float pxf = xf[off], pyf = yf[off], pzf = zf[off];
-      int count = 0, verdict = 1, scans = 0;
+      int count = 0, verdict = 1, scans = 0, nsl = 0;
+      double kr[KG_SLICES]; int ir[KG_SLICES];
       for (int attempt = 0; attempt < KG_MAX_ATTEMPT && verdict == 1; ++attempt) {
         ++scans;
         __syncwarp();
         const double Rc = sqrt(R2try) * g.inv_c + 1.7320508075688772 * eta;
         const float T2f = __double2float_ru(Rc * Rc * (1.0 + 4.0 * u24));
-        const int nf = knn_filter(xf, yf, zf, misc->seg[q], pxf, pyf, pzf, T2f, F, lane);
+        const int nf = knn_filter<ATOM>(xf, yf, zf, misc->seg[q], pxf, pyf, pzf, T2f, F, &misc->cntF[warp], lane);
         if (nf > KG_CAPF) {                                   // too many: shrink the trial radius, scan again
           const double f = cbrt(0.75 * (double)KG_CAPF / (double)nf);
           R2try *= f * f;
           continue;
         }
         __syncwarp();
-        // exact stage over the nf survivors
-        const unsigned lt = (1u << lane) - 1u;
+        // exact stage over the nf survivors: up to four per lane, kept in registers
+        nsl = (nf + 31) >> 5;
         count = 0;
-        for (int e0 = 0; e0 < nf; e0 += 32) {
-          const int e = e0 + lane;
-          bool ok = false; double d2 = 0.0; int o = 0;
-          if (e < nf) {
-            o = F[e];
-            const double4 c = tile[o];
-            const double dx = c.x - p.x, dy = c.y - p.y, dz = c.z - p.z;
-            d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
-            ok = d2 < R2try;
+#pragma unroll
+        for (int r = 0; r < KG_SLICES; ++r) {
+          kr[r] = -1.0; ir[r] = -1;
+          if (r < nsl) {
+            const int e = 32 * r + lane;
+            if (e < nf) {
+              const int o = F[e];
+              const double4 c = tile[o];
+              const double dx = c.x - p.x, dy = c.y - p.y, dz = c.z - p.z;
+              const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+              if (d2 < R2try) { kr[r] = d2; ir[r] = o; }
+            }
+            count += __popc(__ballot_sync(0xffffffffu, ir[r] >= 0));
           }
-          const unsigned b = __ballot_sync(0xffffffffu, ok);
-          if (ok) { const int pos = count + __popc(b & lt); keybuf[pos] = d2; idxbuf[pos] = o; }
-          count += __popc(b);
         }
-        __syncwarp();
         if (count >= a.k) { verdict = 0; break; }
         if (R2try < R2lim) {                                  // too few: grow towards the covered radius
           const double f = cbrt(1.4 * (double)a.k / (double)(count > 0 ? count : 1));
@@ -470,11 +554,26 @@ __global__ void __launch_bounds__(KG_THREADS, KG_MIN_CTAS) knn_group_kernel(KnnG
         verdict = (R2lim >= a.dist2) ? 0 : 2;                // everything inside the cut was seen / k-th neighbour may lie outside
       }
       double h2 = 0.0;
-      if (verdict == 0 && count > KG_CAP) {
-        count = knn_reduce_to_cap(a.k, count, R2try, keybuf, idxbuf, lane);
-        if (count < 0) { verdict = 2; count = 0; }
+      if (verdict == 0) {
+        if (SORTED) {                                          // API layout: rank the candidates through shared memory
+          const unsigned lt = (1u << lane) - 1u;
+          int run = 0;
+          __syncwarp();
+#pragma unroll
+          for (int r = 0; r < KG_SLICES; ++r) {
+            if (r < nsl) {
+              const unsigned bb = __ballot_sync(0xffffffffu, ir[r] >= 0);
+              if (ir[r] >= 0) { const int pos = run + __popc(bb & lt); keybuf[pos] = kr[r]; idxbuf[pos] = ir[r]; }
+              run += __popc(bb);
+            }
+          }
+          h2 = knn_emit<true>(a, i, off, count, keybuf, idxbuf, rowbase, lane);
+        } else {
+          bool ok;
+          h2 = knn_select16(a, i, off, count, nsl, R2try, kr, ir, lane, ok);
+          if (!ok) { verdict = 2; count = 0; }
+        }
       }
-      if (verdict == 0) h2 = knn_emit<SORTED>(a, i, off, count, keybuf, idxbuf, rowbase, lane);
       if (lane == 0) {                                         // result word: nsel | unresolved << 8 | rescans << 16
         t_R2try[t] = h2;
         t_word[t] = min(count, a.k) | ((verdict != 0) << 8) | ((scans - 1) << 16);
@@ -490,7 +589,7 @@ __global__ void __launch_bounds__(KG_THREADS, KG_MIN_CTAS) knn_group_kernel(KnnG
         const int slot = atomicAdd(a.nwork, 1);
         a.worklist[slot] = i;
         if (a.list16) {
-          uint16_t* out = a.list16 + (int64_t)i * a.k;
+          uint16_t* out = a.list16 + (int64_t)i * LIST_STRIDE(a.k);
           out[0] = (uint16_t)LIST_ESCAPED;
           if (a.k > 2) { out[1] = (uint16_t)(slot & 0xffff); out[2] = (uint16_t)(slot >> 16); }
         }
@@ -504,7 +603,7 @@ __global__ void __launch_bounds__(KG_THREADS, KG_MIN_CTAS) knn_group_kernel(KnnG
   }
 }
 
-int knn_group_max_k() { return KG_CAP - 8; }
+int knn_group_max_k() { return KG_CAP - 8; }   // k + 3 candidates must fit two slices comfortably; 56 as before
 
 // Fast path + general-kernel clean-up of the targets it could not resolve inside their tile.
 // `dists` != nullptr selects the API layout (rows in `list` sorted by distance, distances returned);
@@ -533,11 +632,14 @@ int launch_knn_group(sphb200_ctx* ctx, int n, int k, double dist, int use_guess,
   const int blocks = 148 * KG_MIN_CTAS;
   if (dists) {
     const int smem = KG_SMEM + TILE_CAP * 4;
-    CUDA_TRY(cudaFuncSetAttribute(knn_group_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    knn_group_kernel<true><<<blocks, KG_THREADS, smem, st>>>(a);
+    CUDA_TRY(cudaFuncSetAttribute(knn_group_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    knn_group_kernel<true, false><<<blocks, KG_THREADS, smem, st>>>(a);
+  } else if (ctx->knn_atomic) {
+    CUDA_TRY(cudaFuncSetAttribute(knn_group_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, KG_SMEM));
+    knn_group_kernel<false, true><<<blocks, KG_THREADS, KG_SMEM, st>>>(a);
   } else {
-    CUDA_TRY(cudaFuncSetAttribute(knn_group_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, KG_SMEM));
-    knn_group_kernel<false><<<blocks, KG_THREADS, KG_SMEM, st>>>(a);
+    CUDA_TRY(cudaFuncSetAttribute(knn_group_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, KG_SMEM));
+    knn_group_kernel<false, false><<<blocks, KG_THREADS, KG_SMEM, st>>>(a);
   }
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());

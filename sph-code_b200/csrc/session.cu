@@ -692,7 +692,8 @@ static int phase_dt_clamp(sphb200_ctx* ctx, cudaStream_t st) {
 static int phase_sort(sphb200_ctx* ctx, cudaStream_t st, unsigned mask = ~0u) {
   Session& s = sess(ctx);
   // the previous k-th distances (still in the old order) ride into the sorted records as the next trial radii
-  SPH_TRY(build_cells(ctx, fld(ctx, F_POS), s.n, ctx->cell_edge, bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]), false, st));
+  SPH_TRY(build_cells(ctx, fld(ctx, F_POS), s.n, ctx->cell_edge, s.use_guess ? bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]) : nullptr, s.k,
+                      false, st));
   ReorderArgs a;
   for (int f = 0; f < F_NFIELDS; ++f) { a.src[f] = fld(ctx, f, 0); a.dst[f] = fld(ctx, f, 1); }
   a.id_src = bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]);
@@ -720,9 +721,13 @@ static int phase_knn(sphb200_ctx* ctx, cudaStream_t st) {
   double* knnh = bufp<double>(ctx->sbuf[SB_KNNH + s.knnh_cur]);
   // previous k-th distance (in the sorted records, r0.w) as the first trial radius; zeros before start-up
   if (ctx->knn_fast && s.k >= 3 && s.k <= knn_group_max_k()) {
-    SPH_TRY(devbuf_reserve(ctx->list16, (size_t)s.n * s.k * sizeof(uint16_t) + 64));
-    SPH_TRY(launch_knn_group(ctx, (int)s.n, s.k, s.dist, s.use_guess, ctx->knn_margin, bufp<uint16_t>(ctx->list16),
-                             bufp<int32_t>(ctx->list), nullptr, fld(ctx, F_H), bufp<int32_t>(ctx->sbuf[SB_NONTRIV]), st));
+    SPH_TRY(devbuf_reserve(ctx->list16, (size_t)s.n * LIST_STRIDE(s.k) * sizeof(uint16_t) + 64));
+    if (ctx->knn_lane)
+      SPH_TRY(launch_knn_lane(ctx, (int)s.n, s.k, s.dist, s.use_guess, ctx->knn_margin, bufp<uint16_t>(ctx->list16),
+                              bufp<int32_t>(ctx->list), fld(ctx, F_H), bufp<int32_t>(ctx->sbuf[SB_NONTRIV]), st));
+    else
+      SPH_TRY(launch_knn_group(ctx, (int)s.n, s.k, s.dist, s.use_guess, ctx->knn_margin, bufp<uint16_t>(ctx->list16),
+                               bufp<int32_t>(ctx->list), nullptr, fld(ctx, F_H), bufp<int32_t>(ctx->sbuf[SB_NONTRIV]), st));
     ctx->list_is_global = 0;
   } else {
     SPH_TRY(launch_knn(ctx, (int)s.n, s.k, s.dist, s.use_guess, 1.0 + ctx->knn_margin, bufp<int32_t>(ctx->list), nullptr,

@@ -19,6 +19,7 @@
 #define TILE_HALF_CAP 896        // padded particles of the 3 z-layers a half-group pass stages
 #define TILE_MAX_TARGETS 224     // particles of the 2x2x2 cells of a group
 #define TILE_HALF_TARGETS 144    // particles of the 2x2 cells of one z-half of a group
+#define LIST_STRIDE(k) (((k) + 7) & ~7)   // uint16 entries per row: rows are 16-byte aligned (bulk-copyable)
 #define LIST_ESCAPED 0xFFFFu     // column 0 of a uint16 row: the row lives in the global list (slot in columns 1,2)
 #define LIST_MISSING 0xFFFEu     // uint16 row entry: no neighbour (fewer than k inside the distance cut)
 

@@ -7,6 +7,7 @@ for it.  `Session` holds the same struct-of-arrays in HBM and advances it with
 variable names.
 """
 import ctypes
+import os
 
 import numpy as np
 import torch
@@ -36,6 +37,10 @@ class Session(object):
             raise _lib.Sphb200Error("no CUDA device visible: sphb200 runs on a B200 only (no CPU fallback)")
         self.ctx = _lib.Context(torch.cuda.current_device() if device is None else int(device))
         self.lib = _lib.load()
+        # tunables from the environment, "name=value,name=value" (sphb200_set_option), e.g. SPHB200_OPTIONS=knn_margin=0.1
+        for item in filter(None, os.environ.get("SPHB200_OPTIONS", "").split(",")):
+            name, _, val = item.partition("=")
+            self.ctx.set_option(name.strip(), float(val))
         self.n = int(n)
         self.k = int(k)
         self.device = torch.device("cuda", self.ctx.device)

@@ -1,0 +1,4 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_session.py tests/test_gpu_golden.py tests/test_gpu_parity.py -x -q -k "not full_size" > gpurun_out/b3_tests.log 2>&1; echo "tests rc=$?"; tail -5 gpurun_out/b3_tests.log
+python tools/knn_debug.py 1000000 0.2 knn_margin=0.1 2>&1 | tail -2 | cut -c1-250

@@ -1,0 +1,8 @@
+#!/bin/bash
+mkdir -p gpurun_out
+CMD="python bench.py --n 1e6 --steps 2 --warmup 3 --no-cpu --no-e2e"
+$CMD > gpurun_out/ncu_plain.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:'knn_lane_kernel' -s 2 -c 1 -o gpurun_out/r02_prof4a $CMD > gpurun_out/ncu_run.log 2>&1
+echo "ncu rc=$?"
+ncu --set full --clock-control none --import-source on -k regex:'tile_pass_kernel' -s 8 -c 3 -o gpurun_out/r02_prof4b $CMD > gpurun_out/ncu_run2.log 2>&1
+echo "ncu rc=$?"
