@@ -65,7 +65,7 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--n", type=float, default=1e7, help="particles per GPU (weak) / in total (strong)")
+    ap.add_argument("--n", "--particles", dest="n", type=float, default=1e7, help="particles per GPU (weak) / in total (strong)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--kind", default="uniform", choices=["uniform", "clustered"])
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])

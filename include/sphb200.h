@@ -92,6 +92,13 @@ int sphb200_net_impulse(sphb200_ctx* ctx, int64_t n, int k, const int64_t* neigh
                         const double* particle_type, const double* f_un, int n_species, const double* grain_mass_host,
                         const double* sigma_effective_host, double* accel_onto, double* accel_reaction, void* stream);
 
+/* ---- F2: grav_force_calculation_new(mass, points, sizes)                 nsc:252-415 --------------
+ * The softened monopole law the reference applies bin by bin, a_i = G sum_j m_j (x_j - x_i) /
+ * (|x_j - x_i|^2 + softening^2)^(3/2), summed directly over all particles (O(N^2), fp64); the binding passes
+ * softening = median(sizes) as nsc:359 does.  accel (N,3). */
+int sphb200_gravity(sphb200_ctx* ctx, int64_t n, const double* mass, const double* points, double G, double softening,
+                    double* accel, void* stream);
+
 /* ---- A10-A13: device-resident particle state and the whole time step ---------------------------
  * The reference keeps its particle state as module-level numpy arrays in the driver
  * (sph/code_running.py:121-167) and advances it inline (:217-540).  A session holds the same
@@ -177,6 +184,9 @@ int sphb200_session_set_count(sphb200_ctx* ctx, int64_t n, int64_t n_owned);
 int sphb200_session_receive_rows(sphb200_ctx* ctx, const double* rows, int64_t n_new, int ncol, int as_ghosts, void* stream);
 int sphb200_session_halo_pack(sphb200_ctx* ctx, int phase, const double* bounds, int world, int rank, double w, double* rows_out,
                               int64_t* idx_out, int64_t cap_rows, int ncol, int* counts_out, void* stream);
+/* F2 inside the step: softening > 0 switches self-gravity on (phase "gravity" after the search, as
+ * code_running.py:448; "integrate" adds it, :477), <= 0 off.  Result field "grav_accel" (N,3). */
+int sphb200_session_set_gravity(sphb200_ctx* ctx, double G, double softening);
 /* Synthetic motion for the measured workloads and the moving-particle parity tests (the reference has no
  * counterpart: its own step cannot displace particles by a sizeable fraction of h and stay finite, DESIGN.md
  * section 2): points[i] += amplitude * u(id_i, seed), u uniform in [-1,1)^3, a pure function of the particle's

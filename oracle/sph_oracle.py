@@ -319,6 +319,27 @@ def net_impulse(points, mass, sizes, velocities, particle_type, neighbor, f_un, 
 
 
 # --------------------------------------------------------------------------------------------
+# F2  self-gravity                                                navier_stokes_cleaned.py:252-415
+# PARITY UNPINNED for this row: grav_force_calculation_new cannot run (it walks .less/.greater/.idx of scipy's
+# removed pure-Python KDTree, :257-270) and the reference holds no output of it.  What the routine applies, bin
+# by bin, is the Plummer-softened monopole law a = G M (x_c - x) / (|x_c - x|^2 + eps^2)^(3/2) with
+# eps = median(sizes) (:359, :392-397, :411); this oracle sums that law directly over all particles, the limit
+# the reference's KD-bisection bins approximate.
+G_newton = _c.G
+
+
+def gravity_direct(mass, points, sizes, block=1024):
+    eps2 = float(np.median(sizes)) ** 2
+    out = np.zeros(points.shape)
+    for a in range(0, len(points), block):
+        b = min(len(points), a + block)
+        dx = points[None, :, :] - points[a:b, None, :]
+        r2 = np.sum(dx * dx, axis=2) + eps2
+        out[a:b] = G_newton * np.sum((mass[None, :] / r2 ** 1.5)[..., None] * dx, axis=1)
+    return out
+
+
+# --------------------------------------------------------------------------------------------
 # A9-A12  one time step in the driver's order                    code_running.py:217-540
 # Harness conventions: gas/dust only (no stars, so the radiative / supernova block
 # :243-397 is skipped by its own guard), gravity, drag and chemistry zero, the start-up search radius
@@ -357,7 +378,7 @@ def append(s, new, neighbors_fn=neighbors):
     return s
 
 
-def step(s, neighbors_fn=neighbors, hydro_fn=hydro_update, crossing_fn=None, drag_fn=None):
+def step(s, neighbors_fn=neighbors, hydro_fn=hydro_update, crossing_fn=None, drag_fn=None, grav_fn=None):
     """One pass of the `while` body; returns a new state dict (inputs are not mutated).
     The hooks let tests/golden/make_golden.py drive the same harness with the reference's own
     (extracted) functions.  `drag_fn` (net_impulse's signature) switches the dust-gas drag of
@@ -395,7 +416,12 @@ def step(s, neighbors_fn=neighbors, hydro_fn=hydro_update, crossing_fn=None, dra
     with np.errstate(invalid='ignore'):
         clamp = vmag - np.sum(visc_accel ** 2, axis=1) ** 0.5 * dt < 0                    # :475
     visc_accel[clamp] = (-velocities / dt)[clamp]
-    total_accel = pressure_accel + visc_accel                                             # :477 (grav = 0)
+    if grav_fn is not None:
+        grav_accel = grav_fn(mass, points, sizes)                                         # :448 (sizes of the search at :437)
+        total_accel = grav_accel + pressure_accel + visc_accel                            # :477
+    else:
+        grav_accel = None
+        total_accel = pressure_accel + visc_accel                                         # :477 (grav = 0)
     points = points + ((total_accel * dt ** 2) / 2. + velocities * dt)                    # :481
     if np.shape(total_accel) == np.shape(old_accel):                                      # :482-486
         velocities = velocities + (total_accel + old_accel) / 2. * dt
@@ -424,5 +450,5 @@ def step(s, neighbors_fn=neighbors, hydro_fn=hydro_update, crossing_fn=None, dra
     s.update(points=points, velocities=velocities, total_accel=total_accel, E_internal=E_internal, T=T,
              sizes=sizes, neighbor=nb, num_nontrivial=nontriv, densities=densities, densities_0=densities.copy(),
              d=float(d), age=age, dt=dt, ct=float(ct), num_densities=num_d, dust_densities=dust_d,
-             pressure_accel=pressure_accel, visc_accel=visc_accel, visc_heat=av1)
+             pressure_accel=pressure_accel, visc_accel=visc_accel, visc_heat=av1, grav_accel=grav_accel)
     return s

@@ -82,6 +82,7 @@ int sphb200_set_option(sphb200_ctx* ctx, const char* name, double value) {
   else if (!strcmp(name, "knn_atomic")) ctx->knn_atomic = value != 0.0;
   else if (!strcmp(name, "knn_lane")) ctx->knn_lane = value != 0.0;
   else if (!strcmp(name, "tile_cfg")) ctx->tile_cfg = (int)value;
+  else if (!strcmp(name, "grid_pow")) { if (value == 0.0) SPH_FAIL("grid_pow must not be 0"); ctx->grid_pow = value; }
   else if (!strcmp(name, "knn_margin")) { if (!(value >= 0)) SPH_FAIL("knn_margin must be >= 0"); ctx->knn_margin = value; }
   else SPH_FAIL("unknown option '%s'", name);
   return 0;
@@ -289,6 +290,15 @@ int sphb200_artificial_viscosity(sphb200_ctx* ctx, int64_t n, int k, const int64
   in.points = points; in.vel = velocities; in.mass = mass; in.ptype = particle_type; in.T = T; in.mu = mu_array;
   in.gamma = gamma_array; in.dens = densities; in.d = d;
   return launch_loop_viscosity(ctx, (int)n, k, bufp<int32_t>(ctx->list), in, visc_accel, visc_heat, st);
+}
+
+// ---- F2 ----------------------------------------------------------------------------------------
+int sphb200_gravity(sphb200_ctx* ctx, int64_t n, const double* mass, const double* points, double G, double softening,
+                    double* accel, void* stream) {
+  if (!ctx || !mass || !points || !accel) SPH_FAIL("sphb200_gravity: null argument");
+  if (n <= 0 || n >= (int64_t)0x7fffffff) SPH_FAIL("sphb200_gravity: bad particle count %lld", (long long)n);
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  return launch_gravity_direct(ctx, (int)n, points, mass, G, softening, accel, as_stream(stream));
 }
 
 // ---- F1 ----------------------------------------------------------------------------------------

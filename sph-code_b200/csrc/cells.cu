@@ -14,7 +14,7 @@
 // ---- bounding box: per-block partial min/max of the finite coordinates ----
 #define BB_PART 8                  // doubles per block: min xyz, max xyz, sum of guess^-3, number of guesses
 __global__ void __launch_bounds__(256) bbox_partial_kernel(const double* __restrict__ pts, const double* __restrict__ guess,
-                                                           int64_t n, double* __restrict__ part) {
+                                                           double hpow, int64_t n, double* __restrict__ part) {
   double lo[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, hi[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
   double dsum = 0.0, dcnt = 0.0;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
@@ -25,7 +25,7 @@ __global__ void __launch_bounds__(256) bbox_partial_kernel(const double* __restr
     }
     if (guess) {
       const double h = guess[i];
-      if (h > 0.0 && h < DBL_MAX) { dsum += 1.0 / (h * h * h); dcnt += 1.0; }
+      if (h > 0.0 && h < DBL_MAX) { dsum += (hpow == -3.0) ? 1.0 / (h * h * h) : pow(h, hpow); dcnt += 1.0; }
     }
   }
   __shared__ double sh[8][BB_PART];
@@ -96,7 +96,7 @@ __device__ void choose_grid(const double* bb, int64_t n, double occ, double edge
 }
 
 __global__ void __launch_bounds__(256)
-grid_choose_kernel(const double* __restrict__ part, int nblocks, int64_t n, double occ, double edge_hint, int knn_k, int max_cells,
+grid_choose_kernel(const double* __restrict__ part, int nblocks, int64_t n, double occ, double edge_hint, int knn_k, double hpow, int max_cells,
                    GridSpec* __restrict__ spec, double* __restrict__ bbox_out) {
   __shared__ double sh[256][BB_PART];
   double v[BB_PART] = {DBL_MAX, DBL_MAX, DBL_MAX, -DBL_MAX, -DBL_MAX, -DBL_MAX, 0.0, 0.0};
@@ -125,7 +125,9 @@ grid_choose_kernel(const double* __restrict__ part, int nblocks, int64_t n, doub
     // density, n_p = mean_i k / (4 pi/3 h_i^3): a bounding box inflated by a few stragglers (or a dilute envelope
     // around a dense cloud) then no longer makes the cells of the bulk hold more than `occ` particles.
     if (!(edge_hint > 0.0) && knn_k > 0 && sh[0][7] >= 0.5 * (double)n) {
-      const double dens = (double)knn_k / 4.1887902047863905 * (sh[0][6] / sh[0][7]);
+      // h_eff = (mean h^p)^(1/p): p = -3 is the particles' mean number density, larger p leans towards the dilute regions
+      const double heff = pow(sh[0][6] / sh[0][7], 1.0 / hpow);
+      const double dens = (double)knn_k / (4.1887902047863905 * heff * heff * heff);
       if (dens > 0.0 && dens < DBL_MAX) edge_hint = cbrt(occ / dens);
     }
     GridSpec g;
@@ -368,8 +370,8 @@ int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint
   uint32_t* rank = bufp<uint32_t>(ctx->perm_alt);
   int bb_blocks = ceil_div(n, 256); if (bb_blocks > BB_BLOCKS) bb_blocks = BB_BLOCKS;
   const int nblk = ceil_div(n, 256);
-  bbox_partial_kernel<<<bb_blocks, 256, 0, st>>>(pts, guess, n, part);
-  grid_choose_kernel<<<1, 256, 0, st>>>(part, bb_blocks, n, ctx->cell_occ, edge_hint, knn_k, max_cells, spec, scal + SC_BBOX);
+  bbox_partial_kernel<<<bb_blocks, 256, 0, st>>>(pts, guess, ctx->grid_pow, n, part);
+  grid_choose_kernel<<<1, 256, 0, st>>>(part, bb_blocks, n, ctx->cell_occ, edge_hint, knn_k, ctx->grid_pow, max_cells, spec, scal + SC_BBOX);
   zero_counts_kernel<<<148 * 4, 256, 0, st>>>(spec, cs);
   cell_key_kernel<<<nblk, 256, 0, st>>>(pts, n, spec, keys_src, rank, cs);
   scan_tiles_kernel<<<scan_blocks, 256, 0, st>>>(spec, 0, cs, bufp<uint32_t>(ctx->scan_tops));

@@ -95,6 +95,7 @@ struct sphb200_ctx {
   DevBuf tmp0, tmp1, tmp2, tmp3;   // generic scratch
   DevBuf sbuf[48];                 // session arrays (session.cu)
   double cell_occ = 16.0;          // target mean particles per cell (tunable)
+  double grid_pow = -3.0;          // cell edge from h_eff = (mean h^p)^(1/p) of the previous k-th distances (cells.cu)
   double cell_edge = 0.0;          // fixed cell edge (0 = from cell_occ)
   int knn_group = 32;              // lanes per target in the general k-NN kernel
   int tile_cfg = 0;                // pair passes: 0 two stages per CTA, 1 one stage and more resident CTAs (hydro.cu)

@@ -63,6 +63,10 @@ int launch_crossing_time(sphb200_ctx* ctx, int n, int k, const RowsRef& rows, co
                          const double* ptype, double dt_0, double* out_dev, const uint32_t* id, uint32_t n_owned, cudaStream_t st);
 int launch_expand_list(sphb200_ctx* ctx, int n, int k, const uint16_t* list16, const int32_t* glist, int32_t* out, cudaStream_t st);
 
+// gravity.cu (F2: direct Plummer-softened sum, nsc:252-415)
+int launch_gravity_direct(sphb200_ctx* ctx, int n, const double* pos, const double* mass, double G, double eps, double* out,
+                          cudaStream_t st);
+
 // loopgen.cu  (loop generation, nsc:673-816)
 struct LoopIn {
   const double* points; const double* vel; const double* mass; const double* sizes; const double* ptype;

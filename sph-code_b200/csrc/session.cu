@@ -17,7 +17,7 @@ static const char* kFieldName[F_NFIELDS] = {"points", "velocities", "total_accel
 enum Out { O_RHO = 0, O_NUM, O_DUST, O_HACC, O_VACC, O_HEAT, O_PACC, O_NOUT };
 static const int kOutWidth[O_NOUT] = {1, 1, 1, 3, 3, 1, 3};
 static const char* kOutName[O_NOUT] = {"densities", "num_densities", "dust_densities", "hydro_accel", "visc_accel",
-                                       "visc_heat", "pressure_accel"};
+                                       "visc_heat", "pressure_accel"};   // + "grav_accel" (download only, when gravity is on)
 // sbuf layout: [2*f + which] state double buffers, then ids, outputs, scratch
 #define SB_ID 24
 #define SB_ID_ALT 25
@@ -52,6 +52,8 @@ struct Session {
   int grown = 0;             // particles were appended since the last kick: the old arrays have the old
                              // length, so this step takes dv = a dt (:485) and new_smoothing = 1 (:535)
   int64_t n_owned = -1;      // slab decomposition: caller indices >= n_owned are ghosts (-1: none)
+  int gravity = 0;           // F2: total_accel = grav_accel + pressure_accel + visc_accel (code_running.py:477)
+  double grav_G = 0, grav_eps = 0;
   int has_gid = 0;           // SB_GID holds global ids (rows carry them in column 18)
   int gid_cur = 0;
   SessionScalars sc;
@@ -137,7 +139,8 @@ integrate_kernel(int n, const double* __restrict__ scal, double kB, double m_h, 
                  const double* __restrict__ mass, const double* __restrict__ mu, const double* __restrict__ gamma,
                  const double* __restrict__ ptype, const double* __restrict__ hacc, double* __restrict__ vacc,
                  const double* __restrict__ heat, double* __restrict__ pacc, double* __restrict__ distsq,
-                 unsigned long long* __restrict__ nslow, const uint32_t* __restrict__ id, int n_owned, int grown) {
+                 unsigned long long* __restrict__ nslow, const uint32_t* __restrict__ id, int n_owned, int grown,
+                 const double* __restrict__ grav) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   int slow = 0;
   if (i < n) {
@@ -160,7 +163,7 @@ integrate_kernel(int n, const double* __restrict__ scal, double kB, double m_h, 
     double v2 = 0.0, x2 = 0.0;
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-      a[c] = ap[c] + av[c];                                                      // :477 (gravity = 0)
+      a[c] = grav ? (grav[3 * (int64_t)i + c] + ap[c]) + av[c] : ap[c] + av[c];  // :477
       const double xn = x[c] + ((a[c] * (dt * dt)) / 2. + v[c] * dt);            // :481
       const double vn = grown ? v[c] + a[c] * dt                                 // :484-485 (shapes differ)
                               : v[c] + (a[c] + acc[3 * (int64_t)i + c]) / 2. * dt;       // :482-483
@@ -525,6 +528,7 @@ perturb_kernel(int n, const uint32_t* __restrict__ id, const double* __restrict_
     pos[3 * (int64_t)i + c] = __dadd_rn(pos[3 * (int64_t)i + c], __dmul_rn(amp, perturb_unit(g, c, seed)));
 }
 
+#define SB_GRAV 36           // F2: gravitational acceleration (N,3), sorted order
 #define SB_XLIST 45          // int32 rows of every particle expanded from the uint16 tile rows (download, drag)
 
 // neighbour rows of the last search, in the form the passes take them (kernels.cuh RowsRef)
@@ -783,10 +787,21 @@ static int phase_kick(sphb200_ctx* ctx, cudaStream_t st) {
                                                      outp(ctx, O_HACC), outp(ctx, O_VACC), outp(ctx, O_HEAT),
                                                      outp(ctx, O_PACC), bufp<double>(ctx->sbuf[SB_DISTSQ]), nslow,
                                                      s.n_owned >= 0 ? bufp<uint32_t>(ctx->sbuf[SB_ID + s.id_cur]) : nullptr,
-                                                     (int)s.n_owned, s.grown);
+                                                     (int)s.n_owned, s.grown,
+                                                     s.gravity ? bufp<double>(ctx->sbuf[SB_GRAV]) : nullptr);
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;
+}
+
+// F2: gravitational acceleration of the current positions (after the search, as code_running.py:448)
+static int phase_gravity(sphb200_ctx* ctx, cudaStream_t st) {
+  Session& s = sess(ctx);
+  if (!s.gravity) return 0;
+  if (s.n_owned >= 0 && s.n_owned < s.n) SPH_FAIL("session: gravity is not available on a slab with ghosts");
+  SPH_TRY(devbuf_reserve(ctx->sbuf[SB_GRAV], (size_t)s.n * 3 * sizeof(double)));
+  return launch_gravity_direct(ctx, (int)s.n, fld(ctx, F_POS), fld(ctx, F_MASS), s.grav_G, s.grav_eps,
+                               bufp<double>(ctx->sbuf[SB_GRAV]), st);
 }
 
 // A12: global length scale d from the 90th percentile of |x|^2: radix select, see select_*_kernel.
@@ -1067,6 +1082,7 @@ int sphb200_session_download(sphb200_ctx* ctx, const char* name, void* dst, int6
     const int f = find_field(name);
     if (f >= 0) { src = fld(ctx, f); w = kFieldWidth[f]; }
     for (int o = 0; o < O_NOUT && !src; ++o) if (!strcmp(name, kOutName[o])) { src = outp(ctx, o); w = kOutWidth[o]; }
+    if (!src && !strcmp(name, "grav_accel") && s.gravity) { src = bufp<double>(ctx->sbuf[SB_GRAV]); w = 3; }
     if (!src) { src = aux_field(ctx, name, false); w = 1; }
     if (!src) SPH_FAIL("session_download: unknown field '%s'", name);
     if (count != s.n * w) SPH_FAIL("session_download: '%s' needs %lld values, got %lld", name, (long long)(s.n * w), (long long)count);
@@ -1533,6 +1549,17 @@ int sphb200_session_halo_pack(sphb200_ctx* ctx, int phase, const double* bounds,
   return 0;
 }
 
+// F2: switch self-gravity on (softening > 0: the Plummer length, the reference uses median(sizes), nsc:359) or
+// off (softening <= 0).  The phase "gravity" then fills the acceleration that "integrate" adds (:477).
+int sphb200_session_set_gravity(sphb200_ctx* ctx, double G, double softening) {
+  if (!ctx) SPH_FAIL("null context");
+  if (!ctx->session) SPH_FAIL("no session in this context (call sphb200_session_create first)");
+  Session& s = sess(ctx);
+  s.gravity = softening > 0.0;
+  s.grav_G = G; s.grav_eps = softening;
+  return 0;
+}
+
 int sphb200_session_perturb(sphb200_ctx* ctx, double amplitude, uint64_t seed, void* stream) {
   if (!ctx) SPH_FAIL("null context");
   CUDA_TRY(cudaSetDevice(ctx->device));
@@ -1561,6 +1588,7 @@ int sphb200_session_step(sphb200_ctx* ctx, void* stream) {
   SPH_TRY(phase_density(ctx, st));
   SPH_TRY(phase_pi(ctx, st));
   SPH_TRY(phase_force(ctx, st));
+  SPH_TRY(phase_gravity(ctx, st));
   SPH_TRY(phase_integrate(ctx, st));
   return 0;
 }
@@ -1581,6 +1609,7 @@ int sphb200_session_phase(sphb200_ctx* ctx, const char* phase, void* stream) {
   if (!strcmp(phase, "density")) return phase_density(ctx, st);
   if (!strcmp(phase, "pi")) return phase_pi(ctx, st);
   if (!strcmp(phase, "force")) return phase_force(ctx, st);
+  if (!strcmp(phase, "gravity")) return phase_gravity(ctx, st);
   if (!strcmp(phase, "integrate")) return phase_integrate(ctx, st);
   if (!strcmp(phase, "kick")) return phase_kick(ctx, st);
   if (!strcmp(phase, "length")) return phase_length(ctx, st);

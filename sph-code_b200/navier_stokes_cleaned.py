@@ -191,6 +191,21 @@ def artificial_viscosity(neighbor, points, particle_type, sizes, mass, densities
     return va.cpu().numpy(), vh.cpu().numpy()
 
 
+def grav_force_calculation_new(mass, points, sizes):
+    """nsc:252-415.  The reference bins the cloud with a KD bisection and applies the Plummer-softened
+    monopole law bin by bin with softening = median(sizes) (:359); its tree code cannot run on a current scipy.
+    Here the same law is summed directly over all particles on the GPU (the exact limit of that approximation):
+    a_i = G sum_j m_j (x_j - x_i) / (|x_j - x_i|^2 + eps^2)^(3/2).  Returns (N,3)."""
+    ctx = _lib.context()
+    pts = _dev(points)
+    n = int(pts.shape[0])
+    m = _dev(np.asarray(mass, dtype=np.float64))
+    eps = float(np.median(np.asarray(sizes, dtype=np.float64)))
+    out = torch.empty((n, 3), dtype=torch.float64, device=pts.device)
+    _lib.check(_lib.load().sphb200_gravity(ctx.handle, n, _ptr(m), _ptr(pts), float(G), eps, _ptr(out), _stream()))
+    return out.cpu().numpy()
+
+
 def sigma_effective(mineral_densities, mrn_constants, mu_specie):
     """nsc:69-74: effective cross-section per dust particle for an MRN size distribution (host table)."""
     return mu_specie * amu / mineral_densities * (3. / 4.) * -np.diff(mrn_constants ** -0.5) / np.diff(mrn_constants ** 0.5)

@@ -18,7 +18,7 @@ from . import constants as C
 STATE_FIELDS = {"points": 3, "velocities": 3, "total_accel": 3, "mass": 1, "sizes": 1, "T": 1, "E_internal": 1,
                 "mu_array": 1, "gamma_array": 1, "particle_type": 1, "densities_0": 1}
 RESULT_FIELDS = {"densities": 1, "num_densities": 1, "dust_densities": 1, "visc_heat": 1, "hydro_accel": 3,
-                 "visc_accel": 3, "pressure_accel": 3}
+                 "visc_accel": 3, "pressure_accel": 3, "grav_accel": 3}
 # owner-computed per-particle arrays the slab-decomposed driver reads / overwrites for ghosts (domain.py)
 AUX_FIELDS = {"densities": 1, "visc_pi": 1, "knn_h": 1, "dist_sq": 1, "gid": 1}
 # host-resident stepping (step_host): what crossing time / clamp / cell build / k-NN read, and what must
@@ -229,12 +229,33 @@ class Session(object):
                                                      seff.ctypes.data_as(ctypes.c_void_p), self._stream()))
         torch.cuda.current_stream(self.device).synchronize()       # f lives until the means are computed
 
+    def set_gravity(self, on=True, softening=None):
+        """self-gravity in the step (code_running.py:448,477).  softening=None follows the reference
+        (nsc:359): the median of `sizes` right after the neighbour search, recomputed every step (one host
+        synchronisation per step); a number fixes the Plummer length.  Direct O(N^2) sum: for N up to ~10^5."""
+        self._gravity = bool(on)
+        self._grav_soft = softening
+        if not on:
+            _lib.check(self.lib.sphb200_session_set_gravity(self.ctx.handle, C.G, 0.0))
+        elif softening is not None:
+            _lib.check(self.lib.sphb200_session_set_gravity(self.ctx.handle, C.G, float(softening)))
+
     def startup(self):
         """code_running.py:171-179: first neighbour query + hydro_update; densities_0 <- densities."""
         _lib.check(self.lib.sphb200_session_startup(self.ctx.handle, self._stream()))
 
     def step(self):
         """One pass of the while-body (code_running.py:217-540), asynchronous on the current stream."""
+        if getattr(self, "_gravity", False) and self._grav_soft is None:
+            # the reference's softening is the median of the sizes the search just returned (nsc:359 after :437)
+            for ph in ("crossing", "dt_clamp", "sort", "knn"):
+                self.phase(ph)
+            hs = torch.sort(self.download_tensor("sizes")).values         # np.median: mean of the two middle values
+            eps = float((0.5 * (hs[(self.n - 1) // 2] + hs[self.n // 2])).item())
+            _lib.check(self.lib.sphb200_session_set_gravity(self.ctx.handle, C.G, eps))
+            for ph in ("pack", "density", "pi", "force", "gravity", "integrate"):
+                self.phase(ph)
+            return
         _lib.check(self.lib.sphb200_session_step(self.ctx.handle, self._stream()))
 
     # -- slab decomposition (domain.py drives the collectives) ------------------------------------
