@@ -65,7 +65,8 @@ struct KnnGroupArgs {
 #define KG_TGT_BYTES (TILE_MAX_TARGETS * (8 + 8 + 4 + 4))       // R2lim | R2try/h2 | i | off+code / result
 #define KG_OFF_ROWS (KG_OFF_TGT + KG_TGT_BYTES)                 // TileRows
 #define KG_OFF_MISC (KG_OFF_ROWS + 384)                         // run table, segments, group id, mbarrier
-#define KG_SMEM (KG_OFF_MISC + 256)
+#define KG_OFF_L (KG_OFF_MISC + 256)                            // per warp: uint16 L[9][32], lane-private survivor columns
+#define KG_SMEM (KG_OFF_L + KG_WARPS * 9 * 32 * 2)
 
 struct KgMisc {
   int tbegin[4], tend[4], trow[4], tbase[5];    // target runs (tile.cuh group_target_run) and their prefix
@@ -231,6 +232,46 @@ __device__ __forceinline__ int knn_filter(const float* __restrict__ xf, const fl
   return count;
 }
 
+// FILTER, lane-private form: every lane appends its survivors to its own column of L (no ballots, no prefix sums in
+// the loop: a survivor costs its lane one predicated store and one saturating add); afterwards one warp scan of the
+// per-lane counts packs the columns into F.  Returns the number of survivors, or -1 when a column overflowed (the
+// caller falls back to the ballot form for this scan).
+#define KG_CAPL 8
+__device__ __forceinline__ int knn_filter_private(const float* __restrict__ xf, const float* __restrict__ yf,
+                                                  const float* __restrict__ zf, const int (*seg)[2], float pxf, float pyf,
+                                                  float pzf, float T2f, uint16_t* F, uint16_t* L, int lane) {
+  const unsigned long long PX = f2_pack(pxf, pxf), PY = f2_pack(pyf, pyf), PZ = f2_pack(pzf, pzf);
+  uint16_t* col = L + lane;
+  int nl = 0;
+#pragma unroll 1
+  for (int s = 0; s < 3; ++s) {
+    const int a = seg[s][0], b = seg[s][1];
+#pragma unroll 2
+    for (int base = a; base < b; base += 64) {
+      const int c = base + 2 * lane;
+      const float Tl = (c < b) ? T2f : -1.0f;
+      const unsigned long long X = *reinterpret_cast<const unsigned long long*>(xf + c);
+      const unsigned long long Y = *reinterpret_cast<const unsigned long long*>(yf + c);
+      const unsigned long long Z = *reinterpret_cast<const unsigned long long*>(zf + c);
+      const unsigned long long dx = f2_sub(X, PX), dy = f2_sub(Y, PY), dz = f2_sub(Z, PZ);
+      const unsigned long long d = f2_fma(dz, dz, f2_fma(dy, dy, f2_mul(dx, dx)));
+      if (__uint_as_float((unsigned)d) < Tl) { col[nl * 32] = (uint16_t)c; nl = min(nl + 1, KG_CAPL); }
+      if (__uint_as_float((unsigned)(d >> 32)) < Tl) { col[nl * 32] = (uint16_t)(c + 1); nl = min(nl + 1, KG_CAPL); }
+    }
+  }
+  if (__any_sync(0xffffffffu, nl >= KG_CAPL)) return -1;
+  int inc = nl;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += v; }
+  const int total = __shfl_sync(0xffffffffu, inc, 31);
+  if (total <= KG_CAPF) {
+    const int pre = inc - nl;
+#pragma unroll
+    for (int j = 0; j < KG_CAPL; ++j) if (j < nl) F[pre + j] = col[j * 32];
+  }
+  return total;
+}
+
 // SESSION layout, selection in registers.  Every lane holds up to four candidates (exact d^2, tile offset; absent:
 // idx < 0) of which `count` are valid, count >= k.  Keeps the k smallest by (d^2, offset), writes them as the
 // target's uint16 row (unordered, self in column 0) and returns the squared k-th distance; ok = false when more
@@ -344,6 +385,7 @@ __global__ void __launch_bounds__(KG_THREADS, KG_MIN_CTAS) knn_group_kernel(KnnG
   float* yf = xf + KG_XF_LEN;
   float* zf = yf + KG_XF_LEN;
   uint16_t* F = reinterpret_cast<uint16_t*>(smem + KG_OFF_F) + warp * KG_CAPF;
+  uint16_t* Lcol = reinterpret_cast<uint16_t*>(smem + KG_OFF_L) + warp * 9 * 32;
   double* keybuf = reinterpret_cast<double*>(smem + KG_OFF_KEY) + warp * KG_CAPF;
   int* idxbuf = reinterpret_cast<int*>(smem + KG_OFF_IDX) + warp * KG_CAPF;
   double* t_R2lim = reinterpret_cast<double*>(smem + KG_OFF_TGT);
@@ -520,7 +562,8 @@ __global__ void __launch_bounds__(KG_THREADS, KG_MIN_CTAS) knn_group_kernel(KnnG
         __syncwarp();
         const double Rc = sqrt(R2try) * g.inv_c + 1.7320508075688772 * eta;
         const float T2f = __double2float_ru(Rc * Rc * (1.0 + 4.0 * u24));
-        const int nf = knn_filter<ATOM>(xf, yf, zf, misc->seg[q], pxf, pyf, pzf, T2f, F, &misc->cntF[warp], lane);
+        int nf = ATOM ? -1 : knn_filter_private(xf, yf, zf, misc->seg[q], pxf, pyf, pzf, T2f, F, Lcol, lane);
+        if (nf < 0) { __syncwarp(); nf = knn_filter<ATOM>(xf, yf, zf, misc->seg[q], pxf, pyf, pzf, T2f, F, &misc->cntF[warp], lane); }
         if (nf > KG_CAPF) {                                   // too many: shrink the trial radius, scan again
           const double f = cbrt(0.75 * (double)KG_CAPF / (double)nf);
           R2try *= f * f;
