@@ -495,6 +495,10 @@ def run_ours(args):
         line["strong"] = strong
     if e2e is not None:
         line["e2e"] = e2e
+    if world == 1 and not args.no_e2e:
+        sess.close()
+        torch.cuda.empty_cache()
+        line["e2e_dropin"] = run_dropin(1000000, 3)
     if world == 1 and not args.no_cpu:
         cn = int(args.cpu_n) if args.cpu_n > 0 else 100000
         v, per = cpu_steps(cn, args.kind, seed_for(args.kind, int(args.n)), 5, 0, 1, args.move)   # ~10 s of CPU work at N = 1e5
@@ -557,6 +561,38 @@ def run_verify(world, rank, local_rank):
     dist.all_reduce(flag, op=dist.ReduceOp.MAX)
     torch.cuda.empty_cache()
     return msg
+
+
+def run_dropin(n, steps):
+    """The path a user of the reference gets when they only swap the module: `nsc.neighbors` plus the loop-generation
+    calls of the driver's while-body (code_running.py:437,451-458,222) with numpy arrays in and out, every call
+    crossing PCIe both ways (the uploaded neighbour array is reused between the calls of one step)."""
+    import numpy as np
+    from sphb200 import ics
+    from sphb200 import navier_stokes_cleaned as nsc
+    st = ics.uniform_box(n, 1)
+    p, m, pt, v = st["points"], st["mass"], st["particle_type"], st["velocities"]
+    E, g, mu, T = st["E_internal"], st["gamma_array"], st["mu_array"], st["T"]
+    nsc.d, nsc.dt_0 = st["d"], st["dt_0"] if "dt_0" in st else nsc.dt_0
+    h2d = d2h = 0
+    t0 = None
+    for it in range(steps + 1):
+        if it == 1:
+            t0 = time.perf_counter()
+        nb, _, dd, nontriv, sizes = nsc.neighbors(p, st["dist"], K_NEIGH)                 # :437
+        rho = nsc.density(p, m, pt, nb)                                                    # :451
+        rho_d = nsc.dust_density(p, m, nb, pt, sizes)                                      # :452
+        nd = nsc.num_dens(m, p, mu, nb)                                                    # :453
+        gp = nsc.del_pressure(p, m, pt, nb, E, g)                                          # :456
+        va, vh = nsc.artificial_viscosity(nb, p, pt, sizes, m, rho, v, T, g, mu)           # :458
+        ct = nsc.crossing_time(nb, v, sizes, pt)                                           # :222
+    per = (time.perf_counter() - t0) / steps
+    h2d = n * (24 + 8 * K_NEIGH + 6 * 24 + 30 * 8)      # points for the search, the neighbour array once, per-call vectors
+    d2h = n * (16 * K_NEIGH + 16 + 3 * 8 + 24 + 32)
+    return {"value": n / per, "unit": UNIT, "ms_per_step": per * 1e3, "particles": n, "steps": steps,
+            "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+            "api": "nsc.* drop-in: neighbors + density + dust_density + num_dens + del_pressure + artificial_viscosity + "
+                   "crossing_time, numpy in / numpy out (loop generation, the calls of code_running.py:437,451-458,222)"}
 
 
 def run_e2e(sess, world, dev, K, W, n_total, barrier, amp, step0):

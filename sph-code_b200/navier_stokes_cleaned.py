@@ -66,6 +66,25 @@ def _neighbor_array(neighbor, n):
     return nb
 
 
+# The driver passes the SAME (N,k) neighbour array to six calls per step (code_running.py:451-458); at 320 B per
+# particle its upload dominates each call.  The last uploaded array is kept on the device and reused when the
+# caller passes the same buffer again with the same content fingerprint (address, shape and a strided checksum:
+# an in-place edit of a sampled entry, or any new array, triggers a fresh upload).
+_nb_cache = {"key": None, "dev": None}
+
+
+def _neighbor_dev(neighbor, n):
+    nb = _neighbor_array(neighbor, n)
+    step = max(1, nb.size // 4096)
+    flat = nb.reshape(-1)
+    key = (nb.__array_interface__["data"][0], nb.shape, int(flat[::step].sum()), int(flat[-1]), int(flat[0]))
+    if _nb_cache["key"] == key and _nb_cache["dev"] is not None and isinstance(neighbor, np.ndarray):
+        return _nb_cache["dev"]
+    dev = _dev(nb, np.int64)
+    _nb_cache["key"], _nb_cache["dev"] = (key if isinstance(neighbor, np.ndarray) else None), dev
+    return dev
+
+
 def _check_bad_index(ctx, n):
     bad = ctx.counter("bad_index", _stream())
     if bad:
@@ -97,7 +116,7 @@ def hydro_update(neighbor, points, mass, sizes, f_un, particle_type, T, mu_array
     """nsc:556-671.  Returns (hydro_accel (N,3), visc_accel (N,3), visc_heat (N,), density (N,),
     num_density (N,), f_un_neighbor (S,N), dust_density (N,))."""
     ctx = _lib.context()
-    nb = _dev(_neighbor_array(neighbor, len(points)), np.int64)
+    nb = _neighbor_dev(neighbor, len(points))
     n, kk = nb.shape
     pts = _dev(points); vel = _dev(velocities)
     m = _dev(mass); hs = _dev(sizes); pt = _dev(particle_type); Tt = _dev(T); mu = _dev(mu_array); ga = _dev(gamma_array)
@@ -121,7 +140,7 @@ def hydro_update(neighbor, points, mass, sizes, f_un, particle_type, T, mu_array
 
 def _loop_density(mode, points, mass, neighbor, particle_type=None, sizes=None, mu_array=None):
     ctx = _lib.context()
-    nb = _dev(_neighbor_array(neighbor, len(points)), np.int64)
+    nb = _neighbor_dev(neighbor, len(points))
     n, kk = nb.shape
     pts = _dev(points); m = _dev(mass)
     pt = _dev(particle_type) if particle_type is not None else None
@@ -152,7 +171,7 @@ def num_dens(mass, points, mu_array, neighbor):
 def del_pressure(points, mass, particle_type, neighbor, E_internal, gamma_array):
     """nsc:755-774 (reads module global `d`)."""
     ctx = _lib.context()
-    nb = _dev(_neighbor_array(neighbor, len(points)), np.int64)
+    nb = _neighbor_dev(neighbor, len(points))
     n, kk = nb.shape
     pts = _dev(points); m = _dev(mass); pt = _dev(particle_type); E = _dev(E_internal); ga = _dev(gamma_array)
     out = torch.empty((n, 3), dtype=torch.float64, device=pts.device)
@@ -165,7 +184,7 @@ def del_pressure(points, mass, particle_type, neighbor, E_internal, gamma_array)
 def crossing_time(neighbor, velocities, sizes, particle_type):
     """nsc:776-786 (reads module global `dt_0`)."""
     ctx = _lib.context()
-    nb = _dev(_neighbor_array(neighbor, len(velocities)), np.int64)
+    nb = _neighbor_dev(neighbor, len(velocities))
     n, kk = nb.shape
     vel = _dev(velocities); hs = _dev(sizes); pt = _dev(particle_type)
     out = ctypes.c_double(0.0)
@@ -178,7 +197,7 @@ def crossing_time(neighbor, velocities, sizes, particle_type):
 def artificial_viscosity(neighbor, points, particle_type, sizes, mass, densities, velocities, T, gamma_array, mu_array):
     """nsc:788-816 (reads module global `d`).  Returns (visc_accel (N,3), visc_heat (N,))."""
     ctx = _lib.context()
-    nb = _dev(_neighbor_array(neighbor, len(points)), np.int64)
+    nb = _neighbor_dev(neighbor, len(points))
     n, kk = nb.shape
     pts = _dev(points); pt = _dev(particle_type); hs = _dev(sizes); m = _dev(mass); de = _dev(densities)
     vel = _dev(velocities); Tt = _dev(T); ga = _dev(gamma_array); mu = _dev(mu_array)
@@ -219,7 +238,7 @@ def grain_mass(mineral_densities, mrn_constants):
 def net_impulse(points, mass, sizes, velocities, particle_type, neighbor, f_un):
     """nsc:719-742, dust-gas drag.  Returns (accel_onto (N,3), accel_reaction (N,3))."""
     ctx = _lib.context()
-    nb = _dev(_neighbor_array(neighbor, len(points)), np.int64)
+    nb = _neighbor_dev(neighbor, len(points))
     n, kk = nb.shape
     pts = _dev(points); m = _dev(mass); hs = _dev(sizes); vel = _dev(velocities); pt = _dev(particle_type)
     f = _dev(np.ascontiguousarray(np.asarray(f_un, dtype=np.float64)))
