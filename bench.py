@@ -430,13 +430,17 @@ def run_ours(args):
         torch.cuda.empty_cache()
         s2, _, h2 = build_session(args, world, local_rank, "strong", 1e7)
         k2 = max(5, K // 2)
+        s2.counters(reset=True)
         ms2, ph2, _ = timed_steps(s2, s2.phases(), k2, 3, args.move * h2, barrier)
         s2.check()
+        c2 = s2.counters(reset=True)
         ms2 = allred([ms2], dist.ReduceOp.MAX)[0]
         nt2 = allred([float(s2.n_owned())], dist.ReduceOp.SUM)[0]
         strong = {"workload": "BASELINE configs[3]: uniform box, N=%d in total split over %d GPUs (strong), seed 3" % (int(nt2), world),
                   "particles_total": int(nt2), "steps": k2, "warmup": 3, "ms_per_step": ms2 / k2,
-                  "value": nt2 * k2 / (ms2 * 1e-3), "unit": UNIT, "phase_ms": {p: round(v, 4) for p, v in ph2.items()}}
+                  "value": nt2 * k2 / (ms2 * 1e-3), "unit": UNIT, "phase_ms": {p: round(v, 4) for p, v in ph2.items()},
+                  "per_step_rank0": {k: (v / float(k2 + 3) if k != "knn_worklist_last" else v) for k, v in c2.items()},
+                  "particles_rank0": int(s2.n_owned()), "particles_with_ghosts_rank0": int(s2.sess.n)}
         sess = s2
 
     if rank != 0:
