@@ -56,7 +56,8 @@ ALGO_BYTES = {"sort": 216.0, "knn": 32.0, "density": 76.0, "pi": 116.0, "force":
 # fp64 instructions per evaluated pair in the inner loops of the pair passes (counted in the SASS of the
 # shipped kernels, profiles/r02_sass_pair_loops.txt; a DFMA counts as one instruction)
 FP64_INSTR_PER_PAIR = {"density": 16.0, "pi": 46.0, "force": 30.0, "crossing": 9.0}
-PHASE_KERNEL = {"knn": "knn_", "density": "density", "pi": "pi_", "force": "force", "crossing": "crossing",
+PHASE_KERNEL = {"knn": "knn_group_kernel", "density": "tile_pass_kernel<DensityPass", "pi": "tile_pass_kernel<PiPass",
+                "force": "tile_pass_kernel<ForcePass", "crossing": "tile_pass_kernel<CrossingPass",
                 "integrate": "integrate_kernel", "sort": "reorder_kernel"}
 
 

@@ -13,6 +13,12 @@ KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "launch__grid_size", "launch__block_size", "smsp__thread_inst_executed_per_inst_executed.ratio"]
 
 
+EXTRA = ["l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
+         "smsp__inst_executed_pipe_fp64.sum", "smsp__inst_executed_pipe_lsu.sum", "smsp__inst_executed_pipe_alu.sum",
+         "smsp__inst_executed_pipe_fma.sum", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+         "launch__occupancy_limit_shared_mem", "launch__shared_mem_per_block_dynamic"]
+
+
 def launches(path, out):
     rows = [r for r in csv.reader(open(path)) if len(r) > 5]
     h = rows[0]
@@ -29,15 +35,19 @@ def launches(path, out):
             fh.write("%-72s %5d %10.1f %6.2f%%\n" % (n, a[0], a[1] / 1e3, 100 * a[1] / tot))
 
 
-def full(rep, out):
-    txt = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+def full(rep, out, header=""):
+    txt = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv", "--print-kernel-base", "demangled"],
+                         capture_output=True, text=True).stdout
     rows = list(csv.reader(txt.splitlines()))
     h, u = rows[0], rows[1]
     with open(out, "w") as fh:
+        if header:
+            fh.write("# %s\n" % header)
         for v in rows[2:]:
             fh.write("== %s\n" % v[h.index("Kernel Name")])
             for i, n in enumerate(h):
-                if n in KEYS or ("warp_issue_stalled" in n and n.endswith("_per_warp_active.pct") and float(v[i] or 0) > 5):
+                if n in KEYS or (n.startswith("smsp__average_warps_issue_stalled") and n.endswith("_per_issue_active.ratio")
+                                 and float(v[i] or 0) > 0.25) or n in EXTRA:
                     fh.write("  %-75s %-14s %s\n" % (n, u[i], v[i]))
 
 
@@ -45,4 +55,4 @@ if __name__ == "__main__":
     if sys.argv[1] == "launches":
         launches(sys.argv[2], sys.argv[3])
     else:
-        full(sys.argv[2], sys.argv[3])
+        full(sys.argv[2], sys.argv[3], " ".join(sys.argv[4:]))
