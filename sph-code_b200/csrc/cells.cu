@@ -351,6 +351,7 @@ int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint
   const int64_t max_cells64 = 2 * n + 4096;
   const int max_cells = (int)(max_cells64 < 1000000000 ? max_cells64 : 1000000000);
   ctx->max_cells = max_cells;
+  ctx->unit_tab_valid = 0;                                  // the pair passes rebuild their per-unit geometry table (hydro.cu)
   const int scan_blocks = ceil_div((int64_t)max_cells + 2, SCAN_TILE);
   SPH_TRY(devbuf_reserve(ctx->scal, SC_COUNT * sizeof(double)));
   SPH_TRY(devbuf_reserve(ctx->tmp0, 64 + BB_BLOCKS * BB_PART * sizeof(double)));

@@ -90,6 +90,8 @@ struct sphb200_ctx {
   DevBuf list16;                   // (N,k) uint16 neighbour rows as tile offsets (tile.cuh); session path
   DevBuf recD, recP, recK;         // per-pass records in sorted order: 48 B density, 80 B Pi/force, 8 B Pi coefficient
   DevBuf worklist;                 // k-NN targets left to the general kernel
+  DevBuf unit_tab;                 // per-unit tile geometry of the current cell list (hydro.cu), built on first use
+  int unit_tab_valid = 0;          // reset by build_cells
   DevBuf scal;                     // device scalars (doubles), see enum Scal
   DevBuf flags;                    // device ints: error / statistics counters
   DevBuf tmp0, tmp1, tmp2, tmp3;   // generic scratch
@@ -98,7 +100,7 @@ struct sphb200_ctx {
   double grid_pow = -3.0;          // cell edge from h_eff = (mean h^p)^(1/p) of the previous k-th distances (cells.cu)
   double cell_edge = 0.0;          // fixed cell edge (0 = from cell_occ)
   int knn_group = 32;              // lanes per target in the general k-NN kernel
-  int tile_cfg = 0;                // pair passes: 0 two stages per CTA, 1 one stage and more resident CTAs (hydro.cu)
+  int tile_cfg = 0;                // pair passes: 0 = measured best split of CTAs / producer / consumer warps, 1..3 others (hydro.cu)
   int knn_lane = 0;                // session fast path: lane-per-target kernel (knn_lane.cu); 0: warp-per-target (knn_group.cu)
   int knn_atomic = 0;              // fast path: filter survivors reserve their slot with shared-memory atomics
   int knn_fast = 1;                // 1: cell-tiled fast path (knn_cell.cu), 0: general kernel only

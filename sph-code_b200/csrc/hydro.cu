@@ -23,6 +23,7 @@
 #include "common.cuh"
 #include "kernels.cuh"
 #include "tile.cuh"
+#include <type_traits>
 #include <float.h>
 
 #define HY_THREADS 256
@@ -338,144 +339,276 @@ struct CrossingPass {
 
 // ---------------------------------------------------------------------------------------------
 // TILE form: producer / consumer pipeline over the half-groups of cells.
-// One producer warp computes the geometry of the NEXT unit and issues its bulk copies (records of the three
-// z-layers, the 8-byte coefficients, the uint16 rows of the unit's targets) into the other of two shared-memory
-// stages while the consumer warps work on the current one; "full" / "empty" mbarriers hand the stages over, so
-// the DRAM / L2 latency of a tile is hidden behind the arithmetic of the previous tile.
+// One producer warp walks the CTA's units (a unit = the targets of one z-half of a group), computes the geometry
+// of each one unit ahead and issues its bulk copies (records of the three z-layers, the 8-byte coefficients, the
+// uint16 rows of the unit's targets) into a RING of shared memory: a unit takes exactly the bytes it needs
+// (typically 30-50 KB of the ~220 KB ring), so four to seven units are in flight or being consumed at any time
+// and the DRAM / L2 latency of a fill (~2 us) is hidden behind the arithmetic of the units before it.  Each unit
+// has a descriptor slot with a "full" mbarrier (transaction count of its copies) and an "empty" mbarrier (one
+// arrival per consumer warp); units are released in the order they were filled, which is what lets the
+// producer reclaim ring space by waiting for the oldest unit only.
 // ---------------------------------------------------------------------------------------------
 struct TilePassArgs {
   const GridSpec* spec;
   const uint32_t* cell_start;
   const uint16_t* list16;      // (N, LIST_STRIDE(k)) tile offsets
   int n, k;
+  int ring_bytes;              // shared-memory ring (multiple of 128)
+  const int* unit_tab;         // per-unit geometry (TP_TAB_INTS ints each) of the current cell list, or nullptr
+  int unit_cap;                // units the table has room for
+  int debug;                   // tile_cfg option: 9 = consumers skip the pair loops (measures the fill pipeline alone)
 };
+
+#define TP_SLOTS 12            // descriptor slots = units in flight at most (divisible by the producer counts 1..4)
+#define TP_TEAMS 1             // consumer warps work in teams; a unit belongs to ONE team (unit sequence number mod TP_TEAMS)
+#define TP_PREFETCH 4          // units whose table entry the producer has requested ahead of the one it is issuing
 
 struct TpMeta {                // what the consumers need to know about a staged unit
   int tbegin[2], tbase[3];
   int o_lo, ntgt;
+  int base;                    // byte offset of the unit's data in the ring
+  int nrec;                    // records staged (padded); coefficients follow the records, rows follow those
+  int pad[3];
+};
+
+struct TpShared {              // fixed part of the shared memory, after the ring
+  TpMeta meta[TP_SLOTS];
+  TileRows rows[4];            // producers' scratch (geometry computed in the kernel when there is no table)
+  int plen4[4][4];
+  int end_off[TP_SLOTS];       // producer: ring offset where the unit of a slot ends
+  uint64_t full[TP_SLOTS], empty[TP_SLOTS];
 };
 
 template <class P>
-struct TpLayout {              // byte offsets inside one stage
-  static constexpr int OFF_K = TILE_HALF_CAP * P::REC;
-  static constexpr int OFF_L = OFF_K + (P::USE_K ? TILE_HALF_CAP * 8 : 0);
-  __host__ __device__ static int off_meta(int ks) { return (OFF_L + TILE_HALF_TARGETS * ks * 2 + 15) & ~15; }
-  __host__ __device__ static int stage_bytes(int ks) { return (off_meta(ks) + (int)sizeof(TpMeta) + 127) & ~127; }
-};
+__host__ __device__ constexpr int tp_unit_bytes_max(int ks) {
+  return ((TILE_HALF_CAP * (P::REC + (P::USE_K ? 8 : 0)) + TILE_HALF_TARGETS * ks * 2) + 127) & ~127;
+}
 
 // geometry of one unit as the producer warp holds it in registers between "computed" and "issued"
 struct TpGeom {
   int skip;                  // nothing to do for this unit (warp-uniform)
   int b0, b1, l0, l1, o_lo;  // target runs of the half-group, first staged tile offset (warp-uniform)
+  int nrec;                  // padded records of the three z-layers (warp-uniform)
   int plen, o, ps;           // this lane's row: padded length, tile offset relative to o_lo, first padded sorted index
 };
 
-template <class P, int NCW, int NS>
-__global__ void __launch_bounds__(32 * (NCW + 1), (NS == 1) ? 2 : 1) tile_pass_kernel(TilePassArgs a, typename P::Params p) {
+// Geometry of unit `unit` (all 32 lanes of one warp; rows / plen4: the warp's shared-memory scratch).
+__device__ __forceinline__ TpGeom tp_geometry(const GridSpec& g, const uint32_t* __restrict__ cell_start, int unit, int nunits,
+                                              int lane, TileRows* rows, int* plen4) {
+  TpGeom gm;
+  gm.skip = 1; gm.b0 = gm.b1 = gm.l0 = gm.l1 = gm.o_lo = gm.nrec = 0; gm.plen = gm.o = gm.ps = 0;
+  if (unit >= nunits) return gm;
+  const int group = unit >> 1, hz = unit & 1;
+  int gx, gy, gz;
+  group_coords(g, group, &gx, &gy, &gz);
+  const int cz = 2 * gz + hz;
+  if (cz >= g.nz) return gm;
+  __syncwarp();
+  tile_rows(g, cell_start, gx, gy, gz, lane, rows);
+  int b = 0, e = 0, r = 0;
+  const bool have = (lane < 4) && group_target_run(g, cell_start, gx, gy, gz, lane, &b, &e, &r);
+  if (lane < 4) plen4[lane] = have ? (e - b) : 0;
+  gm.b0 = __shfl_sync(0xffffffffu, b, 2 * hz);
+  gm.b1 = __shfl_sync(0xffffffffu, b, 2 * hz + 1);
+  gm.l0 = __shfl_sync(0xffffffffu, have ? e - b : 0, 2 * hz);
+  gm.l1 = __shfl_sync(0xffffffffu, have ? e - b : 0, 2 * hz + 1);
+  __syncwarp();
+  const int zlo = max(cz - 1, 0), zhi = min(cz + 1, g.nz - 1);
+  const int r_lo = (zlo - rows->z0) * rows->ysp, r_hi = (zhi - rows->z0 + 1) * rows->ysp;
+  gm.o_lo = rows->toff[r_lo];
+  gm.nrec = rows->toff[r_hi] - gm.o_lo;
+  // the same decision the k-NN kernel took for this group: the targets of a crowded group have global rows
+  gm.skip = (gm.l0 + gm.l1 == 0) || tile_crowded(g, rows, plen4);
+  const int rr = r_lo + lane;
+  if (rr < r_hi) { gm.plen = rows->toff[rr + 1] - rows->toff[rr]; gm.o = rows->toff[rr] - gm.o_lo; gm.ps = rows->ps[rr]; }
+  __syncwarp();
+  return gm;
+}
+
+// The same from the per-step table (unit_geometry_kernel): two coalesced loads per lane instead of a chain of
+// dependent cell_start lookups, so one producer warp keeps up with sixteen consumer warps.
+#define TP_TAB_INTS 48
+__device__ __forceinline__ TpGeom tp_geometry_load(const int* __restrict__ tabp, int unit, int nunits, int lane) {
+  TpGeom gm;
+  gm.skip = 1; gm.b0 = gm.b1 = gm.l0 = gm.l1 = gm.o_lo = gm.nrec = 0; gm.plen = gm.o = gm.ps = 0;
+  if (unit >= nunits) return gm;
+  const int* e = tabp + (size_t)unit * TP_TAB_INTS;
+  const int4 h0 = __ldg(reinterpret_cast<const int4*>(e)), h1 = __ldg(reinterpret_cast<const int4*>(e) + 1);
+  gm.skip = h0.x; gm.b0 = h0.y; gm.b1 = h0.z; gm.l0 = h0.w; gm.l1 = h1.x; gm.o_lo = h1.y; gm.nrec = h1.z;
+  if (lane < 12) { gm.plen = __ldg(e + 8 + 3 * lane); gm.o = __ldg(e + 9 + 3 * lane); gm.ps = __ldg(e + 10 + 3 * lane); }
+  return gm;
+}
+
+__global__ void __launch_bounds__(256) unit_geometry_kernel(const GridSpec* __restrict__ spec, const uint32_t* __restrict__ cell_start,
+                                                            int* __restrict__ tabp, int unit_cap) {
+  __shared__ TileRows rows_s[8];
+  __shared__ int plen4_s[8][4];
+  const GridSpec g = *spec;
+  const int nunits = 2 * g.ngroups;
+  if (nunits > unit_cap) return;                                            // the passes compute the geometry themselves
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int unit = blockIdx.x * 8 + w; unit < nunits; unit += gridDim.x * 8) {
+    const TpGeom gm = tp_geometry(g, cell_start, unit, nunits, lane, &rows_s[w], plen4_s[w]);
+    int* e = tabp + (size_t)unit * TP_TAB_INTS;
+    if (lane == 0) {
+      *reinterpret_cast<int4*>(e) = make_int4(gm.skip, gm.b0, gm.b1, gm.l0);
+      *(reinterpret_cast<int4*>(e) + 1) = make_int4(gm.l1, gm.o_lo, gm.nrec, 0);
+    }
+    if (lane < 12) { e[8 + 3 * lane] = gm.plen; e[9 + 3 * lane] = gm.o; e[10 + 3 * lane] = gm.ps; }
+  }
+}
+
+template <class P, int NCW, int NP, int MINB>
+__global__ void __launch_bounds__(32 * (NCW + NP), MINB) tile_pass_kernel(TilePassArgs a, typename P::Params p) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int ks = LIST_STRIDE(a.k);
-  const int stage_bytes = TpLayout<P>::stage_bytes(ks);
-  TileRows* rows = reinterpret_cast<TileRows*>(smem + NS * stage_bytes);               // producer's scratch
-  int* plen4 = reinterpret_cast<int*>(smem + NS * stage_bytes + 384);                   // target run lengths (producer)
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NS * stage_bytes + 384 + 32);     // full[NS], empty[NS]
+  TpShared* sh = reinterpret_cast<TpShared*>(smem + a.ring_bytes);
   const GridSpec g = *a.spec;
   const char* grec = P::records(p);
   const double* gk = P::kptr(p);
   if (tid == 0) {
-    for (int s = 0; s < NS; ++s) { mbar_init(&bars[s], 1); mbar_init(&bars[NS + s], NCW); }
+    for (int s = 0; s < TP_SLOTS; ++s) { mbar_init(&sh->full[s], 1); mbar_init(&sh->empty[s], NCW / TP_TEAMS); }
     mbar_fence_init();
   }
   __syncthreads();
   const int nunits = 2 * g.ngroups;
 
-  if (warp == NCW) {
-    // ================= producer warp =================
-    // The geometry of a unit (cell_start lookups: dependent global loads) is computed one unit AHEAD, while the
-    // previous unit's copies are in flight, so that a freed stage is refilled after one mbarrier wait only.
+  if (warp >= NCW) {
+    // ================= producer warps =================
+    // A producer spends ~200 dependent instructions per unit (ring bookkeeping, descriptor, expect_tx, 14-26 bulk
+    // copies), about 1.3 us next to 20 busy consumer warps, so NP of them share the work: producer r fills the
+    // units r, r + NP, ... (sequence numbers within the CTA) into its own NP-th of the ring; no coordination.
+    static_assert(TP_SLOTS % NP == 0, "a slot must always belong to the same producer");
+    const int pr = warp - NCW;
+    const int RING = (a.ring_bytes / NP) & ~127;
+    unsigned char* ring0 = smem + pr * RING;
+    TileRows* rows = &sh->rows[pr];
+    int* plen4 = sh->plen4[pr];
+    const bool tab = a.unit_tab != nullptr && nunits <= a.unit_cap;
     auto geometry = [&](int unit) -> TpGeom {
-      TpGeom gm;
-      gm.skip = 1; gm.b0 = gm.b1 = gm.l0 = gm.l1 = gm.o_lo = 0; gm.plen = gm.o = gm.ps = 0;
-      if (unit >= nunits) return gm;
-      const int group = unit >> 1, hz = unit & 1;
-      int gx, gy, gz;
-      group_coords(g, group, &gx, &gy, &gz);
-      const int cz = 2 * gz + hz;
-      if (cz >= g.nz) return gm;
-      __syncwarp();
-      tile_rows(g, a.cell_start, gx, gy, gz, lane, rows);
-      int b = 0, e = 0, r = 0;
-      const bool have = (lane < 4) && group_target_run(g, a.cell_start, gx, gy, gz, lane, &b, &e, &r);
-      if (lane < 4) plen4[lane] = have ? (e - b) : 0;
-      gm.b0 = __shfl_sync(0xffffffffu, b, 2 * hz);
-      gm.b1 = __shfl_sync(0xffffffffu, b, 2 * hz + 1);
-      gm.l0 = __shfl_sync(0xffffffffu, have ? e - b : 0, 2 * hz);
-      gm.l1 = __shfl_sync(0xffffffffu, have ? e - b : 0, 2 * hz + 1);
-      __syncwarp();
-      const int zlo = max(cz - 1, 0), zhi = min(cz + 1, g.nz - 1);
-      const int r_lo = (zlo - rows->z0) * rows->ysp, r_hi = (zhi - rows->z0 + 1) * rows->ysp;
-      gm.o_lo = rows->toff[r_lo];
-      // the same decision the k-NN kernel took for this group: the targets of a crowded group have global rows
-      gm.skip = (gm.l0 + gm.l1 == 0) || tile_crowded(g, rows, plen4);
-      const int rr = r_lo + lane;
-      if (rr < r_hi) { gm.plen = rows->toff[rr + 1] - rows->toff[rr]; gm.o = rows->toff[rr] - gm.o_lo; gm.ps = rows->ps[rr]; }
-      __syncwarp();
-      return gm;
+      if (tab) return tp_geometry_load(a.unit_tab, unit, nunits, lane);
+      return tp_geometry(g, a.cell_start, unit, nunits, lane, rows, plen4);
     };
-    int it = 0;
-    TpGeom gm = geometry(blockIdx.x);
-    for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x, ++it) {
-      const int s = it % NS, j = it / NS;
-      if (j >= 1) mbar_wait(&bars[NS + s], (j - 1) & 1);                   // the consumers released this stage
-      unsigned char* sb = smem + s * stage_bytes;
-      TpMeta* meta = reinterpret_cast<TpMeta*>(sb + TpLayout<P>::off_meta(ks));
+    int it = pr;
+    int head = 0, tail = 0, tail_it = pr;                                   // ring state (warp-uniform)
+#ifdef TP_PROFILE
+    long long t_wait = 0, t_issue = 0, t_geo = 0, t_all = clock64(); int n_wait = 0;
+#endif
+    // table entries are requested TP_PREFETCH units ahead, so the producer never waits for a global load
+    TpGeom pf[TP_PREFETCH];
+#pragma unroll
+    const int ustride = NP * gridDim.x;
+    for (int j = 0; j < TP_PREFETCH; ++j) pf[j] = geometry(blockIdx.x + pr * gridDim.x + j * ustride);
+    for (int unit = blockIdx.x + pr * gridDim.x; unit < nunits; unit += ustride, it += NP) {
+      const TpGeom gm = pf[0];
+      const int slot = it % TP_SLOTS;
+      const int ntg = gm.l0 + gm.l1;
+      const int off_k = gm.nrec * P::REC;
+      const int off_l = off_k + (P::USE_K ? gm.nrec * 8 : 0);
+      const int need = gm.skip ? 0 : ((off_l + ntg * ks * 2 + 127) & ~127);
+      int base = 0;
+#ifdef TP_PROFILE
+      long long c0 = clock64();
+#endif
+      for (;;) {
+        const int in_flight = (it - tail_it) / NP;
+        if (in_flight == 0) { head = 0; tail = 0; }
+        bool fits = false;
+        if (in_flight < TP_SLOTS / NP) {
+          if (head >= tail) {
+            if (need <= RING - head) { base = head; fits = true; }
+            else if (need < tail) { base = 0; fits = true; }                // wrap: the bytes up to RING stay unused this lap
+          } else if (need < tail - head) { base = head; fits = true; }
+        }
+        if (fits) break;
+        const int ts = tail_it % TP_SLOTS;
+        mbar_wait(&sh->empty[ts], (uint32_t)((tail_it / TP_SLOTS) & 1));    // the oldest unit was released by every consumer warp
+        tail = sh->end_off[ts];
+        tail_it += NP;
+#ifdef TP_PROFILE
+        ++n_wait;
+#endif
+      }
+#ifdef TP_PROFILE
+      long long c1 = clock64(); t_wait += c1 - c0;
+#endif
+      head = base + need;
+      TpMeta* meta = &sh->meta[slot];
       if (lane == 0) {
+        sh->end_off[slot] = head;
         meta->tbegin[0] = gm.b0; meta->tbegin[1] = gm.b1;
-        meta->tbase[0] = 0; meta->tbase[1] = gm.l0; meta->tbase[2] = gm.l0 + gm.l1;
+        meta->tbase[0] = 0; meta->tbase[1] = gm.l0; meta->tbase[2] = ntg;
         meta->o_lo = gm.o_lo;
-        meta->ntgt = gm.skip ? 0 : gm.l0 + gm.l1;
+        meta->ntgt = gm.skip ? 0 : ntg;
+        meta->base = pr * RING + base; meta->nrec = gm.nrec;
       }
       __syncwarp();
       if (gm.skip) {
-        if (lane == 0) mbar_expect_tx(&bars[s], 0u);                        // plain arrival: nothing to copy
+        if (lane == 0) mbar_expect_tx(&sh->full[slot], 0u);                 // plain arrival: nothing to copy
       } else {
-        fence_proxy_async();
-        unsigned tot = (unsigned)gm.plen * (unsigned)(P::REC + (P::USE_K ? 8 : 0));
-        if (lane == 0) tot += (unsigned)(gm.l0 + gm.l1) * (unsigned)(ks * 2);
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, d);
-        if (lane == 0) mbar_expect_tx(&bars[s], tot);
+        // (no proxy fence: the ring bytes were only READ through the generic proxy, and the consumers' mbarrier
+        //  arrivals that released them order those reads before the asynchronous writes issued here)
+        unsigned char* sb = ring0 + base;
+        const unsigned tot = (unsigned)gm.nrec * (unsigned)(P::REC + (P::USE_K ? 8 : 0)) + (unsigned)ntg * (unsigned)(ks * 2);
+        if (lane == 0) mbar_expect_tx(&sh->full[slot], tot);
         __syncwarp();
         if (gm.plen) {
-          bulk_g2s(sb + (size_t)gm.o * P::REC, grec + (size_t)gm.ps * P::REC, (unsigned)gm.plen * P::REC, &bars[s]);
-          if (P::USE_K) bulk_g2s(sb + TpLayout<P>::OFF_K + (size_t)gm.o * 8, gk + gm.ps, (unsigned)gm.plen * 8u, &bars[s]);
+          bulk_g2s(sb + (size_t)gm.o * P::REC, grec + (size_t)gm.ps * P::REC, (unsigned)gm.plen * P::REC, &sh->full[slot]);
+          if (P::USE_K) bulk_g2s(sb + off_k + (size_t)gm.o * 8, gk + gm.ps, (unsigned)gm.plen * 8u, &sh->full[slot]);
         }
-        uint16_t* rowsm = reinterpret_cast<uint16_t*>(sb + TpLayout<P>::OFF_L);
-        if (lane == 0 && gm.l0) bulk_g2s(rowsm, a.list16 + (int64_t)gm.b0 * ks, (unsigned)gm.l0 * ks * 2u, &bars[s]);
-        if (lane == 1 && gm.l1) bulk_g2s(rowsm + (size_t)gm.l0 * ks, a.list16 + (int64_t)gm.b1 * ks, (unsigned)gm.l1 * ks * 2u, &bars[s]);
+        uint16_t* rowsm = reinterpret_cast<uint16_t*>(sb + off_l);
+        if (lane == 0 && gm.l0) bulk_g2s(rowsm, a.list16 + (int64_t)gm.b0 * ks, (unsigned)gm.l0 * ks * 2u, &sh->full[slot]);
+        if (lane == 1 && gm.l1) bulk_g2s(rowsm + (size_t)gm.l0 * ks, a.list16 + (int64_t)gm.b1 * ks, (unsigned)gm.l1 * ks * 2u, &sh->full[slot]);
       }
-      gm = geometry(unit + gridDim.x);                                      // next unit, while these copies fly
+#ifdef TP_PROFILE
+      long long c2 = clock64(); t_issue += c2 - c1;
+#endif
+#pragma unroll
+      for (int j = 0; j + 1 < TP_PREFETCH; ++j) pf[j] = pf[j + 1];
+      pf[TP_PREFETCH - 1] = geometry(unit + TP_PREFETCH * ustride);
+#ifdef TP_PROFILE
+      t_geo += clock64() - c2;
+#endif
     }
+#ifdef TP_PROFILE
+    if (lane == 0 && (blockIdx.x == 0 || blockIdx.x == 77))
+      printf("TP_PROFILE cta %d rec %d ncw %d: units %d total %lld cyc, ring wait %lld (%d waits), issue %lld, prefetch %lld\n",
+             (int)blockIdx.x, P::REC, NCW, it, clock64() - t_all, t_wait, n_wait, t_issue, t_geo);
+#endif
     return;
   }
   // ================= consumer warps =================
   typename P::Final fin;
   P::final_init(fin);
   const int sub = lane & (HY_G - 1);
-  int it = 0;
-  for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x, ++it) {
-    const int s = it % NS;
-    mbar_wait(&bars[s], (it / NS) & 1);                                     // the stage is filled
-    const unsigned char* sb = smem + s * stage_bytes;
-    const TpMeta* meta = reinterpret_cast<const TpMeta*>(sb + TpLayout<P>::off_meta(ks));
+  constexpr int TPW = 32 / HY_G;                                            // targets a warp works on at a time
+  // Every mbarrier hand-over costs each participating warp ~40 cycles, so a unit is consumed by ONE team of
+  // WPT warps (the other teams work on the units before and after it).  A unit holds ~45 targets = ~11 quads
+  // for the team's WPT * TPW slots per round: the quads are dealt round-robin over the team's warps ACROSS its
+  // units (`rot` = quads dealt so far, mod WPT), so the warp that got one quad less is served first next time.
+  static_assert(NCW % TP_TEAMS == 0, "consumer warps must split evenly into teams");
+  constexpr int WPT = NCW / TP_TEAMS;
+  const int team = warp / WPT, wt = warp - team * WPT;
+  int rot = 0;
+  for (int it = team; blockIdx.x + (long long)it * gridDim.x < nunits; it += TP_TEAMS) {
+    const int slot = it % TP_SLOTS;
+    mbar_wait(&sh->full[slot], (uint32_t)((it / TP_SLOTS) & 1));            // the unit is filled
+    const TpMeta* meta = &sh->meta[slot];
     const int ntgt = meta->ntgt;
-    if (ntgt > 0) {
+    if (ntgt > 0 && a.debug < 90) {
+      const unsigned char* sb = smem + meta->base;
+      const int nrec = meta->nrec;
       const uint32_t trec = smem_u32(sb);
-      const uint32_t tk = smem_u32(sb + TpLayout<P>::OFF_K);
-      const uint32_t rowsm = smem_u32(sb + TpLayout<P>::OFF_L);
+      const uint32_t tk = trec + (uint32_t)(nrec * P::REC);
+      const uint32_t rowsm = tk + (P::USE_K ? (uint32_t)(nrec * 8) : 0u);
       const int o_lo = meta->o_lo, tb1 = meta->tbase[1], b0 = meta->tbegin[0], b1 = meta->tbegin[1];
-      for (int t0 = 0; t0 < ntgt; t0 += NCW * (32 / HY_G)) {
-        const int t = t0 + warp * (32 / HY_G) + (lane / HY_G);
+      const int nq = (ntgt + TPW - 1) / TPW;
+      int q0 = wt - rot;
+      if (q0 < 0) q0 += WPT;
+      rot = (rot + nq) % WPT;
+      for (int q = q0; q < nq; q += WPT) {
+        const int t = q * TPW + (lane / HY_G);
         const bool valid = t < ntgt;
         const int i = valid ? ((t >= tb1) ? b1 + (t - tb1) : b0 + t) : 0;
         const uint32_t row = rowsm + (uint32_t)((valid ? t : 0) * ks) * 2u;
@@ -514,47 +647,65 @@ __global__ void __launch_bounds__(32 * (NCW + 1), (NS == 1) ? 2 : 1) tile_pass_k
       }
     }
     __syncwarp();
-    if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&bars[NS + s])) : "memory");
+    if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&sh->empty[slot])) : "memory");
   }
   if (P::HAS_FINAL) P::final_flush(fin, p);
 }
 
-template <class P>
-static int tile_pass_smem(int k, int ns) {
-  return ns * TpLayout<P>::stage_bytes(LIST_STRIDE(k)) + 384 + 32 + 64;
-}
-
-template <class P, int NCW, int NS>
-static int launch_tile_pass_n(sphb200_ctx* ctx, int n, int k, const uint16_t* list16, const typename P::Params& p, int per_sm,
-                              cudaStream_t st) {
+// MINB CTAs per SM, each with its own producer warp, NCW consumer warps and a ring of 1/MINB of the SM's shared
+// memory.  More CTAs = more producer warps (a producer spends ~200 dependent instructions per unit, which bounds a
+// CTA at about one unit per 1.3 us) but shorter rings; NCW is what the pass's register count allows.
+template <class P, int NCW, int NP, int MINB>
+static int launch_tile_pass_cfg(sphb200_ctx* ctx, int n, int k, const uint16_t* list16, const typename P::Params& p, cudaStream_t st) {
+  const int ks = LIST_STRIDE(k);
+  const int fixed = ((int)sizeof(TpShared) + 127) & ~127;
+  const int ring = (((227 * 1024) / MINB - fixed - 1024) / 128) * 128;
+  if (tp_unit_bytes_max<P>(ks) > ((ring / NP) & ~127)) SPH_FAIL("tile pass: k=%d needs %d B of shared memory per unit", k, tp_unit_bytes_max<P>(ks));
   TilePassArgs a;
   a.spec = bufp<GridSpec>(ctx->grid_dev);
   a.cell_start = bufp<uint32_t>(ctx->cell_start);
   a.list16 = list16;
   a.n = n; a.k = k;
-  const int smem = tile_pass_smem<P>(k, NS);
-  CUDA_TRY(cudaFuncSetAttribute(tile_pass_kernel<P, NCW, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  tile_pass_kernel<P, NCW, NS><<<148 * per_sm, 32 * (NCW + 1), smem, st>>>(a, p);
+  a.ring_bytes = ring;
+  // per-unit geometry table of the current cell list, built by the first pass after a cell build
+  const int64_t cap64 = (int64_t)n / 8 + 4096;
+  const int unit_cap = (int)(cap64 < 40000000 ? cap64 : 40000000);
+  SPH_TRY(devbuf_reserve(ctx->unit_tab, (size_t)unit_cap * TP_TAB_INTS * sizeof(int)));
+  if (!ctx->unit_tab_valid) {
+    const int blocks = (unit_cap + 7) / 8 < 148 * 8 ? (unit_cap + 7) / 8 : 148 * 8;
+    unit_geometry_kernel<<<blocks, 256, 0, st>>>(a.spec, a.cell_start, bufp<int>(ctx->unit_tab), unit_cap);
+    ctx->launches += 1;
+    CUDA_TRY(cudaGetLastError());
+    ctx->unit_tab_valid = 1;
+  }
+  a.unit_tab = bufp<int>(ctx->unit_tab);
+  a.unit_cap = unit_cap;
+  a.debug = ctx->tile_cfg;
+  const int smem = ring + fixed;
+  CUDA_TRY(cudaFuncSetAttribute(tile_pass_kernel<P, NCW, NP, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  tile_pass_kernel<P, NCW, NP, MINB><<<148 * MINB, 32 * (NCW + NP), smem, st>>>(a, p);
   ctx->launches += 1;
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
 
-// tile_cfg 0: two stages per CTA (the producer runs a whole tile ahead), as many CTAs per SM as shared memory allows;
-//          1: one stage per CTA and two or more resident CTAs (more consumer warps per SM, fills hidden by the other CTAs)
+template <class P> struct TpSmall { static constexpr bool V = false; };       // records of <= 48 B: three rings fit an SM
+template <> struct TpSmall<DensityPass> { static constexpr bool V = true; };
+template <> struct TpSmall<CrossingPass> { static constexpr bool V = true; };
+
+// Measured at N = 10^6 (B200, profiles/README.md): the passes with small records are bound by the producers (most
+// CTAs / producers win), Pi and force by the consumers' shared-memory gathers (one CTA with a long ring wins).
+// tile_cfg 1..3 select other splits for experiments.
 template <class P>
 static int launch_tile_pass(sphb200_ctx* ctx, int n, int k, const uint16_t* list16, const typename P::Params& p, cudaStream_t st) {
-  if (ctx->tile_cfg == 1) {
-    const int smem1 = tile_pass_smem<P>(k, 1);
-    const int per1 = (227 * 1024) / (smem1 + 1024);
-    if (per1 >= 2) return launch_tile_pass_n<P, 12, 1>(ctx, n, k, list16, p, per1 > 4 ? 4 : per1, st);
-  }
-  const int smem = tile_pass_smem<P>(k, 2);
-  if (smem > 226 * 1024) SPH_FAIL("tile pass: k=%d needs %d B of shared memory", k, smem);
-  const int per_sm = (227 * 1024) / (smem + 1024);
-  // one resident CTA: 16 consumer warps; two or more: 8 each
-  if (per_sm <= 1) return launch_tile_pass_n<P, 16, 2>(ctx, n, k, list16, p, 1, st);
-  return launch_tile_pass_n<P, 8, 2>(ctx, n, k, list16, p, per_sm > 3 ? 3 : per_sm, st);
+  const int cfg = ctx->tile_cfg % 10;       // (tile_cfg >= 90: consumers skip the pair loops, to time the fill pipeline alone)
+  constexpr bool S = TpSmall<P>::V;
+  if (cfg == 1) return launch_tile_pass_cfg<P, S ? 24 : 20, 1, 1>(ctx, n, k, list16, p, st);
+  if (cfg == 2) return launch_tile_pass_cfg<P, S ? 24 : 20, 2, 1>(ctx, n, k, list16, p, st);
+  if (cfg == 3) return launch_tile_pass_cfg<P, 10, 1, 2>(ctx, n, k, list16, p, st);
+  if (std::is_same<P, CrossingPass>::value) return launch_tile_pass_cfg<P, 8, 1, 3>(ctx, n, k, list16, p, st);
+  if (std::is_same<P, DensityPass>::value) return launch_tile_pass_cfg<P, 12, 2, 2>(ctx, n, k, list16, p, st);
+  return launch_tile_pass_cfg<P, 20, 1, 1>(ctx, n, k, list16, p, st);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -376,6 +376,52 @@ __device__ __forceinline__ double knn_select16(const KnnGroupArgs& a, int i, int
   return (basepos > 0 && km > 0.0) ? km : 0.0;
 }
 
+// SESSION layout, the common case: at most two candidates per lane (count <= 64) and a few more than k of them.
+// The (count - k) largest are removed one at a time: a warp REDUX-max over the float-rounded keys, then every lane
+// clears its entries that equal the maximum - no ballots in the loop.  Two candidates whose float keys tie would be
+// removed together; the count of what is left is checked afterwards and ok = false sends the target to the
+// general kernel (exact by construction), so a tie can cost time but never a wrong row.
+#define KG_FAST_EXCESS 28
+__device__ __forceinline__ double knn_select2(const KnnGroupArgs& a, int i, int self, int count, double k0, double k1, int i0,
+                                              int i1, int lane, bool& ok) {
+  const int k = a.k;
+  unsigned f0 = (i0 >= 0) ? __float_as_uint(__double2float_ru(k0)) + 1u : 0u;   // 0 = absent / removed
+  unsigned f1 = (i1 >= 0) ? __float_as_uint(__double2float_ru(k1)) + 1u : 0u;
+#pragma unroll 1
+  for (int rm = count; rm > k; --rm) {
+    const unsigned m = __reduce_max_sync(0xffffffffu, max(f0, f1));
+    f0 = (f0 == m) ? 0u : f0;
+    f1 = (f1 == m) ? 0u : f1;
+  }
+  const unsigned b0 = __ballot_sync(0xffffffffu, f0 != 0u), b1 = __ballot_sync(0xffffffffu, f1 != 0u);
+  const int n0 = __popc(b0);
+  ok = (n0 + __popc(b1) == k);
+  if (!ok) return 0.0;
+  // squared k-th distance: the exact maximum of what is left
+  const unsigned m = __reduce_max_sync(0xffffffffu, max(f0, f1));
+  const unsigned o0 = __ballot_sync(0xffffffffu, f0 == m), o1 = __ballot_sync(0xffffffffu, f1 == m);
+  double km;
+  if (__popc(o0) + __popc(o1) == 1) {
+    km = __shfl_sync(0xffffffffu, o0 ? k0 : k1, __ffs(o0 | o1) - 1);
+  } else {
+    double kb = -1.0; int ib = -1;
+    if (f0 == m) { kb = k0; ib = i0; }
+    if (f1 == m && (k1 > kb || (k1 == kb && i1 > ib))) { kb = k1; ib = i1; }
+    warp_max_pair(kb, ib);
+    km = kb;
+  }
+  // the row: kept entries in (slice, lane) order, self swapped into column 0
+  const unsigned lt = (1u << lane) - 1u;
+  const unsigned s0 = __ballot_sync(0xffffffffu, f0 != 0u && i0 == self), s1 = __ballot_sync(0xffffffffu, f1 != 0u && i1 == self);
+  int ps = -1;
+  if (s0) ps = __popc(b0 & ((1u << (__ffs(s0) - 1)) - 1u));
+  else if (s1) ps = n0 + __popc(b1 & ((1u << (__ffs(s1) - 1)) - 1u));
+  uint16_t* out = a.list16 + (int64_t)i * LIST_STRIDE(k);
+  if (f0 != 0u) { const int pos = __popc(b0 & lt); out[(pos == ps) ? 0 : (pos == 0 && ps > 0 ? ps : pos)] = (uint16_t)i0; }
+  if (f1 != 0u) { const int pos = n0 + __popc(b1 & lt); out[(pos == ps) ? 0 : (pos == 0 && ps > 0 ? ps : pos)] = (uint16_t)i1; }
+  return (km > 0.0) ? km : 0.0;
+}
+
 template <bool SORTED, bool ATOM>
 __global__ void __launch_bounds__(KG_THREADS, KG_MIN_CTAS) knn_group_kernel(KnnGroupArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
@@ -613,7 +659,8 @@ __global__ void __launch_bounds__(KG_THREADS, KG_MIN_CTAS) knn_group_kernel(KnnG
           h2 = knn_emit<true>(a, i, off, count, keybuf, idxbuf, rowbase, lane);
         } else {
           bool ok;
-          h2 = knn_select16(a, i, off, count, nsl, R2try, kr, ir, lane, ok);
+          if (nsl <= 2 && count >= a.k && count - a.k <= KG_FAST_EXCESS) h2 = knn_select2(a, i, off, count, kr[0], kr[1], ir[0], ir[1], lane, ok);
+          else h2 = knn_select16(a, i, off, count, nsl, R2try, kr, ir, lane, ok);
           if (!ok) { verdict = 2; count = 0; }
         }
       }

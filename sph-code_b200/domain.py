@@ -52,6 +52,59 @@ def rows_from_state(state, gid=None):
 _NCCL_INPLACE = os.environ.get("SPHB200_NCCL_INPLACE", "0") == "1"
 
 
+def _parse_cpulist(text):
+    cpus = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def gpu_numa_info(device_index):
+    """{"bus": PCI bus id, "node": NUMA node of the GPU (-1 unknown), "cpus": CPUs of that node} from sysfs."""
+    info = {"bus": None, "node": -1, "cpus": set()}
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        idx = device_index
+        if vis:
+            ent = vis.split(",")[device_index].strip()
+            idx = int(ent) if ent.isdigit() else device_index
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(idx)).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        info["bus"] = bus
+        short = bus.lower()[-12:]                                   # sysfs uses a 4-digit PCI domain
+        with open("/sys/bus/pci/devices/%s/numa_node" % short) as fh:
+            info["node"] = int(fh.read().strip())
+        if info["node"] >= 0:
+            with open("/sys/devices/system/node/node%d/cpulist" % info["node"]) as fh:
+                info["cpus"] = _parse_cpulist(fh.read())
+    except Exception as e:                                          # no NVML / sysfs entry: leave the affinity alone
+        info["error"] = repr(e)
+    return info
+
+
+def bind_to_gpu_numa(device_index):
+    """Restrict this process to the CPUs of its GPU's NUMA node, so that the pinned staging buffers it allocates
+    afterwards (first touch) live in the memory next to the GPU's PCIe root.  Returns True when the affinity
+    changed.  SPHB200_NUMA_BIND=0 disables it."""
+    if os.environ.get("SPHB200_NUMA_BIND", "1") == "0":
+        return False
+    info = gpu_numa_info(device_index)
+    try:
+        allowed = os.sched_getaffinity(0)
+        target = allowed & info["cpus"]
+        if target and target != allowed:
+            os.sched_setaffinity(0, target)
+            return True
+    except (AttributeError, OSError):
+        pass
+    return False
+
+
 class SlabExchange(object):
     """Ownership by x-slab, migration, ghost selection and ghost refresh.  Works on any device."""
 
