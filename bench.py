@@ -53,9 +53,9 @@ PERTURB_SEED0 = 9000
 # algorithmic bytes per particle per launch (DESIGN.md "Kernels")
 ALGO_BYTES = {"sort": 216.0, "knn": 32.0, "density": 76.0, "pi": 116.0, "force": 156.0, "integrate": 248.0,
               "pack": 0.0, "crossing": 0.0, "dt_clamp": 0.0, "perturb": 0.0, "exchange": 0.0}
-# fp64 instructions per evaluated pair in the inner loops of the pair passes (counted in the SASS of the
-# shipped kernels, profiles/r02_sass_pair_loops.txt; a DFMA counts as one instruction)
-FP64_INSTR_PER_PAIR = {"density": 16.0, "pi": 46.0, "force": 30.0, "crossing": 9.0}
+# fp64 instructions per evaluated pair of the pair passes (executed D* thread-instructions of the ncu source page
+# divided by the pairs, profiles/r02_sass_pair_loops.txt; a DFMA counts as one instruction)
+FP64_INSTR_PER_PAIR = {"density": 17.6, "pi": 36.4, "force": 31.6, "crossing": 9.2}
 PHASE_KERNEL = {"knn": "knn_group_kernel", "density": "tile_pass_kernel<DensityPass", "pi": "tile_pass_kernel<PiPass",
                 "force": "tile_pass_kernel<ForcePass", "crossing": "tile_pass_kernel<CrossingPass",
                 "integrate": "integrate_kernel", "sort": "reorder_kernel"}

@@ -82,6 +82,7 @@ int sphb200_set_option(sphb200_ctx* ctx, const char* name, double value) {
   else if (!strcmp(name, "knn_atomic")) ctx->knn_atomic = value != 0.0;
   else if (!strcmp(name, "knn_lane")) ctx->knn_lane = value != 0.0;
   else if (!strcmp(name, "tile_cfg")) ctx->tile_cfg = (int)value;
+  else if (!strcmp(name, "knn_mma")) ctx->knn_mma = (int)value;
   else if (!strcmp(name, "grid_pow")) { if (value == 0.0) SPH_FAIL("grid_pow must not be 0"); ctx->grid_pow = value; }
   else if (!strcmp(name, "knn_margin")) { if (!(value >= 0)) SPH_FAIL("knn_margin must be >= 0"); ctx->knn_margin = value; }
   else SPH_FAIL("unknown option '%s'", name);

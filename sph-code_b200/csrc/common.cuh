@@ -102,6 +102,7 @@ struct sphb200_ctx {
   int knn_group = 32;              // lanes per target in the general k-NN kernel
   int tile_cfg = 0;                // pair passes: 0 = measured best split of CTAs / producer / consumer warps, 1..3 others (hydro.cu)
   int knn_lane = 0;                // session fast path: lane-per-target kernel (knn_lane.cu); 0: warp-per-target (knn_group.cu)
+  int knn_mma = 0;                 // 1: tensor-core filter variant of the session fast path (knn_mma.cu; same rows, not faster - DESIGN.md 4)
   int knn_atomic = 0;              // fast path: filter survivors reserve their slot with shared-memory atomics
   int knn_fast = 1;                // 1: cell-tiled fast path (knn_cell.cu), 0: general kernel only
   double knn_margin = 0.10;        // trial radius = previous k-th distance * (1 + margin)

@@ -282,6 +282,33 @@ def test_search_with_stale_guess(built_lib, kind, n, frac):
     assert worklist >= 0
 
 
+@pytest.mark.parametrize("option", ["knn_mma", "knn_lane", "knn_atomic"])
+def test_search_variants(built_lib, option):
+    """The optional forms of the session's fast search (tensor-core filter, lane-per-target kernel, atomic
+    survivor slots) give the oracle's rows bit for bit, first search and stale-guess search alike."""
+    from sphb200 import ics
+    from sphb200.session import Session
+    n = 40000
+    st = ics.uniform_box(n, 33)
+    s = Session(n, st["N_NEIGH"], st["dist"])
+    s.ctx.set_option(option, 1)
+    s.upload(st)
+    s.startup()
+    s.check()
+    oi, _, od, on, oh = O.neighbors(st["points"], st["dist"], st["N_NEIGH"])
+    assert np.array_equal(s.download("neighbor"), oi)
+    assert np.array_equal(s.download("sizes"), oh)
+    amp = 0.3 * float(np.median(oh))
+    s.perturb(amp, 78)
+    pts = st["points"] + ics.perturbation(np.arange(n), amp, 78)
+    s.search()
+    s.check()
+    oi, _, od, on, oh = O.neighbors(pts, st["dist"], st["N_NEIGH"])
+    assert np.array_equal(s.download("neighbor"), oi)
+    assert np.array_equal(s.download("sizes"), oh)
+    assert np.array_equal(s.download("num_nontrivial"), on)
+
+
 @pytest.mark.parametrize("kind,n", [("uniform", 20000), ("clustered", 30000)])
 def test_moving_steps(built_lib, kind, n):
     """Five steps in which every particle is displaced by up to 0.2 h per component between steps (the same
