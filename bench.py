@@ -374,6 +374,8 @@ def run_ours(args):
         import datetime
         import faulthandler
         faulthandler.dump_traceback_later(int(os.environ.get("BENCH_WATCHDOG_S", "900")), exit=True)
+        from sphb200 import domain as _domain
+        _domain.bind_to_gpu_numa(local_rank)      # pinned staging buffers next to the GPU's PCIe root (no-op on one NUMA node)
         dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=300))
     if rank == 0:
         ge.build()
