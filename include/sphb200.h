@@ -99,6 +99,21 @@ int sphb200_net_impulse(sphb200_ctx* ctx, int64_t n, int k, const int64_t* neigh
 int sphb200_gravity(sphb200_ctx* ctx, int64_t n, const double* mass, const double* points, double G, double softening,
                     double* accel, void* stream);
 
+/* ---- crossing time without any device allocation ---------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * sphb200_crossing_time (nsc:776-786), but the int32 neighbour list and the minimum slot live in a fixed file-scope
+ * device array of 16 MiB + 256 B that every GPU loading the library holds until exit; the call needs no context and
+ * performs no cudaMalloc / cudaFree.  LIMIT: n * k <= 4 194 304 neighbour entries (k = 40: n <= 104 857); larger
+ * inputs are rejected with an error.  All pointers are DEVICE pointers, including the outputs: result_dev (1 double,
+ * seconds) and bad_index_dev (1 int, may be NULL: entries of `neighbor` outside [-n, n), which are skipped); nothing
+ * is synchronised.  The first call on a device looks up the array's address (cudaGetSymbolAddress); make it before a
+ * stream capture starts.  Every call on a device shares the array: calls that overlap on the GPU (different streams,
+ * concurrently replayed graphs) race; calls ordered on one stream are independent. */
+int sphb200_crossing_time_noalloc(int device, int64_t n, int k, const int64_t* neighbor, const double* velocities,
+                                  const double* sizes, const double* particle_type, double dt_0, double* result_dev,
+                                  int* bad_index_dev, void* stream);
+
 /* ---- A10-A13: device-resident particle state and the whole time step ---------------------------
  * The reference keeps its particle state as module-level numpy arrays in the driver
  * (sph/code_running.py:121-167) and advances it inline (:217-540).  A session holds the same

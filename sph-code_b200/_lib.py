@@ -31,6 +31,7 @@ SIGNATURES = {
     "sphb200_del_pressure": [c_ptr, c_i64, c_int] + [c_ptr] * 6 + [c_dbl, c_ptr, c_ptr],
     "sphb200_artificial_viscosity": [c_ptr, c_i64, c_int] + [c_ptr] * 10 + [c_dbl, c_ptr, c_ptr, c_ptr],
     "sphb200_gravity": [c_ptr, c_i64, c_ptr, c_ptr, c_dbl, c_dbl, c_ptr, c_ptr],
+    "sphb200_crossing_time_noalloc": [c_int, c_i64, c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_dbl, c_ptr, c_ptr, c_ptr],
     "sphb200_session_set_gravity": [c_ptr, c_dbl, c_dbl],
     "sphb200_net_impulse": [c_ptr, c_i64, c_int] + [c_ptr] * 7 + [c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
     "sphb200_session_create": [c_ptr, c_i64, c_int, c_dbl],

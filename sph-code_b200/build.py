@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libsphb200.so")
 STAMP = os.path.join(HERE, "csrc", ".build_stamp")
-SOURCES = ["api.cu", "cells.cu", "knn.cu", "knn_group.cu", "knn_mma.cu", "knn_lane.cu", "hydro.cu", "loopgen.cu", "gravity.cu", "session.cu"]
+SOURCES = ["api.cu", "cells.cu", "knn.cu", "knn_group.cu", "knn_mma.cu", "knn_lane.cu", "hydro.cu", "loopgen.cu", "gravity.cu", "noalloc.cu", "session.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
               "--fmad=true", "-Xptxas", "-v"] + os.environ.get("SPHB200_NVCC_EXTRA", "").split()
 
