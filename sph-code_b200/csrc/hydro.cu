@@ -354,7 +354,8 @@ struct TilePassArgs {
   const uint16_t* list16;      // (N, LIST_STRIDE(k)) tile offsets
   int n, k;
   int ring_bytes;              // shared-memory ring (multiple of 128)
-  const int* unit_tab;         // per-unit geometry (TP_TAB_INTS ints each) of the current cell list, or nullptr
+  const int* unit_tab;         // geometry (TP_TAB_INTS ints each) of the ACTIVE units of the current cell list + rows
+  const int* unit_count;       // device: number of active units (> unit_cap: the table overflowed and is not used)
   int unit_cap;                // units the table has room for
   int debug;                   // tile_cfg option: 9 = consumers skip the pair loops (measures the fill pipeline alone)
 };
@@ -439,17 +440,40 @@ __device__ __forceinline__ TpGeom tp_geometry_load(const int* __restrict__ tabp,
   return gm;
 }
 
+// Table of the ACTIVE units: those with at least one target whose row is not in the global list.  Empty units (a
+// clustered particle distribution leaves most cells of its bounding box empty), crowded groups and units whose
+// targets all escaped to the global list cost the passes nothing.  The order of the table is the order in which the
+// warps of this kernel finish (every target is computed independently, so results do not depend on it).
 __global__ void __launch_bounds__(256) unit_geometry_kernel(const GridSpec* __restrict__ spec, const uint32_t* __restrict__ cell_start,
-                                                            int* __restrict__ tabp, int unit_cap) {
+                                                            const uint16_t* __restrict__ list16, int ks, int* __restrict__ tabp,
+                                                            int* __restrict__ count, int unit_cap) {
   __shared__ TileRows rows_s[8];
   __shared__ int plen4_s[8][4];
   const GridSpec g = *spec;
   const int nunits = 2 * g.ngroups;
-  if (nunits > unit_cap) return;                                            // the passes compute the geometry themselves
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   for (int unit = blockIdx.x * 8 + w; unit < nunits; unit += gridDim.x * 8) {
+    {                                                                       // cheap test first: any target at all?
+      const int group = unit >> 1, hz = unit & 1;
+      int gx, gy, gz;
+      group_coords(g, group, &gx, &gy, &gz);
+      int b = 0, e = 0, r = 0;
+      const bool have = (lane < 2) && group_target_run(g, cell_start, gx, gy, gz, 2 * hz + lane, &b, &e, &r);
+      if (!__any_sync(0xffffffffu, have && e > b)) continue;
+    }
     const TpGeom gm = tp_geometry(g, cell_start, unit, nunits, lane, &rows_s[w], plen4_s[w]);
-    int* e = tabp + (size_t)unit * TP_TAB_INTS;
+    if (gm.skip) continue;
+    bool need = false;
+    for (int t = lane; t < gm.l0 + gm.l1; t += 32) {
+      const int i = (t < gm.l0) ? gm.b0 + t : gm.b1 + (t - gm.l0);
+      need |= list16[(int64_t)i * ks] != (uint16_t)LIST_ESCAPED;
+    }
+    if (!__any_sync(0xffffffffu, need)) continue;
+    int slot = 0;
+    if (lane == 0) slot = atomicAdd(count, 1);
+    slot = __shfl_sync(0xffffffffu, slot, 0);
+    if (slot >= unit_cap) continue;                                         // overflow: the passes fall back to all units
+    int* e = tabp + (size_t)slot * TP_TAB_INTS;
     if (lane == 0) {
       *reinterpret_cast<int4*>(e) = make_int4(gm.skip, gm.b0, gm.b1, gm.l0);
       *(reinterpret_cast<int4*>(e) + 1) = make_int4(gm.l1, gm.o_lo, gm.nrec, 0);
@@ -472,7 +496,9 @@ __global__ void __launch_bounds__(32 * (NCW + NP), MINB) tile_pass_kernel(TilePa
     mbar_fence_init();
   }
   __syncthreads();
-  const int nunits = 2 * g.ngroups;
+  const int nactive = a.unit_tab ? *a.unit_count : 0x7fffffff;
+  const bool tab = nactive <= a.unit_cap;                                   // else: every unit, geometry computed here
+  const int nunits = tab ? nactive : 2 * g.ngroups;
 
   if (warp >= NCW) {
     // ================= producer warps =================
@@ -485,7 +511,6 @@ __global__ void __launch_bounds__(32 * (NCW + NP), MINB) tile_pass_kernel(TilePa
     unsigned char* ring0 = smem + pr * RING;
     TileRows* rows = &sh->rows[pr];
     int* plen4 = sh->plen4[pr];
-    const bool tab = a.unit_tab != nullptr && nunits <= a.unit_cap;
     auto geometry = [&](int unit) -> TpGeom {
       if (tab) return tp_geometry_load(a.unit_tab, unit, nunits, lane);
       return tp_geometry(g, a.cell_start, unit, nunits, lane, rows, plen4);
@@ -670,15 +695,22 @@ static int launch_tile_pass_cfg(sphb200_ctx* ctx, int n, int k, const uint16_t* 
   // per-unit geometry table of the current cell list, built by the first pass after a cell build
   const int64_t cap64 = (int64_t)n / 8 + 4096;
   const int unit_cap = (int)(cap64 < 40000000 ? cap64 : 40000000);
-  SPH_TRY(devbuf_reserve(ctx->unit_tab, (size_t)unit_cap * TP_TAB_INTS * sizeof(int)));
+  {
+    const void* before = ctx->unit_tab.p;
+    SPH_TRY(devbuf_reserve(ctx->unit_tab, 64 + (size_t)unit_cap * TP_TAB_INTS * sizeof(int)));   // [0]: count of active units
+    if (ctx->unit_tab.p != before) ctx->unit_tab_valid = 0;
+  }
   if (!ctx->unit_tab_valid) {
     const int blocks = (unit_cap + 7) / 8 < 148 * 8 ? (unit_cap + 7) / 8 : 148 * 8;
-    unit_geometry_kernel<<<blocks, 256, 0, st>>>(a.spec, a.cell_start, bufp<int>(ctx->unit_tab), unit_cap);
+    CUDA_TRY(cudaMemsetAsync(ctx->unit_tab.p, 0, 64, st));
+    unit_geometry_kernel<<<blocks, 256, 0, st>>>(a.spec, a.cell_start, list16, ks, bufp<int>(ctx->unit_tab) + 16,
+                                                 bufp<int>(ctx->unit_tab), unit_cap);
     ctx->launches += 1;
     CUDA_TRY(cudaGetLastError());
     ctx->unit_tab_valid = 1;
   }
-  a.unit_tab = bufp<int>(ctx->unit_tab);
+  a.unit_tab = bufp<int>(ctx->unit_tab) + 16;
+  a.unit_count = bufp<int>(ctx->unit_tab);
   a.unit_cap = unit_cap;
   a.debug = ctx->tile_cfg;
   const int smem = ring + fixed;

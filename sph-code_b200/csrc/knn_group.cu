@@ -501,6 +501,7 @@ int launch_knn_group(sphb200_ctx* ctx, int n, int k, double dist, int use_guess,
                      int32_t* list, double* dists, double* h_out, int32_t* nontriv, cudaStream_t st) {
   if (k < 1 || k > knn_group_max_k()) SPH_FAIL("knn_group: k=%d outside [1, %d]", k, knn_group_max_k());
   SPH_TRY(devbuf_reserve(ctx->worklist, (size_t)(n + 1) * sizeof(int32_t)));
+  ctx->unit_tab_valid = 0;                                    // the pair passes' table of active units depends on the rows
   int* flags = bufp<int>(ctx->flags);
   int* nwork = flags + FL_KNN_NWORK;
   CUDA_TRY(cudaMemsetAsync(nwork, 0, 2 * sizeof(int), st));   // FL_KNN_NWORK and FL_GROUP_NEXT are adjacent
