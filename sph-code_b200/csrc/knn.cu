@@ -18,6 +18,7 @@
 // distances and the returned h = sqrt(d^2_k) are bit-identical to the CPU oracle.
 #include "common.cuh"
 #include "kernels.cuh"
+#include "knn_select.cuh"
 #include <cooperative_groups.h>
 #include <cooperative_groups/reduce.h>
 #include <float.h>
@@ -203,6 +204,42 @@ knn_kernel(const double4* __restrict__ r0, const uint32_t* __restrict__ keys, co
     if (widened) atomicAdd(&flags[FL_KNN_WIDEN], 1);
   }
   if (count > cap) count = cap;
+  // ---- session rows (work list of the fast path): an unordered set with the nearest candidate in column 0 ----
+  // Ranking by counting costs count^2 / 32 comparisons per lane (half of this kernel's instructions when most
+  // targets of a clustered distribution arrive here); the register-resident removal selection of the fast path
+  // (knn_select.cuh) needs a tenth of that.  It works on POSITIONS in the candidate buffer, which ascend with the
+  // sorted index (rows are scanned in ascending order), so ties in d^2 break as the ranking would break them.
+  if (G == 32 && by_slot && !dists && count >= k && count <= 32 * KG_SLICES) {
+    uint16_t* rowsm = reinterpret_cast<uint16_t*>(smem_raw + (size_t)GROUPS * cap * 12) + (size_t)grp * 64;
+    const int nsl = (count + 31) >> 5;
+    double kr[KG_SLICES]; int ir[KG_SLICES];
+    unsigned long long kmin = ~0ull;
+#pragma unroll
+    for (int r = 0; r < KG_SLICES; ++r) {
+      const int e = 32 * r + lane;
+      kr[r] = -1.0; ir[r] = -1;
+      if (e < count) { const unsigned long long kb = keybuf[e]; kr[r] = __longlong_as_double((long long)kb); ir[r] = e; if (kb < kmin) kmin = kb; }
+    }
+    const unsigned long long kall = cg::reduce(tile, kmin, cg::less<unsigned long long>());
+    int pmin = 0x7fffffff;                                    // first position that holds the smallest key
+#pragma unroll
+    for (int r = KG_SLICES - 1; r >= 0; --r)
+      if (ir[r] >= 0 && (unsigned long long)__double_as_longlong(kr[r]) == kall) pmin = ir[r];
+    pmin = cg::reduce(tile, pmin, cg::less<int>());
+    KnnGroupArgs fa;
+    fa.k = k; fa.list16 = rowsm;
+    bool ok;
+    double h2;
+    if (nsl <= 2 && count - k <= KG_FAST_EXCESS) h2 = knn_select2(fa, 0, pmin, count, kr[0], kr[1], ir[0], ir[1], lane, ok);
+    else h2 = knn_select16(fa, 0, pmin, count, nsl, R2try, kr, ir, lane, ok);
+    tile.sync();
+    if (ok) {
+      for (int s2 = lane; s2 < k; s2 += G) list[row + s2] = idxbuf[rowsm[s2]];
+      if (lane == 0) { nontriv[i] = k; h_out[i] = sqrt(h2); }
+      tile.sync();
+      continue;
+    }
+  }
   // ---- rank by counting; rank < k are the neighbours, in ascending (d^2, index) order ----
   const int nsel = count < k ? count : k;
   for (int e = lane; e < count; e += G) {
@@ -244,7 +281,7 @@ static int launch_knn_impl(sphb200_ctx* ctx, int n, int k, double dist, int use_
   const int cap = knn_cap_for(k);
   const int G = ctx->knn_group;
   const int groups = KNN_THREADS / G;
-  const size_t smem = (size_t)groups * cap * 12;
+  const size_t smem = (size_t)groups * cap * 12 + (size_t)groups * 128;   // candidates + one uint16 row per group (session rows)
   if (smem > 200 * 1024) SPH_FAIL("knn: k=%d needs %zu B of shared memory per block", k, smem);
   double dist2 = dist * dist;                 // cKDTree squares the upper bound for p=2
   if (!(dist2 == dist2)) dist2 = INFINITY;
