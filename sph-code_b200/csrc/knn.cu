@@ -28,7 +28,7 @@ namespace cg = cooperative_groups;
 #define KNN_MAX_ITER 96
 
 template <int G>
-__global__ void __launch_bounds__(KNN_THREADS)
+__global__ void __launch_bounds__(KNN_THREADS, 8)
 knn_kernel(const double4* __restrict__ r0, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ cell_start,
            const GridSpec* __restrict__ spec, int n, int k, double dist2, int cap, int use_guess, double guess_factor,
            int32_t* __restrict__ list, double* __restrict__ dists, double* __restrict__ h_out,
@@ -98,40 +98,71 @@ knn_kernel(const double4* __restrict__ r0, const uint32_t* __restrict__ keys, co
     // The targets that reach this kernel are few (one warp each, nearly empty GPU), so the scan is bound by
     // load latency: the row bounds of up to G rows are fetched by the lanes at once, and two candidate
     // batches are in flight per trip.
+    // Only the cells the trial sphere can reach are scanned: a row (y, z) whose cell column is farther than R_try
+    // from the target is skipped, the others are cut to the chord of the sphere along x.  For a block of (2m+1)^3
+    // cells this leaves about the sphere's share of the cube (a third of the candidates at m = 3).  Distances are
+    // taken in cell units with the expression that assigned the particles to their cells, minus a safety margin;
+    // the clamped boundary cells only hold particles that are farther away than their cell, so the cut is safe.
     ++rescans;
     count = 0;
     for (int rb = 0; rb < nrows; rb += G) {
       int my_s = 0, my_e = 0;
       if (rb + lane < nrows) {
         const int r = rb + lane;
-        const int base = ((z0 + r / ysp) * g.ny + (y0 + r % ysp)) * g.nx;
-        my_s = (int)cell_start[base + x0]; my_e = (int)cell_start[base + x1 + 1];
+        const int yy = y0 + r % ysp, zz = z0 + r / ysp;
+        const int base = (zz * g.ny + yy) * g.nx;
+        const double fx = (p.x - g.ox) * g.inv_c, fy = (p.y - g.oy) * g.inv_c, fz = (p.z - g.oz) * g.inv_c;
+        const double Rc2 = R2try * g.inv_c * g.inv_c * (1.0 + 1e-9);
+        const double dyc = fmax(fmax((double)yy - fy, fy - (double)(yy + 1)) - 1e-6, 0.0);
+        const double dzc = fmax(fmax((double)zz - fz, fz - (double)(zz + 1)) - 1e-6, 0.0);
+        const double rem = Rc2 - dyc * dyc - dzc * dzc;
+        if (rem > 0.0) {
+          const double w = sqrt(rem) + 1e-6;
+          int xa = x0, xb = x1;
+          if (w < 1.0e9) { xa = max(x0, (int)floor(fx - w)); xb = min(x1, (int)floor(fx + w)); }
+          if (xa <= xb) { my_s = (int)cell_start[base + xa]; my_e = (int)cell_start[base + xb + 1]; }
+        }
       }
-      const int rn = min(G, nrows - rb);
-      for (int r = 0; r < rn; ++r) {
-        const int s = tile.shfl(my_s, r), e = tile.shfl(my_e, r);
-        for (int jb = s; jb < e; jb += 2 * G) {
-          const int ja = jb + lane, jc = jb + G + lane;
-          double4 qa = make_double4(0, 0, 0, 0), qc = make_double4(0, 0, 0, 0);
-          if (ja < e) qa = r0[ja];
-          if (jc < e) qc = r0[jc];
+      // The (cut) rows of this batch are short - a few particles each where the grid is finer than the smoothing
+      // length - so they are scanned as ONE flattened sequence: an inclusive scan of the row lengths over the lanes,
+      // then candidate t of the batch is found by a binary search in that prefix (5 shuffles) instead of spending a
+      // trip of 2 G lanes on every row.  Candidates still arrive in ascending sorted index.
+      const int len = my_e - my_s;
+      int inc = len;
 #pragma unroll
-          for (int half = 0; half < 2; ++half) {
-            const int j = half ? jc : ja;
-            const double4 q = half ? qc : qa;
-            bool ok = false;
-            double d2 = 0.0;
-            if (j < e) {
-              const double dx = q.x - p.x, dy = q.y - p.y, dz = q.z - p.z;
-              d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
-              ok = d2 < R2try;
-            }
-            const unsigned b = tile.ballot(ok);
-            if (b) {
-              const int pos = count + __popc(b & ((1u << lane) - 1u));
-              if (ok && pos < cap) { keybuf[pos] = (unsigned long long)__double_as_longlong(d2); idxbuf[pos] = j; }
-              count += __popc(b);
-            }
+      for (int d = 1; d < G; d <<= 1) { const int v = tile.shfl_up(inc, d); if (lane >= d) inc += v; }
+      const int T = tile.shfl(inc, G - 1);
+      const int exc = inc - len;
+      for (int t0 = 0; t0 < T; t0 += 2 * G) {
+        int jj[2]; bool vv[2];
+        double4 qq[2];
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          const int t = t0 + half * G + lane;
+          vv[half] = t < T;
+          const int tc = vv[half] ? t : T - 1;
+          int lo = 0;
+#pragma unroll
+          for (int step = G / 2; step > 0; step >>= 1) { const int v = tile.shfl(inc, lo + step - 1); if (v <= tc) lo += step; }
+          jj[half] = tile.shfl(my_s, lo) + (tc - tile.shfl(exc, lo));
+          qq[half] = make_double4(0, 0, 0, 0);
+          if (vv[half]) qq[half] = r0[jj[half]];
+        }
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          bool ok = false;
+          double d2 = 0.0;
+          if (vv[half]) {
+            const double4 q = qq[half];
+            const double dx = q.x - p.x, dy = q.y - p.y, dz = q.z - p.z;
+            d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+            ok = d2 < R2try;
+          }
+          const unsigned b = tile.ballot(ok);
+          if (b) {
+            const int pos = count + __popc(b & ((1u << lane) - 1u));
+            if (ok && pos < cap) { keybuf[pos] = (unsigned long long)__double_as_longlong(d2); idxbuf[pos] = jj[half]; }
+            count += __popc(b);
           }
         }
       }

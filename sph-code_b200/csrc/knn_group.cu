@@ -386,6 +386,9 @@ __global__ void __launch_bounds__(KG_THREADS, KG_MIN_CTAS) knn_group_kernel(KnnG
         }
         R2try = fmin(R2try, R2lim);
         if (!(R2try > 0.0)) R2try = 0.0;
+        // The previous k-th distance already exceeds what the scanned region covers: the scan would almost surely end
+        // in the work list, so the target goes there at once (the general kernel is exact whatever the reason).
+        if (a.use_guess && p.w > 0.0 && p.w * p.w > R2lim && R2lim < a.dist2) R2try = -2.0;
       }
       t_R2lim[t] = R2lim; t_R2try[t] = R2try; t_i[t] = i; t_word[t] = off | (q << 16);
     }
@@ -393,6 +396,7 @@ __global__ void __launch_bounds__(KG_THREADS, KG_MIN_CTAS) knn_group_kernel(KnnG
     // ---- the search: one warp per target ----
     for (int t = warp; t < ntgt; t += KG_WARPS) {
       double R2try = t_R2try[t];
+      if (R2try == -2.0) { if (lane == 0) { t_R2try[t] = 0.0; t_word[t] = 0x100; } continue; }   // straight to the work list
       if (R2try < 0.0) { if (lane == 0) t_word[t] = -1; continue; }
       const double R2lim = t_R2lim[t];
       const int word = t_word[t];
