@@ -57,7 +57,7 @@ int sphb200_destroy(sphb200_ctx* ctx) {
   session_free(ctx);
   DevBuf* all[] = {&ctx->r0, &ctx->recD, &ctx->recP, &ctx->recK, &ctx->rho, &ctx->pi_, &ctx->aux, &ctx->list, &ctx->list16,
                    &ctx->keys, &ctx->keys_alt, &ctx->perm, &ctx->perm_alt, &ctx->cell_start, &ctx->scan_tops, &ctx->grid_dev,
-                   &ctx->scal, &ctx->flags, &ctx->worklist, &ctx->unit_tab, &ctx->tmp0, &ctx->tmp1, &ctx->tmp2, &ctx->tmp3};
+                   &ctx->scal, &ctx->flags, &ctx->worklist, &ctx->group_list, &ctx->unit_tab, &ctx->tmp0, &ctx->tmp1, &ctx->tmp2, &ctx->tmp3};
   for (DevBuf* b : all) devbuf_free(*b);
   for (DevBuf& b : ctx->sbuf) devbuf_free(b);
   delete ctx;

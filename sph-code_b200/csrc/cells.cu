@@ -344,6 +344,43 @@ void devbuf_free(DevBuf& b) {
 // ctx->keys the sorted cell keys, ctx->perm the sorted->source permutation, ctx->cell_start the
 // (ncells + 2) exclusive scan and ctx->r0 the sorted {x,y,z,guess} records.  Nothing synchronises unless
 // `sync_host` asks for the host copy ctx->grid (function-level API).
+// Groups of 2x2x2 cells (tile.cuh) that hold at least one particle, in roughly ascending order (each block keeps the
+// order of its chunk and appends it with one atomic).  A clustered distribution leaves most cells of its bounding
+// box empty; the group-tiled kernels walk this list instead of every group.
+__global__ void __launch_bounds__(256) active_groups_kernel(const GridSpec* __restrict__ spec, const uint32_t* __restrict__ cell_start,
+                                                            int* __restrict__ list) {
+  __shared__ int wsum[8];
+  __shared__ int base_s;
+  const GridSpec g = *spec;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int first = blockIdx.x * 256; first < g.ngroups; first += gridDim.x * 256) {
+    const int grp = first + threadIdx.x;
+    bool any = false;
+    if (grp < g.ngroups) {
+      const int q = grp / g.ngx;
+      const int gx = grp - q * g.ngx, gz = q / g.ngy, gy = q - gz * g.ngy;
+      const int cx0 = 2 * gx, cx1 = min(2 * gx + 1, g.nx - 1);
+      for (int r = 0; r < 4 && !any; ++r) {
+        const int cy = 2 * gy + (r & 1), cz = 2 * gz + (r >> 1);
+        if (cy >= g.ny || cz >= g.nz) continue;
+        const int base = (cz * g.ny + cy) * g.nx;
+        any = cell_start[base + cx1 + 1] > cell_start[base + cx0];
+      }
+    }
+    const unsigned b = __ballot_sync(0xffffffffu, any);
+    if (lane == 0) wsum[w] = __popc(b);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int tot = 0;
+      for (int i = 0; i < 8; ++i) { const int c = wsum[i]; wsum[i] = tot; tot += c; }
+      base_s = tot ? atomicAdd(&list[0], tot) : 0;
+    }
+    __syncthreads();
+    if (any) list[1 + base_s + wsum[w] + __popc(b & ((1u << lane) - 1u))] = grp;
+    __syncthreads();
+  }
+}
+
 int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint, const double* guess, int knn_k,
                 bool sync_host, cudaStream_t st) {
   if (n <= 0) SPH_FAIL("build_cells: empty particle set");
@@ -356,6 +393,7 @@ int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint
   SPH_TRY(devbuf_reserve(ctx->scal, SC_COUNT * sizeof(double)));
   SPH_TRY(devbuf_reserve(ctx->tmp0, 64 + BB_BLOCKS * BB_PART * sizeof(double)));
   SPH_TRY(devbuf_reserve(ctx->grid_dev, sizeof(GridSpec)));
+  SPH_TRY(devbuf_reserve(ctx->group_list, ((size_t)max_cells + 16) * sizeof(int)));   // ngroups <= ncells
   SPH_TRY(devbuf_reserve(ctx->keys, n * sizeof(uint32_t)));
   SPH_TRY(devbuf_reserve(ctx->keys_alt, n * sizeof(uint32_t)));
   SPH_TRY(devbuf_reserve(ctx->perm, n * sizeof(uint32_t)));
@@ -382,7 +420,9 @@ int build_cells(sphb200_ctx* ctx, const double* pts, int64_t n, double edge_hint
   scatter_kernel<<<nblk, 256, 0, st>>>(n, keys_src, rank, cs, bufp<uint32_t>(ctx->perm), bufp<uint32_t>(ctx->keys));
   cell_order_kernel<<<148 * 4, 256, 0, st>>>(spec, cs, bufp<uint32_t>(ctx->perm), rank);
   gather_pos_kernel<<<nblk, 256, 0, st>>>(pts, bufp<uint32_t>(ctx->perm), guess, n, bufp<double4>(ctx->r0));
-  ctx->launches += 11;
+  CUDA_TRY(cudaMemsetAsync(ctx->group_list.p, 0, sizeof(int), st));
+  active_groups_kernel<<<148 * 2, 256, 0, st>>>(spec, cs, bufp<int>(ctx->group_list));
+  ctx->launches += 12;
   CUDA_TRY(cudaGetLastError());
   if (sync_host) {
     CUDA_TRY(cudaMemcpyAsync(&ctx->grid, spec, sizeof(GridSpec), cudaMemcpyDeviceToHost, st));

@@ -90,6 +90,7 @@ struct sphb200_ctx {
   DevBuf list16;                   // (N,k) uint16 neighbour rows as tile offsets (tile.cuh); session path
   DevBuf recD, recP, recK;         // per-pass records in sorted order: 48 B density, 80 B Pi/force, 8 B Pi coefficient
   DevBuf worklist;                 // k-NN targets left to the general kernel
+  DevBuf group_list;               // [0]: number of groups that hold particles, [1..]: their ids (cells.cu), for the tiled kernels
   DevBuf unit_tab;                 // per-unit tile geometry of the current cell list (hydro.cu), built on first use
   int unit_tab_valid = 0;          // reset by build_cells
   DevBuf scal;                     // device scalars (doubles), see enum Scal

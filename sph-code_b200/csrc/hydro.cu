@@ -445,14 +445,16 @@ __device__ __forceinline__ TpGeom tp_geometry_load(const int* __restrict__ tabp,
 // targets all escaped to the global list cost the passes nothing.  The order of the table is the order in which the
 // warps of this kernel finish (every target is computed independently, so results do not depend on it).
 __global__ void __launch_bounds__(256) unit_geometry_kernel(const GridSpec* __restrict__ spec, const uint32_t* __restrict__ cell_start,
-                                                            const uint16_t* __restrict__ list16, int ks, int* __restrict__ tabp,
-                                                            int* __restrict__ count, int unit_cap) {
+                                                            const int* __restrict__ group_list, const uint16_t* __restrict__ list16,
+                                                            int ks, int* __restrict__ tabp, int* __restrict__ count, int unit_cap) {
   __shared__ TileRows rows_s[8];
   __shared__ int plen4_s[8][4];
   const GridSpec g = *spec;
   const int nunits = 2 * g.ngroups;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  for (int unit = blockIdx.x * 8 + w; unit < nunits; unit += gridDim.x * 8) {
+  const int nwalk = 2 * group_list[0];                                      // only the groups that hold particles (cells.cu)
+  for (int u = blockIdx.x * 8 + w; u < nwalk; u += gridDim.x * 8) {
+    const int unit = 2 * group_list[1 + (u >> 1)] + (u & 1);
     {                                                                       // cheap test first: any target at all?
       const int group = unit >> 1, hz = unit & 1;
       int gx, gy, gz;
@@ -703,7 +705,7 @@ static int launch_tile_pass_cfg(sphb200_ctx* ctx, int n, int k, const uint16_t* 
   if (!ctx->unit_tab_valid) {
     const int blocks = (unit_cap + 7) / 8 < 148 * 8 ? (unit_cap + 7) / 8 : 148 * 8;
     CUDA_TRY(cudaMemsetAsync(ctx->unit_tab.p, 0, 64, st));
-    unit_geometry_kernel<<<blocks, 256, 0, st>>>(a.spec, a.cell_start, list16, ks, bufp<int>(ctx->unit_tab) + 16,
+    unit_geometry_kernel<<<blocks, 256, 0, st>>>(a.spec, a.cell_start, bufp<int>(ctx->group_list), list16, ks, bufp<int>(ctx->unit_tab) + 16,
                                                  bufp<int>(ctx->unit_tab), unit_cap);
     ctx->launches += 1;
     CUDA_TRY(cudaGetLastError());

@@ -249,7 +249,10 @@ __global__ void __launch_bounds__(KG_THREADS, KG_MIN_CTAS) knn_group_kernel(KnnG
 
   for (;;) {
     __syncthreads();                                          // previous group done with every buffer
-    if (tid == 0) misc->group = atomicAdd(&a.flags[FL_GROUP_NEXT], 1);
+    if (tid == 0) {
+      const int idx = atomicAdd(&a.flags[FL_GROUP_NEXT], 1);
+      misc->group = a.group_list ? (idx < a.group_list[0] ? a.group_list[1 + idx] : 0x7fffffff) : idx;
+    }
     __syncthreads();
     const int group = misc->group;
     if (group >= g.ngroups) break;
@@ -523,6 +526,7 @@ int launch_knn_group(sphb200_ctx* ctx, int n, int k, double dist, int use_guess,
   a.worklist = bufp<int>(ctx->worklist);
   a.nwork = nwork;
   a.skip_id = ctx->skip_id; a.skip_from = ctx->skip_from;
+  a.group_list = bufp<int>(ctx->group_list);
   const int blocks = 148 * KG_MIN_CTAS;
   if (!dists && ctx->knn_mma && list16) {
     SPH_TRY(launch_knn_mma(ctx, a, st));

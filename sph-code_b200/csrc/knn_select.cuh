@@ -24,6 +24,7 @@ struct KnnGroupArgs {
   int* flags;
   int* worklist;               // unresolved targets (general kernel)
   int* nwork;
+  const int* group_list;       // [0] = number of groups that hold particles, [1..] their ids (cells.cu); nullptr: every group
   const uint32_t* skip_id;     // slab decomposition: targets with skip_id[i] >= skip_from are ghosts (their owner
   uint32_t skip_from;          // searches for them); nullptr = every particle is a target
 };
