@@ -349,6 +349,11 @@ def timed_steps(sess, phases, K, W, amp, barrier, step0=0):
     t_wall = time.perf_counter() - t_wall0
     total_ms = ev[0][0].elapsed_time(ev[K - 1][-1])
     phase_ms = {ph: sum(ev[s][i].elapsed_time(ev[s][i + 1]) for s in range(K)) / K for i, ph in enumerate(names)}
+    per_step = sorted(ev[s][0].elapsed_time(ev[s][-1]) for s in range(K))
+    timed_steps.last_median_ms = per_step[K // 2] if K % 2 else 0.5 * (per_step[K // 2 - 1] + per_step[K // 2])
+    if os.environ.get("BENCH_VERBOSE") == "2":                   # every rank: mean phase times (who waits for whom)
+        sys.stderr.write("rank %s n=%s: %s\n" % (os.environ.get("RANK", "0"), getattr(getattr(sess, "sess", sess), "n", "?"),
+                                                 " ".join("%s=%.3f" % (ph, v) for ph, v in phase_ms.items())))
     if os.environ.get("BENCH_VERBOSE") and int(os.environ.get("RANK", "0")) == 0:
         for s in range(K):
             sys.stderr.write("step %d: %s\n" % (s, " ".join("%s=%.3f" % (ph, ev[s][i].elapsed_time(ev[s][i + 1]))
@@ -410,6 +415,7 @@ def run_ours(args):
     if rank == 0:
         sampler.start()
     total_ms, phase_ms, t_wall = timed_steps(sess, phases, K, W, amp, barrier)
+    median_ms = timed_steps.last_median_ms
     clocks = sampler.stop() if rank == 0 else None
     sess.check()
     launches = sess.launches() - launches0
@@ -443,7 +449,10 @@ def run_ours(args):
                   "particles_total": int(nt2), "steps": k2, "warmup": 3, "ms_per_step": ms2 / k2,
                   "value": nt2 * k2 / (ms2 * 1e-3), "unit": UNIT, "phase_ms": {p: round(v, 4) for p, v in ph2.items()},
                   "per_step_rank0": {k: (v / float(k2 + 3) if k != "knn_worklist_last" else v) for k, v in c2.items()},
-                  "particles_rank0": int(s2.n_owned()), "particles_with_ghosts_rank0": int(s2.sess.n)}
+                  "particles_rank0": int(s2.n_owned()), "particles_with_ghosts_rank0": int(s2.sess.n),
+                  "ms_per_step_median_rank0": round(timed_steps.last_median_ms, 4),
+                  "note": "mean over the timed steps; a step in which a rank's ghost count outgrows its buffers "
+                          "re-allocates them (tens of ms, once): the median is the typical step"}
         sess = s2
 
     if rank != 0:
@@ -494,7 +503,7 @@ def run_ours(args):
             "dtype": "f64", "data": "synthetic",
             "config": run_config(args, world, n_total, parallelism),
             "pair_interactions_per_s": 2.0 * K_NEIGH * value, "gpu_launches": int(launches),
-            "wall_ms_per_step": t_wall / K * 1e3, "clocks": clocks, "roofline": roofline, "kernels": kernels,
+            "wall_ms_per_step": t_wall / K * 1e3, "ms_per_step_median_rank0": round(median_ms, 4), "clocks": clocks, "roofline": roofline, "kernels": kernels,
             "per_step": {k: (v / float(K + W) if k != "knn_worklist_last" else v) for k, v in counters.items()}}
     if verify is not None:
         line["verify"] = verify

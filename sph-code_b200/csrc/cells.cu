@@ -328,7 +328,7 @@ int scan_exclusive_u32(sphb200_ctx* ctx, uint32_t* a, int m, cudaStream_t st) {
 int devbuf_reserve(DevBuf& b, size_t bytes) {
   if (bytes <= b.bytes) return 0;
   if (b.p) { cudaFree(b.p); b.p = nullptr; b.bytes = 0; }
-  size_t want = bytes + bytes / 8 + 256;
+  size_t want = bytes + bytes / 4 + 256;       // head-room: growing a buffer costs a cudaFree + cudaMalloc (device-wide syncs)
   CUDA_TRY(cudaMalloc(&b.p, want));
   b.bytes = want;
   return 0;
