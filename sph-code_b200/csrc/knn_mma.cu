@@ -1,4 +1,4 @@
-// Group-tiled exact k-NN search, tensor-core filter (the session's default fast path).
+// Group-tiled exact k-NN search, tensor-core filter (option knn_mma=1; the default fast path is knn_group.cu).
 // Same contract and the same stages as knn_group.cu (exact fp64 distances in cKDTree's arithmetic, the k smallest
 // by (d^2, index), rows as uint16 tile offsets; replaces /root/reference/sph/navier_stokes_cleaned.py:544,548);
 // only the FILTER that finds the ~50 candidates worth an exact distance differs:
