@@ -258,6 +258,24 @@ class Session(object):
             return
         _lib.check(self.lib.sphb200_session_step(self.ctx.handle, self._stream()))
 
+    def capture_step(self, steps=2):
+        """`steps` time steps captured into ONE CUDA graph (torch.cuda.CUDAGraph); `replay()` runs them with a single
+        launch.  The step makes no host synchronisation and chooses its grid, its time step and its work lists
+        on the device, so the capture holds every kernel of the step; buffers must have reached their size first
+        (run at least one ordinary step before capturing: a capture cannot call cudaMalloc).  `steps` must be even:
+        the sort writes the state into the other half of a pair of buffers and the library flips which half is
+        current on the host, so the captured pointers are right again after two steps.  Not available with
+        self-gravity, whose softening is read back by the host."""
+        if getattr(self, "_gravity", False):
+            raise _lib.Sphb200Error("capture_step: the gravity step reads its softening back on the host")
+        if int(steps) < 2 or int(steps) % 2:
+            raise ValueError("capture_step: an even number of steps (the state buffers alternate every step)")
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            for _ in range(int(steps)):
+                _lib.check(self.lib.sphb200_session_step(self.ctx.handle, self._stream()))
+        return graph
+
     # -- slab decomposition (domain.py drives the collectives) ------------------------------------
     def enable_gid(self):
         _lib.check(self.lib.sphb200_session_enable_gid(self.ctx.handle))

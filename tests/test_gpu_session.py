@@ -282,6 +282,39 @@ def test_search_with_stale_guess(built_lib, kind, n, frac):
     assert worklist >= 0
 
 
+def test_step_in_a_cuda_graph(built_lib):
+    """The whole step is asynchronous and allocation-free once its buffers are sized, so it can be captured in a
+    CUDA graph (two steps per graph: the state buffers alternate): two replays give bit for bit the state of four
+    ordinary steps."""
+    import torch
+    from sphb200 import ics
+    from sphb200.session import Session
+    n = 30000
+    st = ics.uniform_box(n, 51)
+    st["dt_0"] = O.dt_0 * 1e-6
+    runs = []
+    for use_graph in (False, True):
+        s = Session(n, st["N_NEIGH"], st["dist"], dt_0=st["dt_0"])
+        s.upload(st)
+        s.startup()
+        s.step()                                              # sizes every buffer
+        torch.cuda.synchronize()
+        if use_graph:
+            g = s.capture_step(2)
+            for _ in range(2):
+                g.replay()
+        else:
+            for _ in range(4):
+                s.step()
+        torch.cuda.synchronize()
+        s.check()
+        runs.append({f: s.download(f) for f in ("points", "velocities", "sizes", "E_internal", "densities", "neighbor")})
+        runs[-1]["age"] = s.scalar("age")
+        s.close()
+    for f, a in runs[0].items():
+        assert np.array_equal(a, runs[1][f]), f
+
+
 @pytest.mark.parametrize("option", ["knn_mma", "knn_lane", "knn_atomic"])
 def test_search_variants(built_lib, option):
     """The optional forms of the session's fast search (tensor-core filter, lane-per-target kernel, atomic
