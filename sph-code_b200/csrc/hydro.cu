@@ -524,8 +524,8 @@ __global__ void __launch_bounds__(32 * (NCW + NP), MINB) tile_pass_kernel(TilePa
 #endif
     // table entries are requested TP_PREFETCH units ahead, so the producer never waits for a global load
     TpGeom pf[TP_PREFETCH];
-#pragma unroll
     const int ustride = NP * gridDim.x;
+#pragma unroll
     for (int j = 0; j < TP_PREFETCH; ++j) pf[j] = geometry(blockIdx.x + pr * gridDim.x + j * ustride);
     for (int unit = blockIdx.x + pr * gridDim.x; unit < nunits; unit += ustride, it += NP) {
       const TpGeom gm = pf[0];
