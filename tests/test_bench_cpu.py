@@ -60,3 +60,33 @@ def test_ncu_summary_parsers():
     assert bench.ncu_traffic("no_such_kernel") == (None, None)
     assert set(bench.ALGO_BYTES) >= {"sort", "knn", "density", "pi", "force", "integrate"}
     assert sum(bench.ALGO_BYTES[k] for k in ("sort", "knn", "density", "force", "integrate")) == 728.0   # SURVEY.md §8d total
+
+
+def test_numa_helpers_are_harmless_without_a_gpu():
+    """bench.py binds every rank to the CPUs next to its GPU; without NVML / sysfs entries nothing must change."""
+    sys.path.insert(0, ROOT)
+    from sphb200 import domain
+    assert domain._parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert domain._parse_cpulist("") == set()
+    before = os.sched_getaffinity(0)
+    info = domain.gpu_numa_info(0)
+    assert set(info) >= {"bus", "node", "cpus"}
+    changed = domain.bind_to_gpu_numa(0)
+    assert changed in (False, True)
+    if info["node"] < 0:
+        assert changed is False and os.sched_getaffinity(0) == before
+    os.sched_setaffinity(0, before)
+
+
+def test_committed_ncu_summary_feeds_the_roofline():
+    """bench.py takes the k-NN kernel's DRAM traffic and instruction count from the newest committed capture."""
+    sys.path.insert(0, ROOT)
+    import bench
+    traffic, src = bench.ncu_traffic(bench.PHASE_KERNEL["knn"])
+    assert src == "r02_ncu_full_step.txt" and traffic > 1e7
+    assert bench.ncu_particles(src) == 1.0e6
+    inst, src2 = bench.ncu_value(bench.PHASE_KERNEL["knn"], "smsp__inst_executed.sum")
+    assert src2 == src and 5e8 < inst < 2e9
+    for ph in ("density", "pi", "force", "crossing"):
+        t, s = bench.ncu_traffic(bench.PHASE_KERNEL[ph])
+        assert s == src and t > 0
